@@ -1,0 +1,250 @@
+"""CPU oracle bindings — TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference``
+legs may import this package, and only as the checker / the timed CPU baseline.  The product
+(``genogrove_b200``) never imports it.
+
+Two libraries (built by ``oracle/Makefile``):
+
+* ``liboracle.so``       — ``oracle/gg_oracle.c``: plain-C restatement of the reference's intersect path
+                           (array B+ tree with the reference's node shapes + flat filter).
+* ``_ref/libgg_ref.so``  — the UNMODIFIED reference ``grove<interval, uint32_t>`` behind
+                           ``oracle/ref_shim.cpp`` (compiled from /root/reference where it lies).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+NO_CHROM = 0xFFFFFFFF
+
+_u64p = C.POINTER(C.c_uint64)
+_u32p = C.POINTER(C.c_uint32)
+
+
+def _p64(a):
+    return a.ctypes.data_as(_u64p) if a is not None else None
+
+
+def _p32(a):
+    return a.ctypes.data_as(_u32p) if a is not None else None
+
+
+def _u64(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+def _u32(a):
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+def build(verbose: bool = False) -> None:
+    """Compile liboracle.so and (when /root/reference exists) _ref/libgg_ref.so."""
+    r = subprocess.run(["make", "-C", _HERE], capture_output=True, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout, r.stderr)
+    if r.returncode != 0:
+        raise RuntimeError("oracle build failed")
+
+
+_oracle = None
+_ref = None
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        path = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        for name in ("orc_overlaps", "orc_less", "orc_greater"):
+            getattr(L, name).argtypes = [C.c_uint64] * 4
+            getattr(L, name).restype = C.c_int
+        L.orc_distribute_evenly.argtypes = [C.c_uint64, C.c_uint64, _u64p]
+        L.orc_tree_build_bottom_up.argtypes = [_u64p, _u64p, C.c_size_t, C.c_int]
+        L.orc_tree_build_bottom_up.restype = C.c_void_p
+        L.orc_tree_free.argtypes = [C.c_void_p]
+        L.orc_tree_search_overlaps.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.c_size_t]
+        L.orc_tree_search_overlaps.restype = C.c_size_t
+        L.orc_chain_regular.argtypes = [_u64p, _u64p, C.c_size_t, _u32p]
+        L.orc_chain_sorted_append.argtypes = [_u64p, _u64p, C.c_size_t, C.c_int, _u32p]
+        L.orc_chain_stable_sort.argtypes = [_u64p, _u64p, C.c_size_t, _u32p]
+        L.orc_flat_intersect_batch.argtypes = [_u64p, _u64p, _u64p, C.c_uint32, _u32p, _u64p, _u64p,
+                                               C.c_size_t, _u64p, _u64p, _u32p]
+        _oracle = L
+    return _oracle
+
+
+def ref_available() -> bool:
+    return os.path.exists(os.path.join(_HERE, "_ref", "libgg_ref.so"))
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        path = os.path.join(_HERE, "_ref", "libgg_ref.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError("oracle/_ref/libgg_ref.so not built (needs /root/reference)")
+        L = C.CDLL(path)
+        L.ref_create.argtypes = [C.c_int]
+        L.ref_create.restype = C.c_void_p
+        L.ref_destroy.argtypes = [C.c_void_p]
+        L.ref_insert.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int]
+        L.ref_insert_bulk.argtypes = [C.c_void_p, C.c_uint32, _u64p, _u64p, _u32p, C.c_size_t, C.c_int]
+        L.ref_remove.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+        L.ref_intersect.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint64, _u32p, C.c_size_t]
+        L.ref_intersect.restype = C.c_size_t
+        L.ref_intersect_batch.argtypes = [C.c_void_p, _u32p, _u64p, _u64p, C.c_size_t, C.c_int, _u64p,
+                                          _u64p, _u32p, _u64p]
+        L.ref_intersect_batch.restype = C.c_double
+        for name in ("ref_overlaps", "ref_less", "ref_greater"):
+            getattr(L, name).argtypes = [C.c_uint64] * 4
+            getattr(L, name).restype = C.c_int
+        L.ref_distribute_evenly.argtypes = [C.c_uint64, C.c_uint64, _u64p]
+        L.ref_hardware_threads.restype = C.c_int
+        _ref = L
+    return _ref
+
+
+# ----------------------------------------------------------------------------- C restatement
+
+
+def distribute_evenly(total: int, max_per_group: int, lib=None):
+    out = np.zeros(3, dtype=np.uint64)
+    (lib or oracle_lib()).orc_distribute_evenly(total, max_per_group, _p64(out))
+    return tuple(int(x) for x in out)
+
+
+class OracleTree:
+    """Array B+ tree with the reference's shapes (build_tree_bottom_up) + search_overlaps."""
+
+    def __init__(self, start, end, order: int = 3):
+        self.start = _u64(start)
+        self.end = _u64(end)
+        self.n = len(self.start)
+        self._L = oracle_lib()
+        self._t = self._L.orc_tree_build_bottom_up(_p64(self.start), _p64(self.end), self.n, order)
+
+    def intersect(self, qs: int, qe: int) -> np.ndarray:
+        if not self._t:
+            return np.zeros(0, dtype=np.uint64)
+        cap = 64
+        while True:
+            out = np.zeros(cap, dtype=np.uint64)
+            k = self._L.orc_tree_search_overlaps(self._t, qs, qe, _p64(out), cap)
+            if k <= cap:
+                return out[:k]
+            cap = k
+
+    def __del__(self):
+        if getattr(self, "_t", None):
+            self._L.orc_tree_free(self._t)
+            self._t = None
+
+
+def chain_regular(start, end) -> np.ndarray:
+    s, e = _u64(start), _u64(end)
+    perm = np.zeros(len(s), dtype=np.uint32)
+    oracle_lib().orc_chain_regular(_p64(s), _p64(e), len(s), _p32(perm))
+    return perm
+
+
+def chain_sorted_append(start, end, order: int) -> np.ndarray:
+    s, e = _u64(start), _u64(end)
+    perm = np.zeros(len(s), dtype=np.uint32)
+    oracle_lib().orc_chain_sorted_append(_p64(s), _p64(e), len(s), order, _p32(perm))
+    return perm
+
+
+def chain_stable_sort(start, end) -> np.ndarray:
+    s, e = _u64(start), _u64(end)
+    perm = np.zeros(len(s), dtype=np.uint32)
+    oracle_lib().orc_chain_stable_sort(_p64(s), _p64(e), len(s), _p32(perm))
+    return perm
+
+
+def flat_intersect_batch(start, end, coff, qchrom, qs, qe):
+    """Flat oracle over concatenated per-chromosome chains.  Returns (offsets u64[Q+1], ranks u32[H])
+    with per-chromosome chain ranks, ascending per query."""
+    L = oracle_lib()
+    s, e, co = _u64(start), _u64(end), _u64(coff)
+    qc, a, b = _u32(qchrom), _u64(qs), _u64(qe)
+    nq = len(qc)
+    counts = np.zeros(nq, dtype=np.uint64)
+    L.orc_flat_intersect_batch(_p64(s), _p64(e), _p64(co), len(co) - 1, _p32(qc), _p64(a), _p64(b), nq,
+                               _p64(counts), None, None)
+    offsets = np.zeros(nq + 1, dtype=np.uint64)
+    np.cumsum(counts, out=offsets[1:])
+    out = np.zeros(max(int(offsets[-1]), 1), dtype=np.uint32)
+    L.orc_flat_intersect_batch(_p64(s), _p64(e), _p64(co), len(co) - 1, _p32(qc), _p64(a), _p64(b), nq,
+                               None, _p64(offsets), _p32(out))
+    return offsets, out[: int(offsets[-1])]
+
+
+# ----------------------------------------------------------------------------- the real reference
+
+
+class RefGrove:
+    """The unmodified reference grove<interval, uint32_t> (payload = id)."""
+
+    REGULAR, SORTED = 0, 1
+
+    def __init__(self, order: int = 3):
+        self._L = ref_lib()
+        self._g = self._L.ref_create(order)
+        if not self._g:
+            raise ValueError("grove order must be >= 3")
+
+    def insert(self, chrom: int, start: int, end: int, id_: int, mode: int = 0) -> None:
+        if self._L.ref_insert(self._g, chrom, start, end, id_, mode) != 0:
+            raise ValueError("interval: start must be <= end")
+
+    def insert_bulk(self, chrom: int, start, end, ids, presorted: bool = False) -> None:
+        s, e, i = _u64(start), _u64(end), _u32(ids)
+        if self._L.ref_insert_bulk(self._g, chrom, _p64(s), _p64(e), _p32(i), len(s), int(presorted)) != 0:
+            raise ValueError("interval: start must be <= end")
+
+    def remove(self, chrom: int, id_: int) -> bool:
+        return bool(self._L.ref_remove(self._g, chrom, id_))
+
+    def intersect(self, chrom: int, qs: int, qe: int) -> np.ndarray:
+        cap = 64
+        while True:
+            out = np.zeros(cap, dtype=np.uint32)
+            k = self._L.ref_intersect(self._g, chrom, qs, qe, _p32(out), cap)
+            if k <= cap:
+                return out[:k]
+            cap = k
+
+    def intersect_batch(self, qchrom, qs, qe, threads: int = 1, want_ids: bool = True):
+        """Returns (offsets, ids, seconds_of_query_loop)."""
+        qc, a, b = _u32(qchrom), _u64(qs), _u64(qe)
+        nq = len(qc)
+        counts = np.zeros(nq, dtype=np.uint64)
+        chk = C.c_uint64(0)
+        secs = self._L.ref_intersect_batch(self._g, _p32(qc), _p64(a), _p64(b), nq, threads, _p64(counts),
+                                           None, None, C.byref(chk))
+        offsets = np.zeros(nq + 1, dtype=np.uint64)
+        np.cumsum(counts, out=offsets[1:])
+        if not want_ids:
+            return offsets, None, secs
+        ids = np.zeros(max(int(offsets[-1]), 1), dtype=np.uint32)
+        self._L.ref_intersect_batch(self._g, _p32(qc), _p64(a), _p64(b), nq, threads, None, _p64(offsets),
+                                    _p32(ids), C.byref(chk))
+        return offsets, ids[: int(offsets[-1])], secs
+
+    def hardware_threads(self) -> int:
+        return int(self._L.ref_hardware_threads())
+
+    def close(self):
+        if getattr(self, "_g", None):
+            self._L.ref_destroy(self._g)
+            self._g = None
+
+    def __del__(self):
+        self.close()
