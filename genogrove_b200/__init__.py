@@ -1,0 +1,10 @@
+"""genogrove_b200 — B200-native batched interval-overlap engine for genogrove's grove intersect path.
+
+The product is the CUDA library ``libgg_b200.so`` (C ABI: include/gg_b200.h).  This package holds its sources
+(``csrc/``), a ctypes binding (``index.DeviceIndex``), the Python flavour of the host-side mirror of the
+reference's grove API (``grove.Grove``; the C++20 drop-in facade is include/genogrove_b200/grove.hpp), the
+synthetic workload generators of BASELINE.json (``synth``) and the multi-GPU sharding helpers (``shard``).
+There is no CPU implementation of the path anywhere in this package.
+"""
+from .index import DeviceIndex, GGError, NO_CHROM, TIE_EXPLICIT, TIE_INPUT_ORDER, TIE_REVERSE_INPUT, PinnedArray  # noqa: F401
+from .grove import Grove, Interval, Key, QueryResult  # noqa: F401

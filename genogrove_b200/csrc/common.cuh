@@ -1,0 +1,69 @@
+// common.cuh — shared device/host helpers for libgg_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gg {
+
+constexpr int kFanout = 32;      // keys per node of the implicit B+ tree (one 128-byte line of u32)
+constexpr int kFanoutLog2 = 5;
+constexpr int kMaxLevels = 8;    // 32^7 > 2^32 ranks: 7 levels suffice; 8 leaves slack
+
+template <typename T>
+struct coord_max;
+template <>
+struct coord_max<uint32_t> {
+    static constexpr uint32_t value = 0xFFFFFFFFu;
+};
+template <>
+struct coord_max<uint64_t> {
+    static constexpr uint64_t value = 0xFFFFFFFFFFFFFFFFull;
+};
+
+__host__ __device__ inline uint64_t div_up(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+__host__ __device__ inline uint64_t round_up(uint64_t a, uint64_t b) { return div_up(a, b) * b; }
+
+// ---------------------------------------------------------------- mbarrier + TMA bulk copy (1-D)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA bulk copy global -> shared (SASS: UBLKCP).  dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// ---------------------------------------------------------------- loads
+template <typename T>
+__device__ __forceinline__ T ld_volatile(const T* p) {
+    return *reinterpret_cast<const volatile T*>(p);
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+}  // namespace gg

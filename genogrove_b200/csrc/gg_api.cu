@@ -1,0 +1,944 @@
+// gg_api.cu — C ABI (include/gg_b200.h) and host orchestration of libgg_b200.so.
+//
+// No torch, no C++ types across the boundary.  Everything that computes launches the hand-written
+// sm_100a kernels in radix_sort.cuh / scan.cuh / build.cuh / intersect.cuh; there is no CPU path.
+#include "../../include/gg_b200.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "build.cuh"
+#include "common.cuh"
+#include "intersect.cuh"
+#include "radix_sort.cuh"
+#include "scan.cuh"
+
+using namespace gg;
+
+namespace {
+
+constexpr int kSlots = 3;        // pipeline depth of the host-buffer path
+constexpr int kCountThreadsDefault = 512;
+
+struct DeviceBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap && p) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes ? bytes : 16;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T>
+    T* as() const {
+        return static_cast<T*>(p);
+    }
+};
+
+struct Slot {
+    cudaStream_t st = nullptr;
+    DeviceBuf qc, qs, qe, cnt, hi, off, hits, scan;
+    cudaEvent_t ev_scan = nullptr, ev_total = nullptr, ev_done = nullptr;
+    uint64_t* h_next_base = nullptr;  // pinned
+    bool busy = false;
+};
+
+}  // namespace
+
+struct gg_index {
+    int device = 0;
+    int sm_count = 148;
+    std::string err;
+    cudaStream_t stream = nullptr;  // build + two-phase host API
+
+    // ---- index snapshot
+    bool built = false;
+    int coord_bytes = 4;
+    uint64_t n = 0;
+    uint32_t n_chrom = 0;
+    int n_levels = 0;
+    int stage_level = 0;
+    uint32_t staged_elems = 0;
+    uint64_t total_elems = 0;
+    DeviceBuf S, E, M, tab, cnt;
+    std::vector<uint64_t> h_cnt;
+    std::vector<uint32_t> h_tab;   // [n_levels][n_chrom+1]
+    std::vector<uint64_t> h_lvbase;
+    gg_index_stats istats{};
+
+    // ---- device-API scratch
+    DeviceBuf q_cnt, q_hi, scan_scratch, err_flag;
+    size_t counted_nq = 0;
+    bool timing = false;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool ev_count_valid = false, ev_emit_valid = false;
+
+    // ---- two-phase host API state
+    DeviceBuf h2_qc, h2_qs, h2_qe, h2_off, h2_hits;
+    size_t h2_nq = 0;
+    uint64_t h2_total = 0;
+    bool h2_valid = false;
+
+    // ---- pipelined host path
+    Slot slots[kSlots];
+    bool slots_ready = false;
+    DeviceBuf d_base;
+    uint32_t* pinned_hits = nullptr;
+    size_t pinned_cap = 0;  // elements
+    uint32_t* h_err = nullptr;  // pinned
+
+    // ---- options
+    int64_t chunk_queries = 8388608;
+    int64_t stage_bytes = 98304;
+    int64_t count_threads = kCountThreadsDefault;
+    int64_t count_ctas_per_sm = 0;  // 0 = occupancy API
+    int64_t emit_ctas_per_sm = 0;
+
+    gg_batch_stats bstats{};
+};
+
+namespace {
+
+gg_status fail(gg_index* idx, gg_status st, const char* what, cudaError_t e = cudaSuccess) {
+    if (idx) {
+        idx->err = what;
+        if (e != cudaSuccess) {
+            idx->err += ": ";
+            idx->err += cudaGetErrorString(e);
+        }
+    }
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        return GG_ERR_OOM;
+    }
+    return st;
+}
+
+#define GG_CUDA(call)                                                    \
+    do {                                                                 \
+        cudaError_t e_ = (call);                                         \
+        if (e_ != cudaSuccess) return fail(idx, GG_ERR_CUDA, #call, e_); \
+    } while (0)
+
+inline unsigned blocks_for(size_t n, unsigned threads) { return static_cast<unsigned>(div_up(n ? n : 1, threads)); }
+
+template <typename C>
+IndexView<C> make_view(const gg_index* idx) {
+    IndexView<C> v;
+    v.S = idx->S.as<C>();
+    v.E = idx->E.as<C>();
+    v.M = idx->M.as<C>();
+    v.tab = idx->tab.as<uint32_t>();
+    v.cnt = idx->cnt.as<uint32_t>();
+    v.n_chrom = idx->n_chrom;
+    v.n_levels = idx->n_levels;
+    v.stage_level = idx->stage_level;
+    v.staged_elems = idx->staged_elems;
+    return v;
+}
+
+size_t count_smem_bytes(const gg_index* idx) {
+    size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
+    return 2 * static_cast<size_t>(idx->staged_elems) * idx->coord_bytes + ((tab_elems + 3) & ~size_t(3)) * 4 + 16;
+}
+size_t emit_smem_bytes(const gg_index* idx) {
+    size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
+    return tab_elems * 4 + 16;
+}
+
+template <typename C, typename Q>
+gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, size_t nq,
+                       uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, cudaStream_t st) {
+    auto kern = intersect_count_kernel<C, Q>;
+    size_t smem = count_smem_bytes(idx);
+    GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int threads = static_cast<int>(idx->count_threads);
+    int per_sm = static_cast<int>(idx->count_ctas_per_sm);
+    if (per_sm <= 0) {
+        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+        if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
+    }
+    size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(threads));
+    unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+    kern<<<grid, threads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi, d_err);
+    GG_CUDA(cudaGetLastError());
+    idx->bstats.kernel_launches++;
+    return GG_OK;
+}
+
+template <typename C, typename Q>
+gg_status launch_emit(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, size_t nq, const uint32_t* d_hi,
+                      const uint64_t* d_off, uint32_t* d_hits, uint64_t hits_base, cudaStream_t st) {
+    auto kern = intersect_emit_kernel<C, Q>;
+    size_t smem = emit_smem_bytes(idx);
+    if (smem > 48 * 1024)
+        GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int per_sm = static_cast<int>(idx->emit_ctas_per_sm);
+    if (per_sm <= 0) {
+        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+        if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "emit kernel does not fit on an SM");
+    }
+    size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads));
+    unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+    kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_hi, d_off, d_hits, hits_base);
+    GG_CUDA(cudaGetLastError());
+    idx->bstats.kernel_launches++;
+    return GG_OK;
+}
+
+// dispatch on (index coord width, query coord width)
+gg_status dispatch_count(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                         int q_bytes, size_t nq, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, cudaStream_t st) {
+    if (idx->coord_bytes == 4 && q_bytes == 4)
+        return launch_count<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+    if (idx->coord_bytes == 4 && q_bytes == 8)
+        return launch_count<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+    if (idx->coord_bytes == 8 && q_bytes == 4)
+        return launch_count<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+    return launch_count<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+}
+gg_status dispatch_emit(gg_index* idx, const uint32_t* d_chrom, const void* d_start, int q_bytes, size_t nq,
+                        const uint32_t* d_hi, const uint64_t* d_off, uint32_t* d_hits, uint64_t hits_base,
+                        cudaStream_t st) {
+    if (idx->coord_bytes == 4 && q_bytes == 4)
+        return launch_emit<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+    if (idx->coord_bytes == 4 && q_bytes == 8)
+        return launch_emit<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+    if (idx->coord_bytes == 8 && q_bytes == 4)
+        return launch_emit<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+    return launch_emit<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+}
+
+// ------------------------------------------------------------------------------------------ build
+
+// Level geometry from per-chromosome counts (host; C is small).  Fills h_tab / h_lvbase / n_levels.
+gg_status plan_levels(gg_index* idx) {
+    const uint32_t C = idx->n_chrom;
+    int depth = 1;
+    for (uint32_t c = 0; c < C; ++c) {
+        uint64_t m = idx->h_cnt[c];
+        int d = 1;
+        while (m > kFanout) {
+            m = div_up(m, kFanout);
+            ++d;
+        }
+        depth = std::max(depth, d);
+    }
+    if (depth > kMaxLevels) return fail(idx, GG_ERR_CAPACITY, "too many levels");
+    idx->n_levels = depth;
+    std::vector<std::vector<uint64_t>> sz(depth, std::vector<uint64_t>(C));
+    std::vector<uint64_t> level_total(depth, 0);
+    for (uint32_t c = 0; c < C; ++c) {
+        uint64_t m = idx->h_cnt[c];
+        for (int l = 0; l < depth; ++l) {
+            sz[l][c] = round_up(std::max<uint64_t>(m, 1), kFanout);
+            level_total[l] += sz[l][c];
+            m = div_up(m, kFanout);
+        }
+    }
+    idx->h_lvbase.assign(depth + 1, 0);
+    uint64_t run = 0;
+    for (int l = depth - 1; l >= 0; --l) {  // top level first
+        idx->h_lvbase[l] = run;
+        run += level_total[l];
+    }
+    idx->total_elems = run;
+    if (run >= 0xFFFFFFFFull) return fail(idx, GG_ERR_CAPACITY, "index exceeds 2^32-1 padded ranks per handle");
+    idx->h_tab.assign(static_cast<size_t>(depth) * (C + 1), 0);
+    for (int l = 0; l < depth; ++l) {
+        uint64_t off = idx->h_lvbase[l];
+        for (uint32_t c = 0; c < C; ++c) {
+            idx->h_tab[static_cast<size_t>(l) * (C + 1) + c] = static_cast<uint32_t>(off);
+            off += sz[l][c];
+        }
+        idx->h_tab[static_cast<size_t>(l) * (C + 1) + C] = static_cast<uint32_t>(off);
+    }
+    // staging: the longest top-first prefix of whole levels with 2 * bytes <= stage_bytes
+    idx->stage_level = depth;
+    idx->staged_elems = 0;
+    for (int l = depth - 1; l >= 0; --l) {
+        uint64_t prefix = idx->h_lvbase[l] + level_total[l];
+        if (2 * prefix * idx->coord_bytes > static_cast<uint64_t>(idx->stage_bytes)) break;
+        idx->stage_level = l;
+        idx->staged_elems = static_cast<uint32_t>(prefix);
+    }
+    return GG_OK;
+}
+
+template <typename Field, typename Key>
+gg_status sort_by_field(gg_index* idx, const Field* d_field, int nbits, Key* keys_a, Key* keys_b, uint32_t*& perm,
+                        uint32_t*& perm_alt, size_t n, RadixWorkspace& ws, cudaStream_t st) {
+    if (nbits <= 0 || n == 0) return GG_OK;
+    gather_field_kernel<Field, Key><<<blocks_for(n, 256), 256, 0, st>>>(d_field, perm, keys_a, n);
+    ws.launches++;
+    bool in_alt = false;
+    GG_CUDA(radix_sort_pairs<Key>(keys_a, keys_b, perm, perm_alt, n, nbits, ws, st, &in_alt));
+    if (in_alt) std::swap(perm, perm_alt);
+    return GG_OK;
+}
+
+// Shared by gg_index_build (do_sort = true) and gg_index_upload_sorted (do_sort = false).
+gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
+                     const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom, uint32_t* rank_to_input,
+                     bool do_sort) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    idx->built = false;
+    idx->h2_valid = false;
+    if (n_chrom == 0 || n_chrom == GG_NO_CHROM) return fail(idx, GG_ERR_INVALID_ARG, "n_chrom must be in [1, 2^32-2]");
+    if (n > 0 && (!chrom || !start || !end)) return fail(idx, GG_ERR_INVALID_ARG, "null input array");
+    if (tie_mode == GG_TIE_EXPLICIT && !tie_key && n > 0) return fail(idx, GG_ERR_INVALID_ARG, "GG_TIE_EXPLICIT needs tie_key");
+    if (tie_mode < 0 || tie_mode > 2) return fail(idx, GG_ERR_INVALID_ARG, "bad tie_mode");
+    if (n >= 0xFFFFFFF0ull) return fail(idx, GG_ERR_CAPACITY, "more than 2^32-16 intervals per handle");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    cudaEvent_t e0, e1, e2, e3;
+    GG_CUDA(cudaEventCreate(&e0));
+    GG_CUDA(cudaEventCreate(&e1));
+    GG_CUDA(cudaEventCreate(&e2));
+    GG_CUDA(cudaEventCreate(&e3));
+
+    // temporaries (freed on every exit path by the guard)
+    DeviceBuf d_chrom, d_start, d_end, d_tie, d_stats, d_perm, d_perm_alt, d_perm_end, d_perm_end_alt, d_keys_a, d_keys_b,
+        d_hist, d_scan, d_cbegin, d_s32, d_e32;
+    struct Guard {
+        std::vector<DeviceBuf*> bufs;
+        std::vector<cudaEvent_t> evs;
+        ~Guard() {
+            for (auto* b : bufs) b->release();
+            for (auto e : evs) cudaEventDestroy(e);
+        }
+    } guard;
+    guard.bufs = {&d_chrom, &d_start, &d_end, &d_tie, &d_stats, &d_perm, &d_perm_alt, &d_perm_end, &d_perm_end_alt,
+                  &d_keys_a, &d_keys_b, &d_hist, &d_scan, &d_cbegin, &d_s32, &d_e32};
+    guard.evs = {e0, e1, e2, e3};
+
+    const size_t nn = n ? n : 1;
+    GG_CUDA(cudaEventRecord(e0, st));
+    GG_CUDA(d_chrom.ensure(nn * 4));
+    GG_CUDA(d_start.ensure(nn * 8));
+    GG_CUDA(d_end.ensure(nn * 8));
+    GG_CUDA(d_stats.ensure(sizeof(BuildStats)));
+    GG_CUDA(idx->cnt.ensure(static_cast<size_t>(n_chrom) * 4));
+    GG_CUDA(cudaMemsetAsync(d_stats.p, 0, sizeof(BuildStats), st));
+    GG_CUDA(cudaMemsetAsync(idx->cnt.p, 0, static_cast<size_t>(n_chrom) * 4, st));
+    if (n) {
+        GG_CUDA(cudaMemcpyAsync(d_chrom.p, chrom, n * 4, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(d_start.p, start, n * 8, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(d_end.p, end, n * 8, cudaMemcpyHostToDevice, st));
+        if (tie_mode == GG_TIE_EXPLICIT) {
+            GG_CUDA(d_tie.ensure(n * 8));
+            GG_CUDA(cudaMemcpyAsync(d_tie.p, tie_key, n * 8, cudaMemcpyHostToDevice, st));
+        }
+        index_stats_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(),
+                                                              d_end.as<uint64_t>(), d_tie.as<uint64_t>(), n, n_chrom,
+                                                              idx->cnt.as<uint32_t>(), d_stats.as<BuildStats>());
+        if (!do_sort)
+            check_chain_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(), n,
+                                                                  d_stats.as<BuildStats>());
+    }
+    BuildStats hs{};
+    std::vector<uint32_t> h_cnt32(n_chrom);
+    GG_CUDA(cudaMemcpyAsync(&hs, d_stats.p, sizeof(BuildStats), cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaMemcpyAsync(h_cnt32.data(), idx->cnt.p, static_cast<size_t>(n_chrom) * 4, cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaStreamSynchronize(st));
+    if (hs.invalid_chrom) return fail(idx, GG_ERR_INVALID_ARG, "chrom id >= n_chrom in index input");
+    if (hs.invalid_interval) return fail(idx, GG_ERR_INVALID_INTERVAL, "interval: start must be <= end");
+    if (hs.unsorted) return fail(idx, GG_ERR_UNSORTED, "upload_sorted input is not in (chrom, start) order");
+
+    idx->n = n;
+    idx->n_chrom = n_chrom;
+    idx->coord_bytes = (hs.max_coord > 0xFFFFFFFFull) ? 8 : 4;
+    idx->h_cnt.assign(h_cnt32.begin(), h_cnt32.end());
+    gg_status ps = plan_levels(idx);
+    if (ps != GG_OK) return ps;
+    const uint32_t C = n_chrom;
+
+    std::vector<uint32_t> h_cbegin(C + 1, 0);
+    for (uint32_t c = 0; c < C; ++c) h_cbegin[c + 1] = h_cbegin[c] + h_cnt32[c];
+    GG_CUDA(d_cbegin.ensure((C + 1) * 4));
+    GG_CUDA(cudaMemcpyAsync(d_cbegin.p, h_cbegin.data(), (C + 1) * 4, cudaMemcpyHostToDevice, st));
+    GG_CUDA(idx->tab.ensure(idx->h_tab.size() * 4));
+    GG_CUDA(cudaMemcpyAsync(idx->tab.p, idx->h_tab.data(), idx->h_tab.size() * 4, cudaMemcpyHostToDevice, st));
+
+    // ---- sort: permutation of input indices in leaf-chain order, then in (chrom, end) order
+    const bool wide = idx->coord_bytes == 8;
+    const int coord_bits = bits_needed(hs.max_coord);
+    const int chrom_bits = bits_needed(C - 1);
+    RadixWorkspace ws;
+    GG_CUDA(d_perm.ensure(nn * 4));
+    GG_CUDA(d_perm_alt.ensure(nn * 4));
+    GG_CUDA(d_perm_end.ensure(nn * 4));
+    GG_CUDA(d_perm_end_alt.ensure(nn * 4));
+    GG_CUDA(d_keys_a.ensure(nn * 8));
+    GG_CUDA(d_keys_b.ensure(nn * 8));
+    GG_CUDA(d_hist.ensure(radix_hist_entries(n) * 4));
+    GG_CUDA(d_scan.ensure(scan_state_bytes(radix_hist_entries(n))));
+    ws.hist = d_hist.as<uint32_t>();
+    ws.scan_scratch = d_scan.p;
+
+    // narrowed copies of the coordinates (u32 layout) in input order
+    const void* src_s = d_start.p;
+    const void* src_e = d_end.p;
+    if (!wide) {
+        GG_CUDA(d_s32.ensure(nn * 4));
+        GG_CUDA(d_e32.ensure(nn * 4));
+        if (n) {
+            narrow_kernel<uint32_t><<<blocks_for(n, 256), 256, 0, st>>>(d_start.as<uint64_t>(), d_s32.as<uint32_t>(), n);
+            narrow_kernel<uint32_t><<<blocks_for(n, 256), 256, 0, st>>>(d_end.as<uint64_t>(), d_e32.as<uint32_t>(), n);
+        }
+        src_s = d_s32.p;
+        src_e = d_e32.p;
+    }
+
+    GG_CUDA(cudaEventRecord(e1, st));
+    uint32_t* perm = d_perm.as<uint32_t>();
+    uint32_t* perm_alt = d_perm_alt.as<uint32_t>();
+    uint32_t* perm_end = d_perm_end.as<uint32_t>();
+    uint32_t* perm_end_alt = d_perm_end_alt.as<uint32_t>();
+    gg_status s = GG_OK;
+    if (n) {
+        if (do_sort) {
+            iota_kernel<<<blocks_for(n, 256), 256, 0, st>>>(perm, n, tie_mode == GG_TIE_REVERSE_INPUT ? 1 : 0);
+            // least significant field first: tie, end, start, chrom
+            if (tie_mode == GG_TIE_EXPLICIT)
+                s = sort_by_field<uint64_t, uint64_t>(idx, d_tie.as<uint64_t>(), bits_needed(hs.max_tie), d_keys_a.as<uint64_t>(), d_keys_b.as<uint64_t>(), perm, perm_alt, n, ws, st);
+            if (s != GG_OK) return s;
+            if (wide) {
+                s = sort_by_field<uint64_t, uint64_t>(idx, d_end.as<uint64_t>(), coord_bits, d_keys_a.as<uint64_t>(), d_keys_b.as<uint64_t>(), perm, perm_alt, n, ws, st);
+                if (s == GG_OK) s = sort_by_field<uint64_t, uint64_t>(idx, d_start.as<uint64_t>(), coord_bits, d_keys_a.as<uint64_t>(), d_keys_b.as<uint64_t>(), perm, perm_alt, n, ws, st);
+            } else {
+                s = sort_by_field<uint32_t, uint32_t>(idx, d_e32.as<uint32_t>(), coord_bits, d_keys_a.as<uint32_t>(), d_keys_b.as<uint32_t>(), perm, perm_alt, n, ws, st);
+                if (s == GG_OK) s = sort_by_field<uint32_t, uint32_t>(idx, d_s32.as<uint32_t>(), coord_bits, d_keys_a.as<uint32_t>(), d_keys_b.as<uint32_t>(), perm, perm_alt, n, ws, st);
+            }
+            if (s == GG_OK) s = sort_by_field<uint32_t, uint32_t>(idx, d_chrom.as<uint32_t>(), chrom_bits, d_keys_a.as<uint32_t>(), d_keys_b.as<uint32_t>(), perm, perm_alt, n, ws, st);
+            if (s != GG_OK) return s;
+        } else {
+            iota_kernel<<<blocks_for(n, 256), 256, 0, st>>>(perm, n, 0);
+        }
+        // ends sorted per chromosome (E family): sort input indices by (chrom, end)
+        iota_kernel<<<blocks_for(n, 256), 256, 0, st>>>(perm_end, n, 0);
+        if (wide)
+            s = sort_by_field<uint64_t, uint64_t>(idx, d_end.as<uint64_t>(), coord_bits, d_keys_a.as<uint64_t>(), d_keys_b.as<uint64_t>(), perm_end, perm_end_alt, n, ws, st);
+        else
+            s = sort_by_field<uint32_t, uint32_t>(idx, d_e32.as<uint32_t>(), coord_bits, d_keys_a.as<uint32_t>(), d_keys_b.as<uint32_t>(), perm_end, perm_end_alt, n, ws, st);
+        if (s == GG_OK) s = sort_by_field<uint32_t, uint32_t>(idx, d_chrom.as<uint32_t>(), chrom_bits, d_keys_a.as<uint32_t>(), d_keys_b.as<uint32_t>(), perm_end, perm_end_alt, n, ws, st);
+        if (s != GG_OK) return s;
+    }
+    GG_CUDA(cudaEventRecord(e2, st));
+
+    // ---- padded SoA leaf level + upper levels
+    const size_t fam_bytes = static_cast<size_t>(idx->total_elems) * idx->coord_bytes;
+    GG_CUDA(idx->S.ensure(fam_bytes));
+    GG_CUDA(idx->E.ensure(fam_bytes));
+    GG_CUDA(idx->M.ensure(fam_bytes));
+    const uint32_t* tab0 = idx->tab.as<uint32_t>();
+    const uint32_t level0_elems = idx->h_tab[C] - idx->h_tab[0];
+    if (wide)
+        pad_leaf_kernel<uint64_t><<<blocks_for(level0_elems, 256), 256, 0, st>>>(
+            perm, perm_end, (const uint64_t*)src_s, (const uint64_t*)src_e, d_cbegin.as<uint32_t>(), idx->cnt.as<uint32_t>(),
+            tab0, C, idx->S.as<uint64_t>(), idx->E.as<uint64_t>(), idx->M.as<uint64_t>());
+    else
+        pad_leaf_kernel<uint32_t><<<blocks_for(level0_elems, 256), 256, 0, st>>>(
+            perm, perm_end, (const uint32_t*)src_s, (const uint32_t*)src_e, d_cbegin.as<uint32_t>(), idx->cnt.as<uint32_t>(),
+            tab0, C, idx->S.as<uint32_t>(), idx->E.as<uint32_t>(), idx->M.as<uint32_t>());
+    for (int l = 1; l < idx->n_levels; ++l) {
+        const uint32_t* row = tab0 + static_cast<size_t>(l) * (C + 1);
+        const uint32_t* row_below = tab0 + static_cast<size_t>(l - 1) * (C + 1);
+        const uint32_t entries = idx->h_tab[static_cast<size_t>(l) * (C + 1) + C] - idx->h_tab[static_cast<size_t>(l) * (C + 1)];
+        const unsigned warps_per_block = 8;
+        if (wide)
+            build_level_kernel<uint64_t><<<blocks_for(entries, warps_per_block), warps_per_block * 32, 0, st>>>(
+                idx->S.as<uint64_t>(), idx->E.as<uint64_t>(), idx->M.as<uint64_t>(), row, row_below, C);
+        else
+            build_level_kernel<uint32_t><<<blocks_for(entries, warps_per_block), warps_per_block * 32, 0, st>>>(
+                idx->S.as<uint32_t>(), idx->E.as<uint32_t>(), idx->M.as<uint32_t>(), row, row_below, C);
+    }
+    GG_CUDA(cudaGetLastError());
+    if (rank_to_input && n) GG_CUDA(cudaMemcpyAsync(rank_to_input, perm, n * 4, cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaEventRecord(e3, st));
+    GG_CUDA(cudaStreamSynchronize(st));
+
+    float ms_sort = 0, ms_levels = 0, ms_total = 0;
+    cudaEventElapsedTime(&ms_sort, e1, e2);
+    cudaEventElapsedTime(&ms_levels, e2, e3);
+    cudaEventElapsedTime(&ms_total, e0, e3);
+    idx->istats.n_intervals = n;
+    idx->istats.n_chrom = C;
+    idx->istats.coord_bytes = idx->coord_bytes;
+    idx->istats.n_levels = idx->n_levels;
+    idx->istats.fanout = kFanout;
+    idx->istats.staged_levels = idx->n_levels - idx->stage_level;
+    idx->istats.device_bytes = 3 * fam_bytes + idx->h_tab.size() * 4 + static_cast<size_t>(C) * 4;
+    idx->istats.sort_ms = ms_sort;
+    idx->istats.levels_ms = ms_levels;
+    idx->istats.total_ms = ms_total;
+    idx->built = true;
+    return GG_OK;
+}
+
+// ------------------------------------------------------------------------------------------ device path
+
+gg_status ensure_query_scratch(gg_index* idx, size_t nq) {
+    const size_t m = nq ? nq : 1;
+    GG_CUDA(idx->q_cnt.ensure(m * 4));
+    GG_CUDA(idx->q_hi.ensure(m * 4));
+    GG_CUDA(idx->scan_scratch.ensure(scan_state_bytes(m)));
+    GG_CUDA(idx->err_flag.ensure(16));
+    return GG_OK;
+}
+
+gg_status check_query_error(gg_index* idx, cudaStream_t st) {
+    uint32_t flag = 0;
+    GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaStreamSynchronize(st));
+    if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+    return GG_OK;
+}
+
+gg_status ensure_slots(gg_index* idx) {
+    if (idx->slots_ready) return GG_OK;
+    for (int i = 0; i < kSlots; ++i) {
+        Slot& s = idx->slots[i];
+        GG_CUDA(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+        GG_CUDA(cudaEventCreateWithFlags(&s.ev_scan, cudaEventDisableTiming));
+        GG_CUDA(cudaEventCreateWithFlags(&s.ev_total, cudaEventDisableTiming));
+        GG_CUDA(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
+        GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&s.h_next_base), 16, cudaHostAllocDefault));
+    }
+    GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&idx->h_err), 16, cudaHostAllocDefault));
+    idx->slots_ready = true;
+    return GG_OK;
+}
+
+gg_status ensure_pinned_hits(gg_index* idx, size_t need_elems, size_t keep_elems) {
+    if (need_elems <= idx->pinned_cap && idx->pinned_hits) return GG_OK;
+    size_t want = std::max<size_t>(need_elems, 1024);
+    uint32_t* np = nullptr;
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&np), want * 4, cudaHostAllocDefault);
+    if (e != cudaSuccess) return fail(idx, GG_ERR_OOM, "pinned hit buffer", e);
+    if (idx->pinned_hits) {
+        if (keep_elems) std::memcpy(np, idx->pinned_hits, keep_elems * 4);
+        cudaFreeHost(idx->pinned_hits);
+    }
+    idx->pinned_hits = np;
+    idx->pinned_cap = want;
+    return GG_OK;
+}
+
+// The reference-facing host-buffer call: chunked count -> scan -> emit pipeline over kSlots streams.
+template <typename Q>
+gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* q_start, const Q* q_end, size_t nq,
+                               uint64_t* offsets, const uint32_t** hits, uint64_t* n_hits) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!offsets || !hits || !n_hits || (nq && (!q_chrom || !q_start || !q_end)))
+        return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (sizeof(Q) == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    gg_status s = ensure_slots(idx);
+    if (s != GG_OK) return s;
+    idx->h2_valid = false;
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+
+    const size_t chunk = static_cast<size_t>(std::max<int64_t>(idx->chunk_queries, kScanTile) / kScanTile * kScanTile);
+    const size_t n_chunks = nq ? div_up(nq, chunk) : 0;
+    idx->bstats.n_chunks = static_cast<uint32_t>(n_chunks);
+    *hits = nullptr;
+    *n_hits = 0;
+    if (nq == 0) {
+        offsets[0] = 0;
+        s = ensure_pinned_hits(idx, 1, 0);
+        *hits = idx->pinned_hits;
+        return s;
+    }
+    GG_CUDA(idx->d_base.ensure((n_chunks + 1) * 8));
+    GG_CUDA(idx->err_flag.ensure(16));
+    cudaStream_t st0 = idx->slots[0].st;
+    GG_CUDA(cudaMemsetAsync(idx->d_base.p, 0, 8, st0));
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st0));
+    GG_CUDA(cudaStreamSynchronize(st0));
+    for (int i = 0; i < kSlots; ++i) idx->slots[i].busy = false;
+
+    std::vector<uint64_t> base(n_chunks + 1, 0);
+    cudaEvent_t prev_scan = nullptr;
+
+    // stage A: H2D + count + scan for chunk k
+    auto stage_a = [&](size_t k) -> gg_status {
+        Slot& sl = idx->slots[k % kSlots];
+        if (sl.busy) {
+            GG_CUDA(cudaEventSynchronize(sl.ev_done));
+            sl.busy = false;
+        }
+        const size_t q0 = k * chunk, m = std::min(chunk, nq - q0);
+        GG_CUDA(sl.qc.ensure(m * 4));
+        GG_CUDA(sl.qs.ensure(m * sizeof(Q)));
+        GG_CUDA(sl.qe.ensure(m * sizeof(Q)));
+        GG_CUDA(sl.cnt.ensure(m * 4));
+        GG_CUDA(sl.hi.ensure(m * 4));
+        GG_CUDA(sl.off.ensure((m + 1) * 8));
+        GG_CUDA(sl.scan.ensure(scan_state_bytes(m)));
+        GG_CUDA(cudaMemcpyAsync(sl.qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qs.p, q_start + q0, m * sizeof(Q), cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qe.p, q_end + q0, m * sizeof(Q), cudaMemcpyHostToDevice, sl.st));
+        gg_status r = dispatch_count(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, sizeof(Q), m, sl.cnt.as<uint32_t>(),
+                                     sl.hi.as<uint32_t>(), idx->err_flag.as<uint32_t>(), sl.st);
+        if (r != GG_OK) return r;
+        if (prev_scan) GG_CUDA(cudaStreamWaitEvent(sl.st, prev_scan, 0));
+        uint64_t* d_base = idx->d_base.as<uint64_t>();
+        GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(sl.cnt.as<uint32_t>(), sl.off.as<uint64_t>(), m, sl.scan.p,
+                                                           d_base + k, nullptr, sl.st)));
+        idx->bstats.kernel_launches++;
+        // next base = last offset of this chunk (off[m] = base + total)
+        GG_CUDA(cudaMemcpyAsync(d_base + k + 1, sl.off.as<uint64_t>() + m, 8, cudaMemcpyDeviceToDevice, sl.st));
+        GG_CUDA(cudaEventRecord(sl.ev_scan, sl.st));
+        prev_scan = sl.ev_scan;
+        GG_CUDA(cudaMemcpyAsync(sl.h_next_base, sl.off.as<uint64_t>() + m, 8, cudaMemcpyDeviceToHost, sl.st));
+        GG_CUDA(cudaEventRecord(sl.ev_total, sl.st));
+        const size_t n_off = (k + 1 == n_chunks) ? m + 1 : m;
+        GG_CUDA(cudaMemcpyAsync(offsets + q0, sl.off.p, n_off * 8, cudaMemcpyDeviceToHost, sl.st));
+        sl.busy = true;
+        return GG_OK;
+    };
+    // stage B: learn the chunk's hit total, emit, D2H the hits
+    auto stage_b = [&](size_t k) -> gg_status {
+        Slot& sl = idx->slots[k % kSlots];
+        const size_t q0 = k * chunk, m = std::min(chunk, nq - q0);
+        GG_CUDA(cudaEventSynchronize(sl.ev_total));
+        base[k + 1] = *sl.h_next_base;
+        const uint64_t total = base[k + 1] - base[k];
+        if (total) {
+            GG_CUDA(sl.hits.ensure(total * 4));
+            if (base[k + 1] > idx->pinned_cap) {
+                // grow with an estimate of the final size; earlier chunks' copies must have landed first
+                for (int i = 0; i < kSlots; ++i)
+                    if (i != static_cast<int>(k % kSlots) && idx->slots[i].busy) GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
+                GG_CUDA(cudaStreamSynchronize(sl.st));
+                double per_q = static_cast<double>(base[k + 1]) / static_cast<double>(q0 + m);
+                size_t est = static_cast<size_t>(per_q * 1.15 * static_cast<double>(nq)) + 4096;
+                gg_status r = ensure_pinned_hits(idx, std::max<size_t>(est, base[k + 1]), base[k]);
+                if (r != GG_OK) return r;
+            }
+            gg_status r = dispatch_emit(idx, sl.qc.as<uint32_t>(), sl.qs.p, sizeof(Q), m, sl.hi.as<uint32_t>(),
+                                        sl.off.as<uint64_t>(), sl.hits.as<uint32_t>(), base[k], sl.st);
+            if (r != GG_OK) return r;
+            GG_CUDA(cudaMemcpyAsync(idx->pinned_hits + base[k], sl.hits.p, total * 4, cudaMemcpyDeviceToHost, sl.st));
+        }
+        GG_CUDA(cudaEventRecord(sl.ev_done, sl.st));
+        return GG_OK;
+    };
+
+    // software pipeline: A(0) A(1) B(0) A(2) B(1) ...
+    const size_t lead = std::min<size_t>(kSlots - 1, n_chunks);
+    for (size_t k = 0; k < lead; ++k) {
+        s = stage_a(k);
+        if (s != GG_OK) return s;
+    }
+    for (size_t k = 0; k < n_chunks; ++k) {
+        if (k + lead < n_chunks) {
+            // the slot of chunk k+lead was last used by chunk k+lead-kSlots = k-1: done by now or waited in stage_a
+            s = stage_a(k + lead);
+            if (s != GG_OK) return s;
+        }
+        s = stage_b(k);
+        if (s != GG_OK) return s;
+    }
+    for (int i = 0; i < kSlots; ++i) {
+        GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
+        idx->slots[i].busy = false;
+    }
+    s = check_query_error(idx, st0);
+    if (s != GG_OK) return s;
+    if (!idx->pinned_hits) {
+        s = ensure_pinned_hits(idx, 1, 0);
+        if (s != GG_OK) return s;
+    }
+    *hits = idx->pinned_hits;
+    *n_hits = base[n_chunks];
+    idx->bstats.n_hits = base[n_chunks];
+    return GG_OK;
+}
+
+}  // namespace
+
+// ============================================================================================== C ABI
+
+extern "C" {
+
+int gg_version(void) { return GG_B200_VERSION; }
+
+int gg_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+gg_status gg_index_create(gg_index** out, int device) {
+    if (!out) return GG_ERR_INVALID_ARG;
+    *out = nullptr;
+    int n = gg_device_count();
+    if (n <= 0 || device < 0 || device >= n) return GG_ERR_CUDA;
+    gg_index* idx = new (std::nothrow) gg_index();
+    if (!idx) return GG_ERR_OOM;
+    idx->device = device;
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete idx;
+        cudaGetLastError();
+        return GG_ERR_CUDA;
+    }
+    idx->sm_count = prop.multiProcessorCount;
+    for (auto& e : idx->ev) cudaEventCreate(&e);
+    *out = idx;
+    return GG_OK;
+}
+
+void gg_index_destroy(gg_index* idx) {
+    if (!idx) return;
+    cudaSetDevice(idx->device);
+    cudaDeviceSynchronize();
+    for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
+                         &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base})
+        b->release();
+    for (auto& s : idx->slots) {
+        for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan}) b->release();
+        if (s.st) cudaStreamDestroy(s.st);
+        if (s.ev_scan) cudaEventDestroy(s.ev_scan);
+        if (s.ev_total) cudaEventDestroy(s.ev_total);
+        if (s.ev_done) cudaEventDestroy(s.ev_done);
+        if (s.h_next_base) cudaFreeHost(s.h_next_base);
+    }
+    if (idx->pinned_hits) cudaFreeHost(idx->pinned_hits);
+    if (idx->h_err) cudaFreeHost(idx->h_err);
+    for (auto& e : idx->ev)
+        if (e) cudaEventDestroy(e);
+    if (idx->stream) cudaStreamDestroy(idx->stream);
+    delete idx;
+}
+
+const char* gg_last_error(const gg_index* idx) { return idx ? idx->err.c_str() : "null handle"; }
+
+gg_status gg_index_build(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
+                         const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom, uint32_t* rank_to_input) {
+    return build_impl(idx, chrom, start, end, tie_key, tie_mode, n, n_chrom, rank_to_input, true);
+}
+
+gg_status gg_index_upload_sorted(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
+                                 size_t n, uint32_t n_chrom) {
+    return build_impl(idx, chrom, start, end, nullptr, GG_TIE_INPUT_ORDER, n, n_chrom, nullptr, false);
+}
+
+gg_status gg_index_get_stats(const gg_index* idx, gg_index_stats* out) {
+    if (!idx || !out) return GG_ERR_INVALID_ARG;
+    if (!idx->built) return GG_ERR_NOT_BUILT;
+    *out = idx->istats;
+    return GG_OK;
+}
+
+gg_status gg_index_chrom_counts(const gg_index* idx, uint64_t* counts) {
+    if (!idx || !counts) return GG_ERR_INVALID_ARG;
+    if (!idx->built) return GG_ERR_NOT_BUILT;
+    for (uint32_t c = 0; c < idx->n_chrom; ++c) counts[c] = idx->h_cnt[c];
+    return GG_OK;
+}
+
+gg_status gg_intersect_batch(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                             size_t nq, uint64_t* offsets, const uint32_t** hits, uint64_t* n_hits) {
+    return intersect_batch_host<uint64_t>(idx, q_chrom, q_start, q_end, nq, offsets, hits, n_hits);
+}
+
+gg_status gg_intersect_batch_u32(gg_index* idx, const uint32_t* q_chrom, const uint32_t* q_start,
+                                 const uint32_t* q_end, size_t nq, uint64_t* offsets, const uint32_t** hits,
+                                 uint64_t* n_hits) {
+    return intersect_batch_host<uint32_t>(idx, q_chrom, q_start, q_end, nq, offsets, hits, n_hits);
+}
+
+gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                    int coord_bytes, size_t nq, uint64_t* d_offsets, uint64_t* total_hits,
+                                    void* stream) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!d_offsets || (nq && (!d_chrom || !d_start || !d_end))) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
+    if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    gg_status s = ensure_query_scratch(idx, nq);
+    if (s != GG_OK) return s;
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+    idx->bstats.n_chunks = 1;
+    idx->ev_count_valid = idx->ev_emit_valid = false;
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[0], st));
+    s = dispatch_count(idx, d_chrom, d_start, d_end, coord_bytes, nq, idx->q_cnt.as<uint32_t>(), idx->q_hi.as<uint32_t>(),
+                       idx->err_flag.as<uint32_t>(), st);
+    if (s != GG_OK) return s;
+    if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[1], st));
+    GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(idx->q_cnt.as<uint32_t>(), d_offsets, nq, idx->scan_scratch.p, nullptr,
+                                                       nullptr, st)));
+    idx->bstats.kernel_launches++;
+    if (idx->timing) {
+        GG_CUDA(cudaEventRecord(idx->ev[2], st));
+        idx->ev_count_valid = true;
+    }
+    idx->counted_nq = nq;
+    if (total_hits) {
+        GG_CUDA(cudaMemcpyAsync(total_hits, d_offsets + nq, 8, cudaMemcpyDeviceToHost, st));
+        s = check_query_error(idx, st);  // synchronises the stream
+        if (s != GG_OK) return s;
+        idx->bstats.n_hits = *total_hits;
+    }
+    return GG_OK;
+}
+
+gg_status gg_intersect_emit_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                   int coord_bytes, size_t nq, const uint64_t* d_offsets, uint32_t* d_hits,
+                                   void* stream) {
+    (void)d_end;
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (nq != idx->counted_nq) return fail(idx, GG_ERR_NOT_BUILT, "emit must follow count on the same batch");
+    if (!d_offsets || (nq && (!d_chrom || !d_start))) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
+    if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[3], st));
+    gg_status s = dispatch_emit(idx, d_chrom, d_start, coord_bytes, nq, idx->q_hi.as<uint32_t>(), d_offsets, d_hits, 0, st);
+    if (s != GG_OK) return s;
+    if (idx->timing) {
+        GG_CUDA(cudaEventRecord(idx->ev[4], st));
+        idx->ev_emit_valid = true;
+    }
+    return GG_OK;
+}
+
+gg_status gg_intersect_count(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                             size_t nq, uint64_t* offsets) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    idx->h2_valid = false;
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!offsets || (nq && (!q_chrom || !q_start || !q_end))) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    const size_t m = nq ? nq : 1;
+    GG_CUDA(idx->h2_qc.ensure(m * 4));
+    GG_CUDA(idx->h2_qs.ensure(m * 8));
+    GG_CUDA(idx->h2_qe.ensure(m * 8));
+    GG_CUDA(idx->h2_off.ensure((m + 1) * 8));
+    if (nq) {
+        GG_CUDA(cudaMemcpyAsync(idx->h2_qc.p, q_chrom, nq * 4, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->h2_qs.p, q_start, nq * 8, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->h2_qe.p, q_end, nq * 8, cudaMemcpyHostToDevice, st));
+    }
+    uint64_t total = 0;
+    gg_status s = gg_intersect_count_device(idx, idx->h2_qc.as<uint32_t>(), idx->h2_qs.p, idx->h2_qe.p, 8, nq,
+                                            idx->h2_off.as<uint64_t>(), &total, st);
+    if (s != GG_OK) return s;
+    GG_CUDA(cudaMemcpyAsync(offsets, idx->h2_off.p, (nq + 1) * 8, cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaStreamSynchronize(st));
+    idx->h2_nq = nq;
+    idx->h2_total = total;
+    idx->h2_valid = true;
+    return GG_OK;
+}
+
+gg_status gg_intersect_emit(gg_index* idx, uint32_t* hits, uint64_t capacity) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built || !idx->h2_valid) return fail(idx, GG_ERR_NOT_BUILT, "gg_intersect_emit must follow gg_intersect_count");
+    if (capacity < idx->h2_total) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]");
+    if (idx->h2_total == 0) return GG_OK;
+    if (!hits) return fail(idx, GG_ERR_INVALID_ARG, "null hit buffer");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    GG_CUDA(idx->h2_hits.ensure(idx->h2_total * 4));
+    gg_status s = gg_intersect_emit_device(idx, idx->h2_qc.as<uint32_t>(), idx->h2_qs.p, idx->h2_qe.p, 8, idx->h2_nq,
+                                           idx->h2_off.as<uint64_t>(), idx->h2_hits.as<uint32_t>(), st);
+    if (s != GG_OK) return s;
+    GG_CUDA(cudaMemcpyAsync(hits, idx->h2_hits.p, idx->h2_total * 4, cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaStreamSynchronize(st));
+    return GG_OK;
+}
+
+gg_status gg_last_batch_stats(const gg_index* cidx, gg_batch_stats* out) {
+    if (!cidx || !out) return GG_ERR_INVALID_ARG;
+    gg_index* idx = const_cast<gg_index*>(cidx);
+    if (idx->timing && idx->ev_count_valid) {
+        float a = 0, b = 0;
+        if (cudaEventSynchronize(idx->ev[2]) == cudaSuccess) {
+            cudaEventElapsedTime(&a, idx->ev[0], idx->ev[1]);
+            cudaEventElapsedTime(&b, idx->ev[1], idx->ev[2]);
+            idx->bstats.count_ms = a;
+            idx->bstats.scan_ms = b;
+        }
+    }
+    if (idx->timing && idx->ev_emit_valid) {
+        float c = 0;
+        if (cudaEventSynchronize(idx->ev[4]) == cudaSuccess) {
+            cudaEventElapsedTime(&c, idx->ev[3], idx->ev[4]);
+            idx->bstats.emit_ms = c;
+        }
+    }
+    idx->bstats.total_ms = idx->bstats.count_ms + idx->bstats.scan_ms + idx->bstats.emit_ms;
+    *out = idx->bstats;
+    return GG_OK;
+}
+
+gg_status gg_host_alloc(void** out, size_t bytes) {
+    if (!out) return GG_ERR_INVALID_ARG;
+    *out = nullptr;
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 16, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return e == cudaErrorMemoryAllocation ? GG_ERR_OOM : GG_ERR_CUDA;
+    }
+    return GG_OK;
+}
+
+void gg_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
+    if (!idx || !key) return GG_ERR_INVALID_ARG;
+    std::string k(key);
+    if (k == "chunk_queries" && value >= 1) idx->chunk_queries = value;
+    else if (k == "stage_bytes" && value >= 0 && value <= 200 * 1024) {
+        idx->stage_bytes = value;
+        if (idx->built) {  // re-plan staging for the existing snapshot (geometry itself is unchanged)
+            gg_status s = plan_levels(idx);
+            if (s != GG_OK) return s;
+        }
+    } else if (k == "count_threads" && (value == 128 || value == 256 || value == 512 || value == 1024)) idx->count_threads = value;
+    else if (k == "count_ctas_per_sm" && value >= 0 && value <= 32) idx->count_ctas_per_sm = value;
+    else if (k == "emit_ctas_per_sm" && value >= 0 && value <= 32) idx->emit_ctas_per_sm = value;
+    else if (k == "timing") idx->timing = value != 0;
+    else return fail(idx, GG_ERR_INVALID_ARG, "unknown option or value out of range");
+    return GG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,160 @@
+/*
+ * gg_b200.h — C ABI of the B200-native batched interval-overlap engine (libgg_b200.so).
+ *
+ * This is the drop-in boundary for genogrove's grove<interval, T>::intersect hot path.  Plain C
+ * types, caller-owned buffers unless stated, `gg_status` return codes, no exceptions and no torch /
+ * C++ types across the boundary.  One opaque handle per grove snapshot; calls on one handle must be
+ * serialised by the caller (the reference is single-threaded with no internal locking,
+ * CHANGELOG.md:46).  There is NO CPU fallback: every entry point that computes runs hand-written
+ * sm_100a kernels and fails with GG_ERR_CUDA when no device is usable.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *
+ *   gg_index_build            <- grove::insert_data(idx, vec, bulk): std::sort + build_tree_bottom_up
+ *                                include/genogrove/structure/grove/grove_insert.ipp:160-172, 545-669
+ *                                (one call covers every chromosome; the reference is called per index)
+ *   gg_index_upload_sorted    <- the leaf chain left by insert / insert_sorted / remove_key / compact
+ *                                grove_insert.ipp:182-274, 501-531; grove_remove.ipp:24-98
+ *   gg_intersect_*            <- grove::intersect(query, index) -> detail::search_overlaps
+ *                                include/genogrove/structure/grove/grove_query.ipp:33-43
+ *                                include/genogrove/structure/grove/query_engine.hpp:76-134
+ *                                with query_result::add_key (data_type/query_result.hpp:108-113)
+ *                                replaced by CSR output: offsets[Q+1] (u64) + hits[H] (u32 ranks)
+ *   q_chrom (u32 id)          <- grove::get_root(index) hash lookup, grove.hpp:234-236; an id of
+ *                                GG_NO_CHROM (or >= n_chrom) yields zero hits, like an unknown index
+ *                                name does in grove_query.ipp:37-39
+ *   GG_ERR_INVALID_INTERVAL   <- interval ctor's std::invalid_argument on start > end, interval.hpp:70-74
+ *
+ * Semantics (bit-exact with the reference): for query q on chromosome c the hits are exactly
+ * { r : start_c[r] <= q.end && end_c[r] >= q.start } (closed intervals, adjacency overlaps,
+ * interval.hpp:140-142), reported as per-chromosome LEAF-CHAIN RANKS r in ascending order — the order
+ * search_overlaps appends keys in.  The host keeps rank -> key* per chromosome.
+ */
+#ifndef GG_B200_H
+#define GG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GG_B200_VERSION 100 /* 0.1.0 */
+#define GG_NO_CHROM 0xFFFFFFFFu
+
+typedef struct gg_index gg_index;
+
+typedef enum gg_status {
+    GG_OK = 0,
+    GG_ERR_INVALID_ARG = 1,      /* null pointer, bad size, chrom id >= n_chrom in the index input */
+    GG_ERR_CUDA = 2,             /* a CUDA call or kernel failed; see gg_last_error */
+    GG_ERR_OOM = 3,              /* device or pinned-host allocation failed */
+    GG_ERR_INVALID_INTERVAL = 4, /* start > end in an index interval or a query */
+    GG_ERR_NOT_BUILT = 5,        /* intersect before build/upload, or emit before count */
+    GG_ERR_UNSORTED = 6,         /* gg_index_upload_sorted input not ordered by (chrom, start) */
+    GG_ERR_CAPACITY = 7          /* caller's hit buffer too small / more than 2^32-1 intervals */
+} gg_status;
+
+/* Order among intervals with equal (chrom, start, end) — the only freedom in hit order (the leaf chain):
+ *   GG_TIE_INPUT_ORDER    stable: equal keys keep input order  == insert_data(idx, vec, sorted, bulk)
+ *   GG_TIE_REVERSE_INPUT  equal keys in reverse input order    == one insert_data(idx, key, data) per
+ *                         record (lower_bound insertion, node.hpp:247-254)
+ *   GG_TIE_EXPLICIT       ascending caller-supplied tie_key[i] (then input order) */
+typedef enum gg_tie_mode { GG_TIE_INPUT_ORDER = 0, GG_TIE_REVERSE_INPUT = 1, GG_TIE_EXPLICIT = 2 } gg_tie_mode;
+
+typedef struct gg_index_stats {
+    uint64_t n_intervals;
+    uint32_t n_chrom;
+    uint32_t coord_bytes;   /* 4: u32 device layout (all coordinates < 2^32), 8: u64 layout */
+    uint32_t n_levels;      /* levels of the implicit B+ tree, leaf level included */
+    uint32_t fanout;        /* keys per node (32) */
+    uint32_t staged_levels; /* upper levels copied into shared memory by TMA in the count kernel */
+    uint32_t reserved;
+    uint64_t device_bytes;  /* HBM held by the index */
+    double sort_ms;         /* device time of the radix sorts of the last build */
+    double levels_ms;       /* device time of padding + level construction of the last build */
+    double total_ms;        /* device time of the last build/upload incl. host<->device copies */
+} gg_index_stats;
+
+typedef struct gg_batch_stats {
+    uint64_t n_queries;
+    uint64_t n_hits;
+    uint32_t n_chunks;       /* pipeline chunks used by the host-buffer entry points */
+    uint32_t kernel_launches;/* kernels launched by the last intersect call */
+    double count_ms;         /* device time: count kernel (last call, summed over chunks) */
+    double scan_ms;          /* device time: exclusive scan */
+    double emit_ms;          /* device time: emit kernel */
+    double total_ms;         /* device time first launch/copy -> last, host buffers included */
+} gg_batch_stats;
+
+int gg_version(void);
+/* number of visible CUDA devices (0 when none or no driver) */
+int gg_device_count(void);
+
+/* ---- handle ------------------------------------------------------------------------------------ */
+gg_status gg_index_create(gg_index** out, int device);
+void gg_index_destroy(gg_index* idx);
+/* message of the last failure on this handle ("" if none); valid until the next call on the handle */
+const char* gg_last_error(const gg_index* idx);
+
+/* ---- index build (host buffers in) -------------------------------------------------------------- */
+/* Sort (chrom, start, end[, tie]) with the hand-written LSD radix sort, build the flattened B+ tree
+ * (pivot levels + per-node max-end augmentation) on the device.  rank_to_input (nullable, n entries)
+ * receives, chromosome by chromosome in id order, the input index of each chain rank:
+ *   rank_to_input[chrom_begin[c] + r] = i  where chrom_begin = exclusive prefix of per-chrom counts. */
+gg_status gg_index_build(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
+                         const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom,
+                         uint32_t* rank_to_input);
+/* Same, for a chain the host already ordered: input must be grouped by ascending chrom id and, inside
+ * a chromosome, in leaf-chain order (non-decreasing start).  No sort of (start,end) is performed. */
+gg_status gg_index_upload_sorted(gg_index* idx, const uint32_t* chrom, const uint64_t* start,
+                                 const uint64_t* end, size_t n, uint32_t n_chrom);
+gg_status gg_index_get_stats(const gg_index* idx, gg_index_stats* out);
+/* counts[c] = number of intervals of chromosome c (n_chrom entries) */
+gg_status gg_index_chrom_counts(const gg_index* idx, uint64_t* counts);
+
+/* ---- batched intersect, HOST buffers (the reference-facing call) -------------------------------- */
+/* One call = count -> exclusive scan -> emit for nq queries, chunked and pipelined over CUDA streams
+ * (H2D of chunk k+1 and D2H of chunk k-1 overlap the kernels of chunk k).  offsets: caller buffer of
+ * nq+1 u64.  *hits: library-owned pinned host buffer of *n_hits u32 ranks, valid until the next
+ * intersect call on this handle or gg_index_destroy.  Buffers from gg_host_alloc are pinned. */
+gg_status gg_intersect_batch(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start,
+                             const uint64_t* q_end, size_t nq, uint64_t* offsets, const uint32_t** hits,
+                             uint64_t* n_hits);
+/* u32-coordinate variant (BED/SAM-sized coordinates; needs a coord_bytes == 4 index) */
+gg_status gg_intersect_batch_u32(gg_index* idx, const uint32_t* q_chrom, const uint32_t* q_start,
+                                 const uint32_t* q_end, size_t nq, uint64_t* offsets, const uint32_t** hits,
+                                 uint64_t* n_hits);
+/* Two-phase variant with a caller-owned hit buffer: count fills offsets[nq+1] and keeps the batch on the
+ * device; emit writes offsets[nq] ranks into hits (capacity in elements). */
+gg_status gg_intersect_count(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start,
+                             const uint64_t* q_end, size_t nq, uint64_t* offsets);
+gg_status gg_intersect_emit(gg_index* idx, uint32_t* hits, uint64_t capacity);
+
+/* ---- batched intersect, DEVICE buffers (queries and results stay in HBM) ------------------------ */
+/* d_start/d_end element width = coord_bytes (4 or 8; 4 needs a coord_bytes == 4 index).  d_offsets: nq+1
+ * u64.  stream: a cudaStream_t (NULL = default stream); kernels are enqueued, not synchronised, unless
+ * total_hits (host pointer, nullable) is given, in which case the call waits and stores offsets[nq]. */
+gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
+                                    const void* d_end, int coord_bytes, size_t nq, uint64_t* d_offsets,
+                                    uint64_t* total_hits, void* stream);
+/* must follow gg_intersect_count_device with the same queries and offsets */
+gg_status gg_intersect_emit_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
+                                   const void* d_end, int coord_bytes, size_t nq, const uint64_t* d_offsets,
+                                   uint32_t* d_hits, void* stream);
+gg_status gg_last_batch_stats(const gg_index* idx, gg_batch_stats* out);
+
+/* ---- pinned host memory helpers ------------------------------------------------------------------ */
+gg_status gg_host_alloc(void** out, size_t bytes);
+void gg_host_free(void* p);
+
+/* ---- tuning knobs (defaults are chosen for B200; used by tests/bench to pin behaviour) ----------- */
+/* key: "chunk_queries" (host pipeline chunk, default 8388608), "stage_bytes" (shared-memory budget for
+ * TMA-staged upper levels, default 65536), "count_ctas_per_sm", "emit_ctas_per_sm". */
+gg_status gg_set_option(gg_index* idx, const char* key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GG_B200_H */

@@ -1,0 +1,198 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle, bit-exact (offsets and the
+ordered rank list per query).  Marked gpu: run on the B200 box."""
+import numpy as np
+import pytest
+
+from helpers import expected_chain, oracle_csr, random_index, random_queries
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gg():
+    import genogrove_b200 as g
+    return g
+
+
+def _check(idx, chrom, start, end, n_chrom, q, perm=None, two_phase=False):
+    qc, qs, qe = q
+    exp_off, exp_hits = oracle_csr(chrom, start, end, n_chrom, qc, qs, qe, perm)
+    off, hits = (idx.intersect_two_phase if two_phase else idx.intersect_batch)(qc, qs, qe)
+    assert np.array_equal(off, exp_off)
+    assert np.array_equal(hits, exp_hits)
+    return int(exp_off[-1])
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 32, 33, 63, 64, 65, 1000, 1023, 1024, 1025, 4096, 33000, 100_003])
+def test_build_sizes_single_chrom(gg, oracle, n):
+    rng = np.random.default_rng(n + 1)
+    chrom, start, end = random_index(rng, n, 1, span=50 * max(n, 10))
+    idx = gg.DeviceIndex(0)
+    perm = idx.build(chrom, start, end, 1)
+    assert np.array_equal(perm, expected_chain(chrom, start, end))
+    _check(idx, chrom, start, end, 1, random_queries(rng, 5000, 1, span=50 * max(n, 10)))
+    st = idx.stats()
+    assert st.n_intervals == n and st.coord_bytes == 4 and st.fanout == 32
+
+
+@pytest.mark.parametrize("dup,nested", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("n_chrom", [1, 3, 24, 300])
+def test_multi_chrom_shapes(gg, oracle, n_chrom, dup, nested):
+    rng = np.random.default_rng(1000 + n_chrom + 2 * dup + 4 * nested)
+    n = 60_000
+    chrom, start, end = random_index(rng, n, n_chrom, span=200_000, dup=dup, nested=nested)
+    if n_chrom >= 3:
+        chrom[chrom == 1] = 0  # an empty chromosome in the middle
+    idx = gg.DeviceIndex(0)
+    perm = idx.build(chrom, start, end, n_chrom)
+    assert np.array_equal(perm, expected_chain(chrom, start, end))
+    q = random_queries(rng, 40_000, n_chrom, span=200_000, extra_chrom=2)
+    q[0][::97] = gg.NO_CHROM  # unknown index -> empty result
+    hits = _check(idx, chrom, start, end, n_chrom, q)
+    assert hits > 0
+    counts = idx.chrom_counts()
+    assert np.array_equal(counts, np.bincount(chrom, minlength=n_chrom))
+
+
+@pytest.mark.parametrize("tie_mode", [0, 1, 2])
+def test_tie_modes(gg, oracle, tie_mode):
+    rng = np.random.default_rng(5 + tie_mode)
+    n = 20_000
+    chrom, start, end = random_index(rng, n, 4, span=20_000, dup=True)
+    tie = rng.integers(0, 50, n).astype(np.uint64) if tie_mode == 2 else None
+    idx = gg.DeviceIndex(0)
+    perm = idx.build(chrom, start, end, 4, tie_mode=tie_mode, tie_key=tie)
+    exp = expected_chain(chrom, start, end, tie_mode, tie)
+    assert np.array_equal(perm, exp)
+    _check(idx, chrom, start, end, 4, random_queries(rng, 10_000, 4, span=20_000), perm=exp)
+
+
+def test_wide_coordinates_u64_layout(gg, oracle):
+    rng = np.random.default_rng(11)
+    chrom, start, end = random_index(rng, 30_000, 5, wide=True, nested=True)
+    # coordinates up to SIZE_MAX (tests/data_type/interval_test.cpp:428-451)
+    start[:3] = np.array([2**64 - 10, 2**64 - 1, 0], dtype=np.uint64)
+    end[:3] = np.array([2**64 - 1, 2**64 - 1, 2**64 - 1], dtype=np.uint64)
+    idx = gg.DeviceIndex(0)
+    perm = idx.build(chrom, start, end, 5)
+    assert idx.stats().coord_bytes == 8
+    assert np.array_equal(perm, expected_chain(chrom, start, end))
+    qc, qs, qe = random_queries(rng, 20_000, 5, wide=True)
+    qs[:4] = np.array([2**64 - 1, 0, 2**64 - 5, 5], dtype=np.uint64)
+    qe[:4] = np.array([2**64 - 1, 2**64 - 1, 2**64 - 2, 5], dtype=np.uint64)
+    _check(idx, chrom, start, end, 5, (qc, qs, qe))
+
+
+def test_u32_boundary_values(gg, oracle):
+    # index stays in the u32 layout with coordinates right at 2^32-1; queries beyond it (u64) must clamp
+    chrom = np.zeros(6, np.uint32)
+    start = np.array([0, 0, 10, 2**32 - 2, 2**32 - 1, 2**32 - 1], np.uint64)
+    end = np.array([0, 2**32 - 1, 20, 2**32 - 1, 2**32 - 1, 2**32 - 1], np.uint64)
+    idx = gg.DeviceIndex(0)
+    idx.build(chrom, start, end, 1)
+    assert idx.stats().coord_bytes == 4
+    qs = np.array([0, 2**32 - 1, 2**32, 2**32 - 1, 0, 21, 2**40], np.uint64)
+    qe = np.array([0, 2**32 - 1, 2**33, 2**64 - 1, 2**64 - 1, 2**32 - 3, 2**41], np.uint64)
+    _check(idx, chrom, start, end, 1, (np.zeros(7, np.uint32), qs, qe))
+
+
+def test_upload_sorted_chain_and_errors(gg, oracle):
+    rng = np.random.default_rng(21)
+    chrom, start, end = random_index(rng, 10_000, 3, dup=True)
+    # a host-defined chain: regular-insert order (reverse insertion among equal keys)
+    perm = expected_chain(chrom, start, end, 1)
+    idx = gg.DeviceIndex(0)
+    idx.upload_sorted(chrom[perm], start[perm], end[perm], 3)
+    q = random_queries(rng, 5000, 3)
+    _check(idx, chrom, start, end, 3, q, perm=perm)
+    _check(idx, chrom, start, end, 3, q, perm=perm, two_phase=True)
+    with pytest.raises(gg.GGError) as ei:
+        idx.upload_sorted(chrom, start, end, 3)  # not ordered
+    assert ei.value.status == 6
+    with pytest.raises(gg.GGError) as ei:
+        idx.build(np.array([0], np.uint32), np.array([5], np.uint64), np.array([4], np.uint64), 1)
+    assert ei.value.status == 4  # start > end, like interval's std::invalid_argument
+    with pytest.raises(gg.GGError) as ei:
+        idx.build(np.array([7], np.uint32), np.array([1], np.uint64), np.array([4], np.uint64), 3)
+    assert ei.value.status == 1
+    with pytest.raises(gg.GGError) as ei:
+        idx.intersect_batch(np.zeros(1, np.uint32), np.zeros(1, np.uint64), np.zeros(1, np.uint64))
+    assert ei.value.status == 5  # failed builds leave the handle without a snapshot
+
+
+def test_invalid_query_is_rejected(gg, oracle):
+    idx = gg.DeviceIndex(0)
+    idx.build(np.zeros(3, np.uint32), np.array([1, 5, 9], np.uint64), np.array([3, 7, 11], np.uint64), 1)
+    with pytest.raises(gg.GGError) as ei:
+        idx.intersect_batch(np.zeros(2, np.uint32), np.array([1, 8], np.uint64), np.array([2, 6], np.uint64))
+    assert ei.value.status == 4
+    off, hits = idx.intersect_batch(np.zeros(0, np.uint32), np.zeros(0, np.uint64), np.zeros(0, np.uint64))
+    assert off.tolist() == [0] and len(hits) == 0
+
+
+@pytest.mark.parametrize("opt", [("chunk_queries", 4096), ("chunk_queries", 20_000), ("stage_bytes", 0),
+                                 ("stage_bytes", 16384), ("stage_bytes", 196608), ("count_threads", 128),
+                                 ("count_threads", 1024)])
+def test_options_do_not_change_results(gg, oracle, opt):
+    rng = np.random.default_rng(31)
+    chrom, start, end = random_index(rng, 150_000, 24, span=400_000, nested=True)
+    idx = gg.DeviceIndex(0)
+    idx.set_option(*opt)
+    idx.build(chrom, start, end, 24)
+    q = random_queries(rng, 100_001, 24, span=400_000)
+    _check(idx, chrom, start, end, 24, q)
+    if opt[0] == "chunk_queries":
+        assert idx.batch_stats().n_chunks == -(-100_001 // (opt[1] // 4096 * 4096))
+    # u32 query entry point on the same handle
+    exp_off, exp_hits = oracle_csr(chrom, start, end, 24, *q)
+    off, hits = idx.intersect_batch(q[0], q[1].astype(np.uint32), q[2].astype(np.uint32))
+    assert np.array_equal(off, exp_off) and np.array_equal(hits, exp_hits)
+
+
+def test_device_buffer_api(gg, oracle):
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(41)
+    chrom, start, end = random_index(rng, 80_000, 24, span=300_000, nested=True)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("timing", 1)
+    idx.build(chrom, start, end, 24)
+    qc, qs, qe = random_queries(rng, 200_000, 24, span=300_000)
+    exp_off, exp_hits = oracle_csr(chrom, start, end, 24, qc, qs, qe)
+    dev = torch.device("cuda:0")
+    for dt, nb in ((np.uint32, 4), (np.uint64, 8)):
+        d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
+        d_s = torch.from_numpy(qs.astype(dt).view(np.int32 if nb == 4 else np.int64)).to(dev)
+        d_e = torch.from_numpy(qe.astype(dt).view(np.int32 if nb == 4 else np.int64)).to(dev)
+        d_off = torch.empty(len(qc) + 1, dtype=torch.int64, device=dev)
+        stream = torch.cuda.current_stream().cuda_stream
+        total = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
+                                 stream, sync_total=True)
+        assert total == int(exp_off[-1])
+        d_hits = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+        idx.emit_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
+                        d_hits.data_ptr(), stream)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
+        assert np.array_equal(d_hits.cpu().numpy().view(np.uint32)[:total], exp_hits)
+        bs = idx.batch_stats()
+        assert bs.count_ms > 0 and bs.emit_ms > 0 and bs.kernel_launches == 3
+
+
+def test_long_nested_intervals_use_max_end_pruning(gg, oracle):
+    # one_spanning / nested shapes of tests/structure/routing_test.cpp:52-109 at scale: a few huge intervals
+    # far to the left of dense short ones
+    rng = np.random.default_rng(51)
+    n = 300_000
+    start = np.sort(rng.integers(0, 30_000_000, n)).astype(np.uint64)
+    end = start + rng.integers(1, 200, n).astype(np.uint64)
+    end[::50_000] = start[::50_000] + np.uint64(25_000_000)
+    chrom = np.zeros(n, np.uint32)
+    idx = gg.DeviceIndex(0)
+    idx.build(chrom, start, end, 1)
+    qs = rng.integers(0, 30_000_000, 50_000).astype(np.uint64)
+    _check(idx, chrom, start, end, 1, (np.zeros(50_000, np.uint32), qs, qs + np.uint64(100)))
+
+
+def test_smoke_entry(gg, oracle):
+    import __graft_entry__ as ge
+    ge.smoke()
