@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""bench.py — overlap queries/s of the batched grove intersect path on N B200s (one process per GPU).
+
+Workload (BASELINE.json configs[3], the configuration the metric is quoted on): a 10M-interval hg38-shaped
+grove (24 chromosomes) and, PER GPU, 100M read-shaped (150 bp) queries, coordinate-sorted per chromosome
+(BAM-like); index replicated on every GPU, query batch sharded (weak scaling: per-GPU work is fixed).
+A step = one pass of the hot path (count -> exclusive scan -> emit) over the rank's 100M-query batch.
+
+  value : whole-job queries/s with queries and results resident in HBM (device-buffer C ABI).
+  e2e   : the same metric through the host-buffer C ABI call (gg_intersect_batch, u64 coordinates as the
+          reference's interval uses), pinned host buffers, H2D + D2H inside the timed region.
+  --impl reference : the reference's own CPU intersect loop (oracle/_ref = unmodified genogrove) on this
+          box's host cores, all threads, on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "overlap_queries_per_sec"
+UNIT = "queries/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--intervals", type=int, default=10_000_000)
+    ap.add_argument("--queries", type=int, default=100_000_000, help="queries per GPU")
+    ap.add_argument("--shuffled", action="store_true", help="shuffled instead of coordinate-sorted queries")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-sample", type=int, default=4_000_000, help="queries in the CPU baseline sample")
+    ap.add_argument("--cpu-order", type=int, default=32, help="B+ tree order of the reference grove (3 = library default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args, world):
+    return {
+        "workload": "cfg4: 10M-interval hg38-shaped grove (24 chromosomes) x 100M 150bp read-shaped queries per GPU, "
+                    + ("shuffled" if args.shuffled else "coordinate-sorted per chromosome (BAM-like)"),
+        "intervals": args.intervals,
+        "queries_per_gpu": args.queries,
+        "query_order": "shuffled" if args.shuffled else "sorted",
+        "parallelism": f"index replicated, query batch sharded x{world}",
+        "l2_policy": "inputs+outputs per step (>4 GB) exceed the 126 MB L2; no flush needed",
+    }
+
+
+# ----------------------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.samples = []
+        self.proc = None
+        self.gpu_index = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu_index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.samples:
+            if ts < t0 - 0.05 or ts > t1 + 0.05:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+                for nm, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        if not sm:  # region shorter than the sampling period: fall back to everything captured
+            for ts, line in self.samples:
+                f = [x.strip() for x in line.split(",")]
+                try:
+                    sm.append(float(f[0]))
+                    mx = float(f[1])
+                except Exception:
+                    pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------- reference arm
+def cpu_reference_run(args, w, steps, warmup, threads=None):
+    """Times the unmodified reference (oracle/_ref) on a bounded sample; returns (q/s, info dict)."""
+    import oracle as O
+    if not O.ref_available():
+        return None, {"unavailable": "oracle/_ref/libgg_ref.so not built"}
+    g = O.RefGrove(args.cpu_order)
+    T = threads or g.hardware_threads()
+    t0 = time.time()
+    ids = np.arange(len(w.chrom), dtype=np.uint32)
+    for c in range(w.n_chrom):
+        m = w.chrom == c
+        g.insert_bulk(c, w.start[m], w.end[m], ids[m], presorted=False)
+    build_s = time.time() - t0
+    nq = len(w.q_chrom)
+    S = min(args.cpu_sample, nq)
+    lo = (nq - S) // 2
+    qc, qs, qe = w.q_chrom[lo:lo + S], w.q_start[lo:lo + S], w.q_end[lo:lo + S]
+    secs, hits = [], 0
+    for i in range(warmup + steps):
+        off, _, s = g.intersect_batch(qc, qs, qe, threads=T, want_ids=False)
+        hits = int(off[-1])
+        if i >= warmup:
+            secs.append(s)
+    ms = 1e3 * float(np.mean(secs))
+    info = {"value": S / (ms / 1e3), "unit": UNIT, "cores": T, "kind": "reference",
+            "sample": f"{S} contiguous queries from the middle of the batch x {steps} steps, reference grove order "
+                      f"{args.cpu_order}, bulk build {build_s:.1f}s, {hits / S:.2f} hits/query",
+            "ms_per_step": ms, "hit_pairs_per_sec": hits / (ms / 1e3)}
+    return info["value"], info
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    from genogrove_b200 import synth
+    w = synth.cfg4(args.intervals, min(args.queries, max(args.cpu_sample * 2, 1_000_000)), sorted_queries=not args.shuffled)
+    steps, warmup = max(1, min(args.steps, 5)), max(0, min(args.warmup, 1))
+    v, info = cpu_reference_run(args, w, steps, warmup)
+    if v is None:
+        print(json.dumps({"impl": "reference", "unavailable": info["unavailable"]}))
+        return
+    out = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+           "ms_per_step": info["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "u64", "data": "synthetic", "impl": "reference", "config": workload_config(args, world),
+           "cpu_baseline": {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")},
+           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "hit_pairs_per_sec": info["hit_pairs_per_sec"], "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+# ----------------------------------------------------------------------------------------- B200 arm
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from genogrove_b200 import DeviceIndex, PinnedArray, synth, shard
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- synthetic inputs: same grove on every rank, a different 100M-query shard per rank
+    c, s, e = synth.hg38_intervals(args.intervals, 42)
+    qc, qs, qe = synth.hg38_queries(args.queries, 150, 43 + rank, not args.shuffled)
+    nq = len(qc)
+
+    idx = DeviceIndex(local_rank)
+    idx.build(c, s, e, 24, want_perm=False)
+    ist = idx.stats()
+
+    d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
+    d_s = torch.from_numpy(qs.astype(np.uint32).view(np.int32)).to(dev)
+    d_e = torch.from_numpy(qe.astype(np.uint32).view(np.int32)).to(dev)
+    d_off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    total = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), stream, sync_total=True)
+    d_hits = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+    d_tot = torch.zeros(1, dtype=torch.int64, device=dev)
+    d_all = torch.zeros(world, dtype=torch.int64, device=dev)
+
+    def step(ev=None):
+        # pass 1 + scan; the host needs the hit total to size the output (a real caller allocates here)
+        if ev:
+            ev[0].record()
+        t = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), stream, sync_total=True)
+        assert t <= d_hits.numel()
+        if ev:
+            ev[1].record()
+        idx.emit_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(), stream)
+        if ev:
+            ev[2].record()
+        if world > 1:  # the path's only collective: gather hit totals -> global CSR base
+            d_tot.copy_(d_off[nq:nq + 1])
+            dist.all_gather_into_tensor(d_all, d_tot)
+        return t
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.25)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.time()
+    e0.record()
+    for k in range(args.steps):
+        step(evs[k])
+    e1.record()
+    barrier()
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1)
+    ms_total = e0.elapsed_time(e1)
+    t_ms = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t_ms.item()) / args.steps
+    count_scan_ms = float(np.mean([ev[0].elapsed_time(ev[1]) for ev in evs]))
+    emit_ms = float(np.mean([ev[1].elapsed_time(ev[2]) for ev in evs]))
+
+    # count vs scan split (library CUDA events on the same stream), outside the timed region
+    idx.set_option("timing", 1)
+    step()
+    torch.cuda.synchronize()
+    bs = idx.batch_stats()
+    idx.set_option("timing", 0)
+    scan_share = bs.scan_ms / max(bs.count_ms + bs.scan_ms, 1e-9)
+    count_ms = count_scan_ms * (1 - scan_share)
+    scan_ms = count_scan_ms * scan_share
+
+    totals = torch.tensor([total, nq], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(totals, op=dist.ReduceOp.SUM)
+    job_hits, job_q = int(totals[0].item()), int(totals[1].item())
+    value = job_q / (ms_per_step / 1e3)
+
+    # ---- roofline of the dominant kernel (algorithmic bytes)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    bytes_count = 12 * nq + 8 * nq            # read (chrom,start,end) u32, write count u32 + hi u32
+    bytes_emit = 4 * total + 8 * (nq + 1) + 12 * nq  # write ranks, read offsets, chrom/start/hi
+    bytes_path = 12 * nq + 8 * (nq + 1) + 4 * total  # B_q
+    if emit_ms >= count_ms:
+        dom, dom_ms, dom_bytes = "intersect_emit_kernel", emit_ms, bytes_emit
+    else:
+        dom, dom_ms, dom_bytes = "intersect_count_kernel", count_ms, bytes_count
+    achieved = dom_bytes / (dom_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
+                "algorithmic_bytes_per_launch": dom_bytes,
+                "kernel_ms": {"count": count_ms, "scan": scan_ms, "emit": emit_ms},
+                "path_achieved_gbs": bytes_path / (ms_per_step / 1e3) / 1e9,
+                "path_frac": bytes_path / (ms_per_step / 1e3) / 1e9 / peak}
+
+    # ---- e2e: host-buffer C ABI call (u64 coordinates, pinned buffers), H2D + D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        p_c, p_s, p_e = PinnedArray(nq, np.uint32), PinnedArray(nq, np.uint64), PinnedArray(nq, np.uint64)
+        p_off = PinnedArray(nq + 1, np.uint64)
+        p_c.array[:], p_s.array[:], p_e.array[:] = qc, qs, qe
+        del d_hits
+        torch.cuda.empty_cache()
+
+        def e2e_step():
+            off, hits = idx.intersect_batch(p_c.array, p_s.array, p_e.array, offsets_out=p_off.array, copy_hits=False)
+            return int(off[-1])
+
+        e2e_step()  # warm-up: grows the pinned result buffer and the pipeline slots
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            h = e2e_step()
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / args.e2e_steps
+        assert h == total
+        t_e = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+        e2e = {"value": job_q / float(t_e.item()), "unit": UNIT, "h2d_bytes_per_step": int(nq * 20),
+               "d2h_bytes_per_step": int((nq + 1) * 8 + total * 4), "ms_per_step": float(t_e.item()) * 1e3,
+               "steps": args.e2e_steps, "api": "gg_intersect_batch (u64 coordinates, pinned host buffers)",
+               "timer": "host wall clock around the blocking C ABI call, max over ranks"}
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): the unmodified reference on a bounded sample
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        w = synth.Workload("cfg4", 24, c, s, e, qc, qs, qe)
+        v, info = cpu_reference_run(args, w, steps=2, warmup=1)
+        cpu = {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")} if v else info
+        v1, info1 = cpu_reference_run(args, w, steps=1, warmup=0, threads=1) if v else (None, None)
+        if v1:
+            cpu["single_thread_value"] = v1
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+               "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+               "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+               "config": workload_config(args, world), "hit_pairs_per_sec": job_hits / (ms_per_step / 1e3),
+               "hits_per_query": job_hits / job_q, "gpu_launches": 3 * args.steps, "clocks": clocks,
+               "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+               "index": {"levels": ist.n_levels, "fanout": ist.fanout, "staged_levels": ist.staged_levels,
+                         "coord_bytes": ist.coord_bytes, "device_mb": ist.device_bytes / 1e6,
+                         "build_sort_ms": ist.sort_ms, "build_levels_ms": ist.levels_ms, "build_total_ms": ist.total_ms}}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
