@@ -156,7 +156,7 @@ size_t count_smem_bytes(const gg_index* idx) {
 }
 size_t emit_smem_bytes(const gg_index* idx) {
     size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
-    return tab_elems * 4 + 16;
+    return static_cast<size_t>(kQueryThreads / 32) * kEmitStage * 4 + tab_elems * 4 + 16;
 }
 
 template <typename C, typename Q>

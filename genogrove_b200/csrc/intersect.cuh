@@ -36,6 +36,7 @@ struct IndexView {
 };
 
 constexpr int kQueryThreads = 256;
+constexpr uint32_t GG_NO_CHROM_DEV = 0xFFFFFFFFu;
 
 // number of keys <= x in one sorted 32-key node (0..32): 6 dependent loads, branch-free
 template <typename C>
@@ -85,6 +86,91 @@ __device__ __forceinline__ C clamp_coord(Q v) {
     return static_cast<C>(v);
 }
 
+// ---- warp-cooperative search (coordinate-sorted batches) ----------------------------------------------
+__device__ __forceinline__ uint32_t warp_min(uint32_t v) { return __reduce_min_sync(0xffffffffu, v); }
+__device__ __forceinline__ uint32_t warp_max(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
+__device__ __forceinline__ uint64_t warp_min(uint64_t v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        uint64_t o = __shfl_xor_sync(0xffffffffu, v, d);
+        v = o < v ? o : v;
+    }
+    return v;
+}
+__device__ __forceinline__ uint64_t warp_max(uint64_t v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        uint64_t o = __shfl_xor_sync(0xffffffffu, v, d);
+        v = o > v ? o : v;
+    }
+    return v;
+}
+
+// v holds one sorted 32-key node, one key per lane.  Returns, per lane, #keys <= x (0..32): a binary search
+// whose "loads" are register shuffles.
+template <typename C>
+__device__ __forceinline__ uint32_t shfl_count_le(C v, C x) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        C t = __shfl_sync(0xffffffffu, v, c + step - 1);
+        if (t <= x) c += step;
+    }
+    C t = __shfl_sync(0xffffffffu, v, c);
+    if (t <= x) c += 1;
+    return c;
+}
+
+// Warp-cooperative upper bound for 32 queries on the SAME chromosome (warp-uniform chrom, n_c).  The warp
+// descends the tree twice at once — for min(x) and max(x) over its lanes — one coalesced node load and one
+// ballot per level (the in-node compare is a ballot + popc, not a loop); every lane's answer then lies in
+// leaf nodes [n_lo, n_hi].  When these are the same or adjacent nodes (always, for coordinate-sorted
+// batches) each lane finishes with shuffles on the keys already in registers.  Returns false (warp-uniform)
+// when the bracket spans more nodes: the caller falls back to the per-lane descent.
+template <typename C>
+__device__ __forceinline__ bool warp_upper_bound(const C* __restrict__ g, const C* __restrict__ s,
+                                                 const uint32_t* __restrict__ tab, uint32_t stride, int n_levels,
+                                                 int stage_level, uint32_t chrom, C x, uint32_t n_c, uint32_t& result) {
+    const uint32_t lane = lane_id();
+    const C xmin = warp_min(x), xmax = warp_max(x);
+    uint32_t n_lo = 0, n_hi = 0;
+    C a_lo = 0, a_hi = 0;
+    int l = n_levels - 1;
+    for (; l >= stage_level && l >= 0; --l) {  // staged levels: shared memory
+        const C* base = s + tab[l * stride + chrom];
+        a_lo = base[(n_lo << kFanoutLog2) + lane];
+        a_hi = (n_hi == n_lo) ? a_lo : base[(n_hi << kFanoutLog2) + lane];
+        const uint32_t c_lo = __popc(__ballot_sync(0xffffffffu, a_lo <= xmin));
+        const uint32_t c_hi = __popc(__ballot_sync(0xffffffffu, a_hi <= xmax));
+        if (l > 0) {
+            const uint32_t below = (tab[(l - 1) * stride + chrom + 1] - tab[(l - 1) * stride + chrom]) >> kFanoutLog2;
+            n_lo = min((n_lo << kFanoutLog2) + c_lo, below - 1);
+            n_hi = min((n_hi << kFanoutLog2) + c_hi, below - 1);
+        }
+    }
+    for (; l >= 0; --l) {  // global levels (L1/L2)
+        const C* base = g + tab[l * stride + chrom];
+        a_lo = base[(n_lo << kFanoutLog2) + lane];
+        a_hi = (n_hi == n_lo) ? a_lo : base[(n_hi << kFanoutLog2) + lane];
+        const uint32_t c_lo = __popc(__ballot_sync(0xffffffffu, a_lo <= xmin));
+        const uint32_t c_hi = __popc(__ballot_sync(0xffffffffu, a_hi <= xmax));
+        if (l > 0) {
+            const uint32_t below = (tab[(l - 1) * stride + chrom + 1] - tab[(l - 1) * stride + chrom]) >> kFanoutLog2;
+            n_lo = min((n_lo << kFanoutLog2) + c_lo, below - 1);
+            n_hi = min((n_hi << kFanoutLog2) + c_hi, below - 1);
+        }
+    }
+    if (n_hi - n_lo > 1) return false;
+    const uint32_t c1 = shfl_count_le<C>(a_lo, x);
+    uint32_t r = (n_lo << kFanoutLog2) + c1;
+    if (n_hi != n_lo) {
+        const uint32_t c2 = shfl_count_le<C>(a_hi, x);
+        if (c1 == kFanout) r += c2;
+    }
+    result = min(r, n_c);
+    return true;
+}
+
 // Pass 1.  cnt_out[q] = number of hits, hi_out[q] = ub(S, q.end) (first rank starting past q.end).
 // err_flag bit 0 is set when a query has start > end (the reference cannot even construct such an
 // interval: interval.hpp:70-74); such queries get zero hits.
@@ -124,77 +210,153 @@ intersect_count_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, con
     const size_t n_tiles = (nq + blockDim.x - 1) / blockDim.x;
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const size_t q = tile * blockDim.x + threadIdx.x;
-        if (q >= nq) continue;
-        const uint32_t chrom = qchrom[q];
-        const Q qs_raw = qstart[q];
-        const Q qe_raw = qend[q];
-        uint32_t cnt = 0, hi = 0;
-        if (qs_raw > qe_raw) {
-            atomicOr(err_flag, 1u);
-        } else if (chrom < ix.n_chrom && !(sizeof(Q) > sizeof(C) && qs_raw > static_cast<Q>(coord_max<C>::value))) {
+        const bool in_range = q < nq;
+        uint32_t chrom = GG_NO_CHROM_DEV;
+        Q qs_raw = 0, qe_raw = 0;
+        if (in_range) {
+            chrom = qchrom[q];
+            qs_raw = qstart[q];
+            qe_raw = qend[q];
+        }
+        const bool bad = qs_raw > qe_raw;
+        if (bad) atomicOr(err_flag, 1u);
+        // answerable: known chromosome, valid interval, start inside the index coordinate domain
+        const bool ok = in_range && !bad && chrom < ix.n_chrom &&
+                        !(sizeof(Q) > sizeof(C) && qs_raw > static_cast<Q>(coord_max<C>::value));
+        const C qe = clamp_coord<C, Q>(qe_raw);
+        const C qs = ok ? static_cast<C>(qs_raw) : C(0);
+        const C xe = qs > 0 ? static_cast<C>(qs - 1) : C(0);  // #{end < q.start} = ub(E, q.start - 1)
+        uint32_t cnt = 0, hi = 0, lo = 0;
+
+        const uint32_t chrom0 = __shfl_sync(0xffffffffu, chrom, 0);
+        bool done = false;
+        if (__all_sync(0xffffffffu, ok && chrom == chrom0)) {
+            const uint32_t n_c = ix.cnt[chrom0];
+            done = warp_upper_bound<C>(ix.S, sS, stab, stride, ix.n_levels, ix.stage_level, chrom0, qe, n_c, hi) &&
+                   warp_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom0, xe, n_c, lo);
+        }
+        if (!done && ok) {  // per-lane descent: mixed chromosomes, invalid lanes or scattered coordinates
             const uint32_t n_c = ix.cnt[chrom];
-            const C qe = clamp_coord<C, Q>(qe_raw);
-            const C qs = static_cast<C>(qs_raw);
             hi = tree_upper_bound<C>(ix.S, sS, stab, stride, ix.n_levels, ix.stage_level, chrom, qe, n_c);
-            uint32_t lo = 0;
-            if (qs > 0) lo = tree_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom, static_cast<C>(qs - 1), n_c);
+            lo = tree_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom, xe, n_c);
+        }
+        if (ok) {
+            if (qs == 0) lo = 0;
             cnt = hi - lo;
         }
-        cnt_out[q] = cnt;
-        hi_out[q] = hi;
+        if (in_range) {
+            cnt_out[q] = cnt;
+            hi_out[q] = hi;
+        }
+    }
+}
+
+// 4 consecutive keys with one (u32) or two (u64) 16-byte loads; p must be 16-byte aligned
+__device__ __forceinline__ void load4(const uint32_t* __restrict__ p, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    a = v.x; b = v.y; c = v.z; d = v.w;
+}
+__device__ __forceinline__ void load4(const uint64_t* __restrict__ p, uint64_t& a, uint64_t& b, uint64_t& c, uint64_t& d) {
+    ulonglong2 v0 = *reinterpret_cast<const ulonglong2*>(p);
+    ulonglong2 v1 = *reinterpret_cast<const ulonglong2*>(p + 2);
+    a = v0.x; b = v0.y; c = v1.x; d = v1.y;
+}
+
+constexpr int kEmitStage = 512;  // staged hits per warp (2 KB): tiles of 32 queries with <= 512 hits are written coalesced
+
+// Backward walk of one query: ranks hi-1, hi-2, ... in aligned groups of 4 (16-byte vector loads of the leaf
+// ends), store(k, rank) for the k-th hit counted from the END of the query's list (k = n_hits-1 ... 0).
+// At a node boundary the max-end levels skip whole nodes / subtrees without a hit.
+template <typename C, typename Store>
+__device__ __forceinline__ void emit_walk(const IndexView<C>& ix, const uint32_t* __restrict__ stab, uint32_t stride,
+                                          int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t n_hits, Store store) {
+    const C* __restrict__ leaf_end = ix.M + stab[chrom];
+    uint32_t r_hi = hi;   // ranks >= r_hi are done
+    uint32_t rem = n_hits;
+    C e0, e1, e2, e3;
+    if ((r_hi & 3u) != 0 && rem != 0) {  // partial top group
+        const uint32_t g4 = r_hi & ~3u, top = r_hi & 3u;
+        load4(leaf_end + g4, e0, e1, e2, e3);
+        if (top > 2 && e2 >= qs && rem != 0) store(--rem, g4 + 2);
+        if (top > 1 && e1 >= qs && rem != 0) store(--rem, g4 + 1);
+        if (e0 >= qs && rem != 0) store(--rem, g4);
+        r_hi = g4;
+    }
+    while (rem != 0 && r_hi != 0) {
+        if ((r_hi & (kFanout - 1)) == 0 && n_levels > 1) {
+            // about to enter leaf node b from its last key: skip it (and, climbing while b is a last child,
+            // whole subtrees) when the max-end augmentation says nothing in there reaches q.start
+            uint32_t b = (r_hi >> kFanoutLog2) - 1;
+            if (ix.M[stab[stride + chrom] + b] < qs) {
+                int l = 1;
+                uint32_t span = kFanout;
+                while (l + 1 < n_levels && (b & (kFanout - 1)) == (kFanout - 1) &&
+                       ix.M[stab[(l + 1) * stride + chrom] + (b >> kFanoutLog2)] < qs) {
+                    b >>= kFanoutLog2;
+                    ++l;
+                    span <<= kFanoutLog2;
+                }
+                r_hi = (span > r_hi) ? 0u : r_hi - span;
+                continue;
+            }
+        }
+        const uint32_t g4 = r_hi - 4;
+        load4(leaf_end + g4, e0, e1, e2, e3);
+        if (e3 >= qs && rem != 0) store(--rem, g4 + 3);
+        if (e2 >= qs && rem != 0) store(--rem, g4 + 2);
+        if (e1 >= qs && rem != 0) store(--rem, g4 + 1);
+        if (e0 >= qs && rem != 0) store(--rem, g4);
+        r_hi = g4;
     }
 }
 
 // Pass 2.  hits[offsets[q] - hits_base ... offsets[q+1] - hits_base) = per-chromosome ranks, ascending.
+// A warp owns 32 consecutive queries, whose output ranges are contiguous in the CSR: lanes drop their hits
+// into a per-warp shared-memory stage and the warp then writes the stage out with coalesced stores.
 template <typename C, typename Q>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                       size_t nq, const uint32_t* __restrict__ hi_in, const uint64_t* __restrict__ offsets,
                       uint32_t* __restrict__ hits, uint64_t hits_base) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw);
+    uint32_t* stage = reinterpret_cast<uint32_t*>(smem_raw) + (threadIdx.x >> 5) * kEmitStage;
+    uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + (kQueryThreads / 32) * kEmitStage;
     const uint32_t stride = ix.n_chrom + 1;
     const uint32_t tab_elems = static_cast<uint32_t>(ix.n_levels) * stride;
     for (uint32_t i = threadIdx.x; i < tab_elems; i += blockDim.x) stab[i] = ix.tab[i];
     __syncthreads();
 
     const int n_levels = ix.n_levels;
+    const uint32_t lane = lane_id();
     const size_t n_tiles = (nq + kQueryThreads - 1) / kQueryThreads;
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const size_t q = tile * kQueryThreads + threadIdx.x;
-        if (q >= nq) continue;
-        const uint64_t o0 = offsets[q], o1 = offsets[q + 1];
-        uint32_t rem = static_cast<uint32_t>(o1 - o0);
-        if (rem == 0) continue;
-        const uint32_t chrom = qchrom[q];
-        const C qs = static_cast<C>(qstart[q]);  // rem > 0 implies q.start fits the index domain
-        const C* __restrict__ leaf_end = ix.M + stab[chrom];
-        uint32_t* out = hits + (o1 - hits_base);
-        int64_t r = static_cast<int64_t>(hi_in[q]) - 1;
-        while (rem != 0 && r >= 0) {
-            const uint32_t ru = static_cast<uint32_t>(r);
-            if ((ru & (kFanout - 1)) == (kFanout - 1) && n_levels > 1) {
-                // entering node b of level 0 from its last key: can the whole node be skipped?
-                uint32_t b = ru >> kFanoutLog2;
-                if (ix.M[stab[stride + chrom] + b] < qs) {
-                    int l = 1;
-                    int64_t span = kFanout;
-                    // climb while b is the last child of its parent and the parent holds no hit either
-                    while (l + 1 < n_levels && (b & (kFanout - 1)) == (kFanout - 1) &&
-                           ix.M[stab[(l + 1) * stride + chrom] + (b >> kFanoutLog2)] < qs) {
-                        b >>= kFanoutLog2;
-                        ++l;
-                        span <<= kFanoutLog2;
-                    }
-                    r -= span;
-                    continue;
-                }
-            }
-            if (leaf_end[ru] >= qs) {
-                *--out = ru;
-                --rem;
-            }
-            --r;
+        const size_t qa = q < nq ? q : nq, qb = q + 1 < nq ? q + 1 : nq;
+        const uint64_t o0 = offsets[qa], o1 = offsets[qb];
+        const uint32_t n_hits = static_cast<uint32_t>(o1 - o0);
+        const uint64_t wbase = __shfl_sync(0xffffffffu, o0, 0);
+        const uint64_t wtotal = __shfl_sync(0xffffffffu, o1, 31) - wbase;
+        if (wtotal == 0) continue;
+        uint32_t chrom = 0, hi = 0;
+        C qs = 0;
+        if (n_hits != 0) {
+            chrom = qchrom[q];
+            qs = static_cast<C>(qstart[q]);  // n_hits > 0 implies q.start fits the index domain
+            hi = hi_in[q];
+        }
+        if (wtotal <= kEmitStage) {
+            uint32_t* dst = stage + static_cast<uint32_t>(o0 - wbase);
+            if (n_hits != 0)
+                emit_walk<C>(ix, stab, stride, n_levels, chrom, qs, hi, n_hits,
+                             [dst](uint32_t k, uint32_t rank) { dst[k] = rank; });
+            __syncwarp();
+            uint32_t* out = hits + (wbase - hits_base);
+            for (uint32_t i = lane; i < static_cast<uint32_t>(wtotal); i += 32) out[i] = stage[i];
+            __syncwarp();
+        } else if (n_hits != 0) {
+            uint32_t* dst = hits + (o0 - hits_base);
+            emit_walk<C>(ix, stab, stride, n_levels, chrom, qs, hi, n_hits,
+                         [dst](uint32_t k, uint32_t rank) { dst[k] = rank; });
         }
     }
 }
