@@ -338,7 +338,7 @@ def main():
                "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
                "config": workload_config(args, world), "hit_pairs_per_sec": job_hits / (ms_per_step / 1e3),
-               "hits_per_query": job_hits / job_q, "gpu_launches": 3 * args.steps, "clocks": clocks,
+               "hits_per_query": job_hits / job_q, "gpu_launches": 4 * args.steps, "clocks": clocks,
                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                "index": {"levels": ist.n_levels, "fanout": ist.fanout, "staged_levels": ist.staged_levels,
                          "coord_bytes": ist.coord_bytes, "device_mb": ist.device_bytes / 1e6,

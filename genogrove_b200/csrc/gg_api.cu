@@ -159,9 +159,12 @@ size_t emit_smem_bytes(const gg_index* idx) {
     return static_cast<size_t>(kQueryThreads / 32) * kEmitStage * 4 + tab_elems * 4 + 16;
 }
 
+// Pass 1 + offsets: count kernel (also accumulates per-4096-query tile totals), scan of the tile totals,
+// per-tile scan of the counts.  3 kernel launches; offsets[0..nq] are final (+ *d_base) afterwards.
 template <typename C, typename Q>
 gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, size_t nq,
-                       uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, cudaStream_t st) {
+                       uint64_t* d_off, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, void* scratch,
+                       const uint64_t* d_base, cudaStream_t st, cudaEvent_t ev_after_count) {
     auto kern = intersect_count_kernel<C, Q>;
     size_t smem = count_smem_bytes(idx);
     GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -172,12 +175,18 @@ gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
     }
     size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(threads));
+    GG_CUDA(scan2_prepare_async(scratch, nq, st));
     unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
-    kern<<<grid, threads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi, d_err);
+    kern<<<grid, threads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi,
+                                      scan2_tile_total(scratch), d_err);
     GG_CUDA(cudaGetLastError());
-    idx->bstats.kernel_launches++;
+    if (ev_after_count) GG_CUDA(cudaEventRecord(ev_after_count, st));
+    GG_CUDA(scan2_finish_async(d_cnt, d_off, nq, scratch, d_base, st));
+    idx->bstats.kernel_launches += 3;
     return GG_OK;
 }
+
+inline size_t count_scratch_bytes(size_t nq) { return scan2_scratch_bytes(nq); }
 
 template <typename C, typename Q>
 gg_status launch_emit(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, size_t nq, const uint32_t* d_hi,
@@ -201,14 +210,15 @@ gg_status launch_emit(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, 
 
 // dispatch on (index coord width, query coord width)
 gg_status dispatch_count(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
-                         int q_bytes, size_t nq, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, cudaStream_t st) {
+                         int q_bytes, size_t nq, uint64_t* d_off, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err,
+                         void* scratch, const uint64_t* d_base, cudaStream_t st, cudaEvent_t ev = nullptr) {
     if (idx->coord_bytes == 4 && q_bytes == 4)
-        return launch_count<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+        return launch_count<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_off, d_cnt, d_hi, d_err, scratch, d_base, st, ev);
     if (idx->coord_bytes == 4 && q_bytes == 8)
-        return launch_count<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+        return launch_count<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_off, d_cnt, d_hi, d_err, scratch, d_base, st, ev);
     if (idx->coord_bytes == 8 && q_bytes == 4)
-        return launch_count<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_cnt, d_hi, d_err, st);
-    return launch_count<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_cnt, d_hi, d_err, st);
+        return launch_count<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_off, d_cnt, d_hi, d_err, scratch, d_base, st, ev);
+    return launch_count<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_off, d_cnt, d_hi, d_err, scratch, d_base, st, ev);
 }
 gg_status dispatch_emit(gg_index* idx, const uint32_t* d_chrom, const void* d_start, int q_bytes, size_t nq,
                         const uint32_t* d_hi, const uint64_t* d_off, uint32_t* d_hits, uint64_t hits_base,
@@ -496,7 +506,7 @@ gg_status ensure_query_scratch(gg_index* idx, size_t nq) {
     const size_t m = nq ? nq : 1;
     GG_CUDA(idx->q_cnt.ensure(m * 4));
     GG_CUDA(idx->q_hi.ensure(m * 4));
-    GG_CUDA(idx->scan_scratch.ensure(scan_state_bytes(m)));
+    GG_CUDA(idx->scan_scratch.ensure(count_scratch_bytes(m)));
     GG_CUDA(idx->err_flag.ensure(16));
     return GG_OK;
 }
@@ -592,18 +602,17 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
         GG_CUDA(sl.cnt.ensure(m * 4));
         GG_CUDA(sl.hi.ensure(m * 4));
         GG_CUDA(sl.off.ensure((m + 1) * 8));
-        GG_CUDA(sl.scan.ensure(scan_state_bytes(m)));
+        GG_CUDA(sl.scan.ensure(count_scratch_bytes(m)));
         GG_CUDA(cudaMemcpyAsync(sl.qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
         GG_CUDA(cudaMemcpyAsync(sl.qs.p, q_start + q0, m * sizeof(Q), cudaMemcpyHostToDevice, sl.st));
         GG_CUDA(cudaMemcpyAsync(sl.qe.p, q_end + q0, m * sizeof(Q), cudaMemcpyHostToDevice, sl.st));
-        gg_status r = dispatch_count(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, sizeof(Q), m, sl.cnt.as<uint32_t>(),
-                                     sl.hi.as<uint32_t>(), idx->err_flag.as<uint32_t>(), sl.st);
-        if (r != GG_OK) return r;
+        // the scan starts from the running hit total left by the previous chunk
         if (prev_scan) GG_CUDA(cudaStreamWaitEvent(sl.st, prev_scan, 0));
         uint64_t* d_base = idx->d_base.as<uint64_t>();
-        GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(sl.cnt.as<uint32_t>(), sl.off.as<uint64_t>(), m, sl.scan.p,
-                                                           d_base + k, nullptr, sl.st)));
-        idx->bstats.kernel_launches++;
+        gg_status r = dispatch_count(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, sizeof(Q), m, sl.off.as<uint64_t>(),
+                                     sl.cnt.as<uint32_t>(), sl.hi.as<uint32_t>(), idx->err_flag.as<uint32_t>(), sl.scan.p,
+                                     d_base + k, sl.st);
+        if (r != GG_OK) return r;
         // next base = last offset of this chunk (off[m] = base + total)
         GG_CUDA(cudaMemcpyAsync(d_base + k + 1, sl.off.as<uint64_t>() + m, 8, cudaMemcpyDeviceToDevice, sl.st));
         GG_CUDA(cudaEventRecord(sl.ev_scan, sl.st));
@@ -791,13 +800,10 @@ gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, cons
     idx->ev_count_valid = idx->ev_emit_valid = false;
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
     if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[0], st));
-    s = dispatch_count(idx, d_chrom, d_start, d_end, coord_bytes, nq, idx->q_cnt.as<uint32_t>(), idx->q_hi.as<uint32_t>(),
-                       idx->err_flag.as<uint32_t>(), st);
+    s = dispatch_count(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_offsets, idx->q_cnt.as<uint32_t>(),
+                       idx->q_hi.as<uint32_t>(), idx->err_flag.as<uint32_t>(), idx->scan_scratch.p, nullptr, st,
+                       idx->timing ? idx->ev[1] : nullptr);
     if (s != GG_OK) return s;
-    if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[1], st));
-    GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(idx->q_cnt.as<uint32_t>(), d_offsets, nq, idx->scan_scratch.p, nullptr,
-                                                       nullptr, st)));
-    idx->bstats.kernel_launches++;
     if (idx->timing) {
         GG_CUDA(cudaEventRecord(idx->ev[2], st));
         idx->ev_count_valid = true;

@@ -19,6 +19,7 @@
 // bulk copy (cp.async.bulk + mbarrier), the rest is read through L1/L2.
 #pragma once
 #include "common.cuh"
+#include "scan.cuh"
 
 namespace gg {
 
@@ -171,14 +172,17 @@ __device__ __forceinline__ bool warp_upper_bound(const C* __restrict__ g, const 
     return true;
 }
 
-// Pass 1.  cnt_out[q] = number of hits, hi_out[q] = ub(S, q.end) (first rank starting past q.end).
+// Pass 1.  cnt_out[q] = number of hits, hi_out[q] = ub(S, q.end) (first rank starting past q.end) for
+// pass 2, and tile_total[q / 4096] += hits (one 64-bit reduction per warp) so that the exclusive scan that
+// follows needs no look-back chain: it reads each count once and writes each offset once (scan.cuh).
 // err_flag bit 0 is set when a query has start > end (the reference cannot even construct such an
 // interval: interval.hpp:70-74); such queries get zero hits.
 template <typename C, typename Q>
 __global__ void __launch_bounds__(1024)
 intersect_count_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                        const Q* __restrict__ qend, size_t nq, uint32_t* __restrict__ cnt_out,
-                       uint32_t* __restrict__ hi_out, uint32_t* __restrict__ err_flag) {
+                       uint32_t* __restrict__ hi_out, unsigned long long* __restrict__ tile_total,
+                       uint32_t* __restrict__ err_flag) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     // layout: [S prefix][E prefix][tab][mbarrier]
     C* sS = reinterpret_cast<C*>(smem_raw);
@@ -248,6 +252,11 @@ intersect_count_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, con
             cnt_out[q] = cnt;
             hi_out[q] = hi;
         }
+        // warp total -> its 4096-query scan tile (the warp's 32 queries never straddle a tile)
+        unsigned long long wsum = cnt;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        if (lane_id() == 0 && wsum != 0) atomicAdd(&tile_total[(tile * blockDim.x + (threadIdx.x & ~31u)) / kScanTile], wsum);
     }
 }
 

@@ -25,6 +25,66 @@ struct ScanTileState {
     uint32_t* ticket; // [1]
 };
 
+// generic versions in tiles (used by the fused count+scan kernel, whose tile is one CTA of queries)
+inline size_t tile_state_bytes(size_t tiles) { return round_up(tiles * 4 + 16, 16) + tiles * 16; }
+inline size_t tile_state_zero_bytes(size_t tiles) { return round_up(tiles * 4 + 16, 16); }
+inline ScanTileState tile_state_carve(void* scratch, size_t tiles) {
+    ScanTileState s;
+    char* p = static_cast<char*>(scratch);
+    s.ticket = reinterpret_cast<uint32_t*>(p);
+    s.flag = reinterpret_cast<uint32_t*>(p + 16);
+    size_t head = round_up(tiles * 4 + 16, 16);
+    s.agg = reinterpret_cast<uint64_t*>(p + head);
+    s.incl = s.agg + tiles;
+    return s;
+}
+
+// Decoupled look-back, executed by ONE WARP of the CTA that owns `tile`: publishes the tile aggregate and
+// returns (to every lane) the exclusive prefix = sum of the aggregates of all earlier tiles.
+__device__ __forceinline__ uint64_t tile_lookback(const ScanTileState& st, uint32_t tile, uint64_t block_total) {
+    const uint32_t lane = threadIdx.x & 31u;
+    uint64_t excl = 0;
+    if (tile == 0) {
+        if (lane == 0) {
+            st.incl[0] = block_total;
+            __threadfence();
+            *reinterpret_cast<volatile uint32_t*>(&st.flag[0]) = 2u;
+        }
+        return 0;
+    }
+    if (lane == 0) {
+        st.agg[tile] = block_total;
+        __threadfence();
+        *reinterpret_cast<volatile uint32_t*>(&st.flag[tile]) = 1u;
+    }
+    int64_t j = static_cast<int64_t>(tile) - 1;
+    while (true) {
+        int64_t idx = j - static_cast<int64_t>(lane);
+        uint32_t f = 2u;  // tiles before tile 0 behave as "inclusive prefix = 0"
+        if (idx >= 0) {
+            do {
+                f = ld_volatile(&st.flag[idx]);
+            } while (f == 0u);
+        }
+        __threadfence();  // acquire: values below were published before the flag
+        uint32_t incl_mask = __ballot_sync(0xffffffffu, f == 2u);
+        uint32_t first_incl = incl_mask ? static_cast<uint32_t>(__ffs(incl_mask) - 1) : 32u;
+        uint64_t val = 0;
+        if (idx >= 0 && lane <= first_incl) val = (f == 2u) ? ld_volatile(&st.incl[idx]) : ld_volatile(&st.agg[idx]);
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+        excl += val;
+        if (incl_mask) break;
+        j -= 32;
+    }
+    if (lane == 0) {
+        st.incl[tile] = excl + block_total;
+        __threadfence();
+        *reinterpret_cast<volatile uint32_t*>(&st.flag[tile]) = 2u;
+    }
+    return excl;
+}
+
 inline size_t scan_state_bytes(size_t n_items) {
     size_t tiles = div_up(n_items ? n_items : 1, kScanTile);
     return round_up(tiles * 4 + 16, 16) + tiles * 16;
@@ -47,7 +107,10 @@ inline size_t scan_state_zero_bytes(size_t n_items) {
     return round_up(tiles * 4 + 16, 16);
 }
 
-template <typename In, typename Out>
+// kLookback = true : single pass, tile prefixes by decoupled look-back (tile ids from an atomic ticket).
+// kLookback = false: tile prefixes are given (st.incl[tile] = exclusive prefix of tile `tile`, e.g. the scanned
+//                    per-tile totals the count kernel accumulated); no inter-CTA dependency at all.
+template <typename In, typename Out, bool kLookback = true>
 __global__ void __launch_bounds__(kScanThreads)
 exclusive_scan_kernel(const In* __restrict__ in, Out* __restrict__ out, size_t n, ScanTileState st,
                       const uint64_t* __restrict__ base_ptr, uint64_t* __restrict__ total_out) {
@@ -55,9 +118,11 @@ exclusive_scan_kernel(const In* __restrict__ in, Out* __restrict__ out, size_t n
     __shared__ uint64_t tile_excl;
     __shared__ uint32_t tile_id_s;
 
-    if (threadIdx.x == 0) tile_id_s = atomicAdd(st.ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = tile_id_s;
+    if (kLookback) {
+        if (threadIdx.x == 0) tile_id_s = atomicAdd(st.ticket, 1u);
+        __syncthreads();
+    }
+    const uint32_t tile = kLookback ? tile_id_s : blockIdx.x;
     const size_t tile_base = static_cast<size_t>(tile) * kScanTile;
     const uint64_t base = base_ptr ? *base_ptr : 0ull;
 
@@ -107,47 +172,7 @@ exclusive_scan_kernel(const In* __restrict__ in, Out* __restrict__ out, size_t n
 
     // decoupled look-back by warp 0
     if (warp == 0) {
-        uint64_t excl = 0;
-        if (tile == 0) {
-            if (lane_id() == 0) {
-                st.incl[0] = block_total;
-                __threadfence();
-                *reinterpret_cast<volatile uint32_t*>(&st.flag[0]) = 2u;
-            }
-        } else {
-            if (lane_id() == 0) {
-                st.agg[tile] = block_total;
-                __threadfence();
-                *reinterpret_cast<volatile uint32_t*>(&st.flag[tile]) = 1u;
-            }
-            int64_t j = static_cast<int64_t>(tile) - 1;
-            while (true) {
-                int64_t idx = j - static_cast<int64_t>(lane_id());
-                uint32_t f = 2u;  // tiles before tile 0 behave as "inclusive prefix = 0"
-                if (idx >= 0) {
-                    do {
-                        f = ld_volatile(&st.flag[idx]);
-                    } while (f == 0u);
-                }
-                __threadfence();  // acquire: values below were published before the flag
-                uint32_t incl_mask = __ballot_sync(0xffffffffu, f == 2u);
-                uint32_t first_incl = incl_mask ? static_cast<uint32_t>(__ffs(incl_mask) - 1) : 32u;
-                uint64_t val = 0;
-                if (idx >= 0 && lane_id() <= first_incl) {
-                    val = (f == 2u) ? ld_volatile(&st.incl[idx]) : ld_volatile(&st.agg[idx]);
-                }
-#pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-                excl += val;
-                if (incl_mask) break;
-                j -= 32;
-            }
-            if (lane_id() == 0) {
-                st.incl[tile] = excl + block_total;
-                __threadfence();
-                *reinterpret_cast<volatile uint32_t*>(&st.flag[tile]) = 2u;
-            }
-        }
+        uint64_t excl = kLookback ? tile_lookback(st, tile, block_total) : st.incl[tile];
         if (lane_id() == 0) tile_excl = excl;
     }
     __syncthreads();
@@ -192,6 +217,35 @@ inline cudaError_t exclusive_scan_async(const In* in, Out* out, size_t n, void* 
     size_t tiles = div_up(n ? n : 1, kScanTile);
     exclusive_scan_kernel<In, Out><<<static_cast<unsigned>(tiles), kScanThreads, 0, stream>>>(in, out, n, st,
                                                                                              base_ptr, total_out);
+    return cudaGetLastError();
+}
+
+// Two-level scan for the query counts.  tile_total[t] (u64, one per kScanTile counts, accumulated by the count
+// kernel) is scanned first (a few CTAs), then every tile scans its own counts from its known prefix:
+// counts are read once, offsets written once, and no CTA waits on another.
+// scratch layout: [tile_total u64 x tiles][tile_prefix u64 x (tiles+1)][look-back state for the small scan]
+inline size_t scan2_tiles(size_t n) { return div_up(n ? n : 1, kScanTile); }
+inline size_t scan2_scratch_bytes(size_t n) {
+    size_t t = scan2_tiles(n);
+    return round_up(t * 8, 256) + round_up((t + 1) * 8, 256) + scan_state_bytes(t);
+}
+inline unsigned long long* scan2_tile_total(void* scratch) { return static_cast<unsigned long long*>(scratch); }
+inline cudaError_t scan2_prepare_async(void* scratch, size_t n, cudaStream_t stream) {
+    return cudaMemsetAsync(scratch, 0, scan2_tiles(n) * 8, stream);
+}
+inline cudaError_t scan2_finish_async(const uint32_t* counts, uint64_t* offsets, size_t n, void* scratch,
+                                      const uint64_t* base_ptr, cudaStream_t stream) {
+    size_t t = scan2_tiles(n);
+    char* p = static_cast<char*>(scratch);
+    uint64_t* tile_total = reinterpret_cast<uint64_t*>(p);
+    uint64_t* tile_prefix = reinterpret_cast<uint64_t*>(p + round_up(t * 8, 256));
+    void* state = p + round_up(t * 8, 256) + round_up((t + 1) * 8, 256);
+    cudaError_t e = exclusive_scan_async<uint64_t, uint64_t>(tile_total, tile_prefix, t, state, nullptr, nullptr, stream);
+    if (e != cudaSuccess) return e;
+    ScanTileState st{};
+    st.incl = tile_prefix;
+    exclusive_scan_kernel<uint32_t, uint64_t, false><<<static_cast<unsigned>(t), kScanThreads, 0, stream>>>(
+        counts, offsets, n, st, base_ptr, nullptr);
     return cudaGetLastError();
 }
 

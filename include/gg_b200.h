@@ -82,8 +82,8 @@ typedef struct gg_batch_stats {
     uint64_t n_hits;
     uint32_t n_chunks;       /* pipeline chunks used by the host-buffer entry points */
     uint32_t kernel_launches;/* kernels launched by the last intersect call */
-    double count_ms;         /* device time: count kernel (last call, summed over chunks) */
-    double scan_ms;          /* device time: exclusive scan */
+    double count_ms;         /* device time: count kernel (device-buffer calls with option "timing" on) */
+    double scan_ms;          /* device time: exclusive scan (tile-total scan + per-tile scan kernels) */
     double emit_ms;          /* device time: emit kernel */
     double total_ms;         /* device time first launch/copy -> last, host buffers included */
 } gg_batch_stats;

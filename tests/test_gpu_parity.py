@@ -175,7 +175,7 @@ def test_device_buffer_api(gg, oracle):
         assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
         assert np.array_equal(d_hits.cpu().numpy().view(np.uint32)[:total], exp_hits)
         bs = idx.batch_stats()
-        assert bs.count_ms > 0 and bs.emit_ms > 0 and bs.kernel_launches == 3
+        assert bs.count_ms > 0 and bs.emit_ms > 0 and bs.kernel_launches == 4
 
 
 def test_long_nested_intervals_use_max_end_pruning(gg, oracle):
