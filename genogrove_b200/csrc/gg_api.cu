@@ -22,7 +22,7 @@ using namespace gg;
 namespace {
 
 constexpr int kSlots = 3;        // pipeline depth of the host-buffer path
-constexpr int kCountThreadsDefault = 512;
+constexpr int kCountThreadsDefault = 256;
 
 struct DeviceBuf {
     void* p = nullptr;
@@ -102,7 +102,7 @@ struct gg_index {
 
     // ---- options
     int64_t chunk_queries = 8388608;
-    int64_t stage_bytes = 98304;
+    int64_t stage_bytes = 16384;
     int64_t count_threads = kCountThreadsDefault;
     int64_t count_ctas_per_sm = 0;  // 0 = occupancy API
     int64_t emit_ctas_per_sm = 0;
@@ -152,11 +152,11 @@ IndexView<C> make_view(const gg_index* idx) {
 
 size_t count_smem_bytes(const gg_index* idx) {
     size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
-    return 2 * static_cast<size_t>(idx->staged_elems) * idx->coord_bytes + ((tab_elems + 3) & ~size_t(3)) * 4 + 16;
+    return 2 * (static_cast<size_t>(idx->staged_elems) + kWin) * idx->coord_bytes + ((tab_elems + 3) & ~size_t(3)) * 4 + 32;
 }
 size_t emit_smem_bytes(const gg_index* idx) {
     size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
-    return static_cast<size_t>(kQueryThreads / 32) * kEmitStage * 4 + tab_elems * 4 + 16;
+    return static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitSlack) * 4 + tab_elems * 4 + 16;
 }
 
 // Pass 1 + offsets: count kernel (also accumulates per-4096-query tile totals), scan of the tile totals,

@@ -172,9 +172,62 @@ __device__ __forceinline__ bool warp_upper_bound(const C* __restrict__ g, const 
     return true;
 }
 
+// ---- CTA-cooperative search window (coordinate-sorted batches) ------------------------------------------
+constexpr int kWin = 512;  // keys per staged window (per family, per CTA)
+
+// Warp-cooperative descents for FOUR search keys at once (ILP across the four dependent chains): ub(S, x[0]),
+// ub(S, x[1]), ub(E, x[2]), ub(E, x[3]) on one chromosome.  One coalesced node load + one ballot per level
+// and key.  All arguments warp-uniform; results warp-uniform.
+template <typename C>
+__device__ __forceinline__ void coop_upper_bound4(const IndexView<C>& ix, const C* __restrict__ sS, const C* __restrict__ sE,
+                                                  const uint32_t* __restrict__ tab, uint32_t stride, uint32_t chrom,
+                                                  uint32_t n_c, const C (&x)[4], uint32_t (&res)[4]) {
+    const uint32_t lane = lane_id();
+    uint32_t node[4] = {0, 0, 0, 0};
+    for (int l = ix.n_levels - 1; l >= 0; --l) {
+        const uint32_t off = tab[l * stride + chrom];
+        const bool staged = l >= ix.stage_level;
+        const C* bS = (staged ? sS : ix.S) + off;
+        const C* bE = (staged ? sE : ix.E) + off;
+        C a[4];
+        a[0] = bS[(node[0] << kFanoutLog2) + lane];
+        a[1] = bS[(node[1] << kFanoutLog2) + lane];
+        a[2] = bE[(node[2] << kFanoutLog2) + lane];
+        a[3] = bE[(node[3] << kFanoutLog2) + lane];
+        const uint32_t below = l > 0 ? (tab[(l - 1) * stride + chrom + 1] - tab[(l - 1) * stride + chrom]) >> kFanoutLog2 : 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t c = __popc(__ballot_sync(0xffffffffu, a[k] <= x[k]));
+            const uint32_t child = (node[k] << kFanoutLog2) + c;
+            if (l > 0) node[k] = min(child, below - 1);
+            else res[k] = min(child, n_c);
+        }
+    }
+}
+
+// #keys <= x among win[0..ws) (sorted, in shared memory); pow2 = largest power of two <= ws (0 when ws == 0)
+template <typename C>
+__device__ __forceinline__ uint32_t window_count_le(const C* __restrict__ win, uint32_t ws, uint32_t pow2, C x) {
+    uint32_t c = 0;
+    for (uint32_t step = pow2; step != 0; step >>= 1) {
+        const uint32_t t = c + step;
+        if (t <= ws && win[t - 1] <= x) c = t;
+    }
+    return c;
+}
+
 // Pass 1.  cnt_out[q] = number of hits, hi_out[q] = ub(S, q.end) (first rank starting past q.end) for
 // pass 2, and tile_total[q / 4096] += hits (one 64-bit reduction per warp) so that the exclusive scan that
-// follows needs no look-back chain: it reads each count once and writes each offset once (scan.cuh).
+// follows needs no look-back chain (scan.cuh).
+//
+// Three tiers, chosen per query tile (one CTA = blockDim.x consecutive queries), all giving identical results:
+//   1. CTA window  — every query of the tile is on one chromosome: warp 0 descends the tree for the tile's
+//      min/max search keys (4 cooperative descents, ballot + popc per node), which brackets every query's
+//      answer inside S[s_lo, s_hi) and E[e_lo, e_hi).  If both brackets fit kWin keys they are copied into
+//      shared memory by TMA bulk copies (cp.async.bulk + mbarrier) and each thread finishes with a short
+//      binary search in shared memory.  This is the path coordinate-sorted batches take.
+//   2. warp bracket — same idea per warp with register shuffles (warp_upper_bound).
+//   3. per-lane descent of the tree (tree_upper_bound) — scattered queries.
 // err_flag bit 0 is set when a query has start > end (the reference cannot even construct such an
 // interval: interval.hpp:70-74); such queries get zero hits.
 template <typename C, typename Q>
@@ -184,33 +237,42 @@ intersect_count_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, con
                        uint32_t* __restrict__ hi_out, unsigned long long* __restrict__ tile_total,
                        uint32_t* __restrict__ err_flag) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    // layout: [S prefix][E prefix][tab][mbarrier]
+    // layout: [S prefix][E prefix][winS][winE][tab][barriers]
     C* sS = reinterpret_cast<C*>(smem_raw);
     C* sE = sS + ix.staged_elems;
-    uint32_t* stab = reinterpret_cast<uint32_t*>(sE + ix.staged_elems);
+    C* winS = sE + ix.staged_elems;
+    C* winE = winS + kWin;
+    uint32_t* stab = reinterpret_cast<uint32_t*>(winE + kWin);
     const uint32_t stride = ix.n_chrom + 1;
     const uint32_t tab_elems = static_cast<uint32_t>(ix.n_levels) * stride;
-    uint64_t* bar = reinterpret_cast<uint64_t*>(stab + ((tab_elems + 3u) & ~3u));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(stab + ((tab_elems + 3u) & ~3u));  // bar[0]: staging, bar[1]: windows
+    __shared__ uint32_t s_wchrom[32];
+    __shared__ C s_wkey[4][32];   // per warp: min q.end, max q.end, min (q.start-1), max (q.start-1)
+    __shared__ uint32_t s_bounds[8];
 
     if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
         mbar_fence_init();
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         const uint32_t bytes = ix.staged_elems * static_cast<uint32_t>(sizeof(C));
-        mbar_arrive_expect_tx(bar, 2u * bytes);
+        mbar_arrive_expect_tx(&bar[0], 2u * bytes);
         constexpr uint32_t kChunk = 32768;
         for (uint32_t o = 0; o < bytes; o += kChunk) {
             uint32_t len = min(kChunk, bytes - o);
-            tma_bulk_g2s(reinterpret_cast<char*>(sS) + o, reinterpret_cast<const char*>(ix.S) + o, len, bar);
-            tma_bulk_g2s(reinterpret_cast<char*>(sE) + o, reinterpret_cast<const char*>(ix.E) + o, len, bar);
+            tma_bulk_g2s(reinterpret_cast<char*>(sS) + o, reinterpret_cast<const char*>(ix.S) + o, len, &bar[0]);
+            tma_bulk_g2s(reinterpret_cast<char*>(sE) + o, reinterpret_cast<const char*>(ix.E) + o, len, &bar[0]);
         }
     }
     for (uint32_t i = threadIdx.x; i < tab_elems; i += blockDim.x) stab[i] = ix.tab[i];
     __syncthreads();
-    mbar_wait(bar, 0);
+    mbar_wait(&bar[0], 0);
 
+    constexpr uint32_t kAlign = 16 / sizeof(C);  // TMA source alignment in keys
+    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    uint32_t phase = 0;
     const size_t n_tiles = (nq + blockDim.x - 1) / blockDim.x;
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const size_t q = tile * blockDim.x + threadIdx.x;
@@ -232,21 +294,83 @@ intersect_count_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, con
         const C xe = qs > 0 ? static_cast<C>(qs - 1) : C(0);  // #{end < q.start} = ub(E, q.start - 1)
         uint32_t cnt = 0, hi = 0, lo = 0;
 
+        // ---- tier 1: tile-wide bracket + TMA-staged windows
         const uint32_t chrom0 = __shfl_sync(0xffffffffu, chrom, 0);
-        bool done = false;
-        if (__all_sync(0xffffffffu, ok && chrom == chrom0)) {
-            const uint32_t n_c = ix.cnt[chrom0];
-            done = warp_upper_bound<C>(ix.S, sS, stab, stride, ix.n_levels, ix.stage_level, chrom0, qe, n_c, hi) &&
-                   warp_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom0, xe, n_c, lo);
+        const bool warp_uniform = __all_sync(0xffffffffu, ok && chrom == chrom0);
+        {
+            const C e_min = warp_min(qe), e_max = warp_max(qe), s_min = warp_min(xe), s_max = warp_max(xe);
+            if (lane == 0) {
+                s_wchrom[warp] = warp_uniform ? chrom0 : GG_NO_CHROM_DEV;
+                s_wkey[0][warp] = e_min;
+                s_wkey[1][warp] = e_max;
+                s_wkey[2][warp] = s_min;
+                s_wkey[3][warp] = s_max;
+            }
         }
-        if (!done && ok) {  // per-lane descent: mixed chromosomes, invalid lanes or scattered coordinates
-            const uint32_t n_c = ix.cnt[chrom];
-            hi = tree_upper_bound<C>(ix.S, sS, stab, stride, ix.n_levels, ix.stage_level, chrom, qe, n_c);
-            lo = tree_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom, xe, n_c);
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t wl = lane < n_warps ? lane : 0;
+            const uint32_t chrom_t = s_wchrom[0];
+            const bool uni = __all_sync(0xffffffffu, s_wchrom[wl] == chrom_t) && chrom_t != GG_NO_CHROM_DEV;
+            uint32_t mode = 0, r[4] = {0, 0, 0, 0}, a_s = 0, a_e = 0, len_s = 0, len_e = 0;
+            if (uni) {
+                C x[4];
+                x[0] = warp_min(s_wkey[0][wl]);
+                x[1] = warp_max(s_wkey[1][wl]);
+                x[2] = warp_min(s_wkey[2][wl]);
+                x[3] = warp_max(s_wkey[3][wl]);
+                const uint32_t n_c = ix.cnt[chrom_t];
+                coop_upper_bound4<C>(ix, sS, sE, stab, stride, chrom_t, n_c, x, r);
+                a_s = r[0] & ~(kAlign - 1);
+                a_e = r[2] & ~(kAlign - 1);
+                len_s = (r[1] - a_s + kAlign - 1) & ~(kAlign - 1);
+                len_e = (r[3] - a_e + kAlign - 1) & ~(kAlign - 1);
+                mode = (len_s <= kWin && len_e <= kWin) ? 1u : 0u;
+            }
+            if (lane == 0) {
+                s_bounds[0] = mode;
+                s_bounds[1] = r[0];            // s_lo
+                s_bounds[2] = r[1] - r[0];     // keys of S in the bracket
+                s_bounds[3] = r[0] - a_s;      // offset of s_lo inside the staged window
+                s_bounds[4] = r[2];            // e_lo
+                s_bounds[5] = r[3] - r[2];
+                s_bounds[6] = r[2] - a_e;
+                if (mode) {
+                    const uint32_t leaf = stab[chrom_t];
+                    mbar_arrive_expect_tx(&bar[1], (len_s + len_e) * static_cast<uint32_t>(sizeof(C)));
+                    if (len_s) tma_bulk_g2s(winS, ix.S + leaf + a_s, len_s * static_cast<uint32_t>(sizeof(C)), &bar[1]);
+                    if (len_e) tma_bulk_g2s(winE, ix.E + leaf + a_e, len_e * static_cast<uint32_t>(sizeof(C)), &bar[1]);
+                } else {
+                    mbar_arrive(&bar[1]);
+                }
+            }
+        }
+        mbar_wait(&bar[1], phase);
+        phase ^= 1u;
+        if (s_bounds[0]) {
+            const uint32_t ws = s_bounds[2], we = s_bounds[5];
+            const uint32_t p2s = ws ? 1u << (31 - __clz(ws)) : 0u, p2e = we ? 1u << (31 - __clz(we)) : 0u;
+            hi = s_bounds[1] + window_count_le<C>(winS + s_bounds[3], ws, p2s, qe);
+            lo = s_bounds[4] + window_count_le<C>(winE + s_bounds[6], we, p2e, xe);
+        } else {
+            // ---- tier 2: warp bracket; tier 3: per-lane descent
+            bool done = false;
+            if (warp_uniform) {
+                const uint32_t n_c = ix.cnt[chrom0];
+                done = warp_upper_bound<C>(ix.S, sS, stab, stride, ix.n_levels, ix.stage_level, chrom0, qe, n_c, hi) &&
+                       warp_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom0, xe, n_c, lo);
+            }
+            if (!done && ok) {
+                const uint32_t n_c = ix.cnt[chrom];
+                hi = tree_upper_bound<C>(ix.S, sS, stab, stride, ix.n_levels, ix.stage_level, chrom, qe, n_c);
+                lo = tree_upper_bound<C>(ix.E, sE, stab, stride, ix.n_levels, ix.stage_level, chrom, xe, n_c);
+            }
         }
         if (ok) {
             if (qs == 0) lo = 0;
             cnt = hi - lo;
+        } else {
+            hi = 0;
         }
         if (in_range) {
             cnt_out[q] = cnt;
@@ -256,7 +380,7 @@ intersect_count_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, con
         unsigned long long wsum = cnt;
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
-        if (lane_id() == 0 && wsum != 0) atomicAdd(&tile_total[(tile * blockDim.x + (threadIdx.x & ~31u)) / kScanTile], wsum);
+        if (lane == 0 && wsum != 0) atomicAdd(&tile_total[(tile * blockDim.x + (threadIdx.x & ~31u)) / kScanTile], wsum);
     }
 }
 
@@ -272,49 +396,96 @@ __device__ __forceinline__ void load4(const uint64_t* __restrict__ p, uint64_t& 
 }
 
 constexpr int kEmitStage = 512;  // staged hits per warp (2 KB): tiles of 32 queries with <= 512 hits are written coalesced
+constexpr int kEmitSlack = 4;    // spare slots in front of each warp's stage (see emit_walk_staged)
+
+// Skip test at a leaf-node boundary (r_hi % 32 == 0): how many ranks below r_hi can be skipped because the
+// max-end augmentation says no key in them reaches q.start (whole node, or whole subtrees while climbing).
+template <typename C>
+__device__ __forceinline__ uint32_t emit_skip_span(const IndexView<C>& ix, const uint32_t* __restrict__ stab, uint32_t stride,
+                                                   int n_levels, uint32_t chrom, C qs, uint32_t r_hi) {
+    uint32_t b = (r_hi >> kFanoutLog2) - 1;  // leaf node about to be entered from its last key
+    if (!(ix.M[stab[stride + chrom] + b] < qs)) return 0;
+    int l = 1;
+    uint32_t span = kFanout;
+    while (l + 1 < n_levels && (b & (kFanout - 1)) == (kFanout - 1) &&
+           ix.M[stab[(l + 1) * stride + chrom] + (b >> kFanoutLog2)] < qs) {
+        b >>= kFanoutLog2;
+        ++l;
+        span <<= kFanoutLog2;
+    }
+    return span > r_hi ? r_hi : span;
+}
 
 // Backward walk of one query: ranks hi-1, hi-2, ... in aligned groups of 4 (16-byte vector loads of the leaf
-// ends), store(k, rank) for the k-th hit counted from the END of the query's list (k = n_hits-1 ... 0).
-// At a node boundary the max-end levels skip whole nodes / subtrees without a hit.
-template <typename C, typename Store>
-__device__ __forceinline__ void emit_walk(const IndexView<C>& ix, const uint32_t* __restrict__ stab, uint32_t stride,
-                                          int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t n_hits, Store store) {
+// ends).  Hits go to the shared-memory stage back to front: s_end = shared address one past the query's last
+// slot, s_begin = address of its first slot; the walk ends when the list is full.  Stores are not individually
+// bounds-checked: with offsets that match the counts the list fills exactly; with inconsistent caller input at
+// most 3 stray slots below s_begin are touched, which stay inside the stage (kEmitSlack).
+template <typename C>
+__device__ __forceinline__ void emit_walk_staged(const IndexView<C>& ix, const uint32_t* __restrict__ stab, uint32_t stride,
+                                                 int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t s_begin,
+                                                 uint32_t s_end) {
     const C* __restrict__ leaf_end = ix.M + stab[chrom];
-    uint32_t r_hi = hi;   // ranks >= r_hi are done
-    uint32_t rem = n_hits;
+    uint32_t r_hi = hi, sp = s_end;
     C e0, e1, e2, e3;
-    if ((r_hi & 3u) != 0 && rem != 0) {  // partial top group
+    if ((r_hi & 3u) != 0) {  // partial top group
         const uint32_t g4 = r_hi & ~3u, top = r_hi & 3u;
         load4(leaf_end + g4, e0, e1, e2, e3);
-        if (top > 2 && e2 >= qs && rem != 0) store(--rem, g4 + 2);
-        if (top > 1 && e1 >= qs && rem != 0) store(--rem, g4 + 1);
-        if (e0 >= qs && rem != 0) store(--rem, g4);
+        if (top > 2 && e2 >= qs) { sp -= 4; sts32(sp, g4 + 2); }
+        if (top > 1 && e1 >= qs) { sp -= 4; sts32(sp, g4 + 1); }
+        if (e0 >= qs) { sp -= 4; sts32(sp, g4); }
         r_hi = g4;
     }
-    while (rem != 0 && r_hi != 0) {
-        if ((r_hi & (kFanout - 1)) == 0 && n_levels > 1) {
-            // about to enter leaf node b from its last key: skip it (and, climbing while b is a last child,
-            // whole subtrees) when the max-end augmentation says nothing in there reaches q.start
-            uint32_t b = (r_hi >> kFanoutLog2) - 1;
-            if (ix.M[stab[stride + chrom] + b] < qs) {
-                int l = 1;
-                uint32_t span = kFanout;
-                while (l + 1 < n_levels && (b & (kFanout - 1)) == (kFanout - 1) &&
-                       ix.M[stab[(l + 1) * stride + chrom] + (b >> kFanoutLog2)] < qs) {
-                    b >>= kFanoutLog2;
-                    ++l;
-                    span <<= kFanoutLog2;
-                }
-                r_hi = (span > r_hi) ? 0u : r_hi - span;
+    const bool has_levels = n_levels > 1;
+    while (sp > s_begin && r_hi != 0) {
+        if ((r_hi & (kFanout - 1)) == 0 && has_levels) {
+            const uint32_t span = emit_skip_span<C>(ix, stab, stride, n_levels, chrom, qs, r_hi);
+            if (span) {
+                r_hi -= span;
                 continue;
             }
         }
         const uint32_t g4 = r_hi - 4;
         load4(leaf_end + g4, e0, e1, e2, e3);
-        if (e3 >= qs && rem != 0) store(--rem, g4 + 3);
-        if (e2 >= qs && rem != 0) store(--rem, g4 + 2);
-        if (e1 >= qs && rem != 0) store(--rem, g4 + 1);
-        if (e0 >= qs && rem != 0) store(--rem, g4);
+        if (e3 >= qs) { sp -= 4; sts32(sp, g4 + 3); }
+        if (e2 >= qs) { sp -= 4; sts32(sp, g4 + 2); }
+        if (e1 >= qs) { sp -= 4; sts32(sp, g4 + 1); }
+        if (e0 >= qs) { sp -= 4; sts32(sp, g4); }
+        r_hi = g4;
+    }
+}
+
+// Same walk writing straight to global memory with every store bounds-checked (warp tiles whose hit lists do
+// not fit the stage: very long lists).
+template <typename C>
+__device__ __forceinline__ void emit_walk_global(const IndexView<C>& ix, const uint32_t* __restrict__ stab, uint32_t stride,
+                                                 int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t* __restrict__ dst,
+                                                 uint32_t n_hits) {
+    const C* __restrict__ leaf_end = ix.M + stab[chrom];
+    uint32_t r_hi = hi, rem = n_hits;
+    C e0, e1, e2, e3;
+    if ((r_hi & 3u) != 0 && rem != 0) {
+        const uint32_t g4 = r_hi & ~3u, top = r_hi & 3u;
+        load4(leaf_end + g4, e0, e1, e2, e3);
+        if (top > 2 && e2 >= qs && rem != 0) dst[--rem] = g4 + 2;
+        if (top > 1 && e1 >= qs && rem != 0) dst[--rem] = g4 + 1;
+        if (e0 >= qs && rem != 0) dst[--rem] = g4;
+        r_hi = g4;
+    }
+    while (rem != 0 && r_hi != 0) {
+        if ((r_hi & (kFanout - 1)) == 0 && n_levels > 1) {
+            const uint32_t span = emit_skip_span<C>(ix, stab, stride, n_levels, chrom, qs, r_hi);
+            if (span) {
+                r_hi -= span;
+                continue;
+            }
+        }
+        const uint32_t g4 = r_hi - 4;
+        load4(leaf_end + g4, e0, e1, e2, e3);
+        if (e3 >= qs && rem != 0) dst[--rem] = g4 + 3;
+        if (e2 >= qs && rem != 0) dst[--rem] = g4 + 2;
+        if (e1 >= qs && rem != 0) dst[--rem] = g4 + 1;
+        if (e0 >= qs && rem != 0) dst[--rem] = g4;
         r_hi = g4;
     }
 }
@@ -328,8 +499,9 @@ intersect_emit_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, cons
                       size_t nq, const uint32_t* __restrict__ hi_in, const uint64_t* __restrict__ offsets,
                       uint32_t* __restrict__ hits, uint64_t hits_base) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint32_t* stage = reinterpret_cast<uint32_t*>(smem_raw) + (threadIdx.x >> 5) * kEmitStage;
-    uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + (kQueryThreads / 32) * kEmitStage;
+    constexpr uint32_t kStageWords = kEmitStage + kEmitSlack;
+    uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + (kQueryThreads / 32) * kStageWords;
+    const uint32_t stage_addr = smem_u32(smem_raw) + ((threadIdx.x >> 5) * kStageWords + kEmitSlack) * 4u;
     const uint32_t stride = ix.n_chrom + 1;
     const uint32_t tab_elems = static_cast<uint32_t>(ix.n_levels) * stride;
     for (uint32_t i = threadIdx.x; i < tab_elems; i += blockDim.x) stab[i] = ix.tab[i];
@@ -354,18 +526,17 @@ intersect_emit_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, cons
             hi = hi_in[q];
         }
         if (wtotal <= kEmitStage) {
-            uint32_t* dst = stage + static_cast<uint32_t>(o0 - wbase);
-            if (n_hits != 0)
-                emit_walk<C>(ix, stab, stride, n_levels, chrom, qs, hi, n_hits,
-                             [dst](uint32_t k, uint32_t rank) { dst[k] = rank; });
+            if (n_hits != 0) {
+                const uint32_t s_begin = stage_addr + static_cast<uint32_t>(o0 - wbase) * 4u;
+                emit_walk_staged<C>(ix, stab, stride, n_levels, chrom, qs, hi, s_begin, s_begin + n_hits * 4u);
+            }
             __syncwarp();
-            uint32_t* out = hits + (wbase - hits_base);
-            for (uint32_t i = lane; i < static_cast<uint32_t>(wtotal); i += 32) out[i] = stage[i];
+            uint32_t* out = hits + (wbase - hits_base) + lane;
+            uint32_t sa = stage_addr + lane * 4u;
+            for (uint32_t i = lane; i < static_cast<uint32_t>(wtotal); i += 32, out += 32, sa += 128) *out = lds32(sa);
             __syncwarp();
         } else if (n_hits != 0) {
-            uint32_t* dst = hits + (o0 - hits_base);
-            emit_walk<C>(ix, stab, stride, n_levels, chrom, qs, hi, n_hits,
-                         [dst](uint32_t k, uint32_t rank) { dst[k] = rank; });
+            emit_walk_global<C>(ix, stab, stride, n_levels, chrom, qs, hi, hits + (o0 - hits_base), n_hits);
         }
     }
 }
