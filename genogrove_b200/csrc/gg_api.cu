@@ -73,7 +73,9 @@ struct gg_index {
     int stage_level = 0;
     uint32_t staged_elems = 0;
     uint64_t total_elems = 0;
-    DeviceBuf S, E, M, tab, cnt;
+    DeviceBuf S, E, M, tab, cnt, dirS, dirE, dir_off;
+    int dir_shift = 0;
+    uint64_t dir_entries = 0;
     std::vector<uint64_t> h_cnt;
     std::vector<uint32_t> h_tab;   // [n_levels][n_chrom+1]
     std::vector<uint64_t> h_lvbase;
@@ -106,6 +108,7 @@ struct gg_index {
     int64_t count_threads = kCountThreadsDefault;
     int64_t count_ctas_per_sm = 0;  // 0 = occupancy API
     int64_t emit_ctas_per_sm = 0;
+    int64_t count_mode = 0;  // 0: root directory + bracketed search, 1: tiered tree kernel (TMA windows / warp / per-lane)
 
     gg_batch_stats bstats{};
 };
@@ -147,6 +150,10 @@ IndexView<C> make_view(const gg_index* idx) {
     v.n_levels = idx->n_levels;
     v.stage_level = idx->stage_level;
     v.staged_elems = idx->staged_elems;
+    v.dirS = idx->dirS.as<uint32_t>();
+    v.dirE = idx->dirE.as<uint32_t>();
+    v.dir_off = idx->dir_off.as<uint32_t>();
+    v.dir_shift = idx->dir_shift;
     return v;
 }
 
@@ -165,20 +172,33 @@ template <typename C, typename Q>
 gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, size_t nq,
                        uint64_t* d_off, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, void* scratch,
                        const uint64_t* d_base, cudaStream_t st, cudaEvent_t ev_after_count) {
-    auto kern = intersect_count_kernel<C, Q>;
-    size_t smem = count_smem_bytes(idx);
-    GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    int threads = static_cast<int>(idx->count_threads);
-    int per_sm = static_cast<int>(idx->count_ctas_per_sm);
-    if (per_sm <= 0) {
-        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
-        if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
-    }
-    size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(threads));
     GG_CUDA(scan2_prepare_async(scratch, nq, st));
-    unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
-    kern<<<grid, threads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi,
-                                      scan2_tile_total(scratch), d_err);
+    if (idx->count_mode == 0) {
+        auto kern = intersect_count_dir_kernel<C, Q>;
+        int per_sm = static_cast<int>(idx->count_ctas_per_sm);
+        if (per_sm <= 0) {
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
+            if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
+        }
+        size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads));
+        unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+        kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi,
+                                             scan2_tile_total(scratch), d_err);
+    } else {
+        auto kern = intersect_count_kernel<C, Q>;
+        size_t smem = count_smem_bytes(idx);
+        GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        int threads = static_cast<int>(idx->count_threads);
+        int per_sm = static_cast<int>(idx->count_ctas_per_sm);
+        if (per_sm <= 0) {
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+            if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
+        }
+        size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(threads));
+        unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+        kern<<<grid, threads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi,
+                                          scan2_tile_total(scratch), d_err);
+    }
     GG_CUDA(cudaGetLastError());
     if (ev_after_count) GG_CUDA(cudaEventRecord(ev_after_count, st));
     GG_CUDA(scan2_finish_async(d_cnt, d_off, nq, scratch, d_base, st));
@@ -479,6 +499,51 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     }
     GG_CUDA(cudaGetLastError());
     if (rank_to_input && n) GG_CUDA(cudaMemcpyAsync(rank_to_input, perm, n * 4, cudaMemcpyDeviceToHost, st));
+    {
+        // ---- root directory: per-chromosome max coordinate = max over the (single) top node of M
+        const size_t top_elems = static_cast<size_t>(C) * kFanout;
+        std::vector<uint64_t> top64(top_elems);
+        std::vector<uint32_t> top32(wide ? 0 : top_elems);
+        const size_t top_off = idx->h_tab[static_cast<size_t>(idx->n_levels - 1) * (C + 1)];
+        if (wide)
+            GG_CUDA(cudaMemcpyAsync(top64.data(), idx->M.as<uint64_t>() + top_off, top_elems * 8, cudaMemcpyDeviceToHost, st));
+        else
+            GG_CUDA(cudaMemcpyAsync(top32.data(), idx->M.as<uint32_t>() + top_off, top_elems * 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        std::vector<uint64_t> cmax(C, 0);
+        long double span = 0;
+        for (uint32_t c = 0; c < C; ++c) {
+            for (int j = 0; j < kFanout; ++j) {
+                uint64_t v = wide ? top64[static_cast<size_t>(c) * kFanout + j] : top32[static_cast<size_t>(c) * kFanout + j];
+                cmax[c] = std::max(cmax[c], v);
+            }
+            span += static_cast<long double>(cmax[c]);
+        }
+        // bins of 2^shift positions, ~8 keys per bin on average, at most ~N/8 + 2C entries per family
+        const long double target_bins = std::max<long double>(static_cast<long double>(n) / 8.0L, 1024.0L);
+        int shift = 0;
+        const int max_shift = idx->coord_bytes * 8 - 1;
+        while (shift < max_shift && span / static_cast<long double>(1ull << shift) > target_bins) ++shift;
+        std::vector<uint32_t> h_doff(C + 1, 0);
+        uint64_t entries = 0;
+        for (uint32_t c = 0; c < C; ++c) {
+            h_doff[c] = static_cast<uint32_t>(entries);
+            entries += (cmax[c] >> shift) + 2;
+        }
+        h_doff[C] = static_cast<uint32_t>(entries);
+        if (entries >= 0xFFFFFFF0ull) return fail(idx, GG_ERR_CAPACITY, "root directory too large");
+        idx->dir_shift = shift;
+        idx->dir_entries = entries;
+        GG_CUDA(idx->dirS.ensure(entries * 4));
+        GG_CUDA(idx->dirE.ensure(entries * 4));
+        GG_CUDA(idx->dir_off.ensure((C + 1) * 4));
+        GG_CUDA(cudaMemcpyAsync(idx->dir_off.p, h_doff.data(), (C + 1) * 4, cudaMemcpyHostToDevice, st));
+        if (wide)
+            build_dir_kernel<uint64_t><<<blocks_for(entries, 256), 256, 0, st>>>(make_view<uint64_t>(idx), idx->dirS.as<uint32_t>(), idx->dirE.as<uint32_t>());
+        else
+            build_dir_kernel<uint32_t><<<blocks_for(entries, 256), 256, 0, st>>>(make_view<uint32_t>(idx), idx->dirS.as<uint32_t>(), idx->dirE.as<uint32_t>());
+        GG_CUDA(cudaGetLastError());
+    }
     GG_CUDA(cudaEventRecord(e3, st));
     GG_CUDA(cudaStreamSynchronize(st));
 
@@ -492,7 +557,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     idx->istats.n_levels = idx->n_levels;
     idx->istats.fanout = kFanout;
     idx->istats.staged_levels = idx->n_levels - idx->stage_level;
-    idx->istats.device_bytes = 3 * fam_bytes + idx->h_tab.size() * 4 + static_cast<size_t>(C) * 4;
+    idx->istats.device_bytes = 3 * fam_bytes + idx->h_tab.size() * 4 + static_cast<size_t>(C) * 4 + idx->dir_entries * 8;
     idx->istats.sort_ms = ms_sort;
     idx->istats.levels_ms = ms_levels;
     idx->istats.total_ms = ms_total;
@@ -725,7 +790,7 @@ void gg_index_destroy(gg_index* idx) {
     if (!idx) return;
     cudaSetDevice(idx->device);
     cudaDeviceSynchronize();
-    for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
+    for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base})
         b->release();
     for (auto& s : idx->slots) {
@@ -942,6 +1007,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     } else if (k == "count_threads" && (value == 128 || value == 256 || value == 512 || value == 1024)) idx->count_threads = value;
     else if (k == "count_ctas_per_sm" && value >= 0 && value <= 32) idx->count_ctas_per_sm = value;
     else if (k == "emit_ctas_per_sm" && value >= 0 && value <= 32) idx->emit_ctas_per_sm = value;
+    else if (k == "count_mode" && (value == 0 || value == 1)) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;
     else return fail(idx, GG_ERR_INVALID_ARG, "unknown option or value out of range");
     return GG_OK;

@@ -34,6 +34,12 @@ struct IndexView {
     int n_levels;
     int stage_level;       // levels >= stage_level are staged in shared memory (== n_levels: none)
     uint32_t staged_elems; // number of leading elements of S and E staged (multiple of 32)
+    // root directory (direct-address top level, see build_dir_kernel): for chromosome c and bin b,
+    // dirS[dir_off[c] + b] = #{start < b << dir_shift}, dirE likewise over the sorted ends
+    const uint32_t* dirS;
+    const uint32_t* dirE;
+    const uint32_t* dir_off;  // [n_chrom + 1]; chromosome c has dir_off[c+1] - dir_off[c] - 1 bins
+    int dir_shift;
 };
 
 constexpr int kQueryThreads = 256;
@@ -170,6 +176,101 @@ __device__ __forceinline__ bool warp_upper_bound(const C* __restrict__ g, const 
     }
     result = min(r, n_c);
     return true;
+}
+
+// ---- root directory ---------------------------------------------------------------------------------------
+// The top of the flattened tree for bounded coordinate domains: instead of walking pivot levels from the root,
+// a query key x indexes a direct-address table by x >> dir_shift and gets the two ranks that bracket its
+// answer (bins hold ~8 keys on average), then finishes with a 2-4 step binary search on the leaf level.
+// Built on the device from the leaf levels by the same tree descent it replaces.
+template <typename C>
+__global__ void build_dir_kernel(IndexView<C> ix, uint32_t* __restrict__ dirS, uint32_t* __restrict__ dirE) {
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= ix.dir_off[ix.n_chrom]) return;
+    uint32_t lo = 0, hi = ix.n_chrom;  // chromosome owning directory entry e
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (ix.dir_off[mid] <= e) lo = mid; else hi = mid;
+    }
+    const uint32_t c = lo, b = e - ix.dir_off[c], n_c = ix.cnt[c];
+    uint32_t vs = 0, ve = 0;
+    if (b != 0) {
+        const C top = coord_max<C>::value >> ix.dir_shift;  // largest bin id whose lower edge is representable
+        if (static_cast<C>(b) > top) {
+            vs = ve = n_c;
+        } else {
+            const C x = (static_cast<C>(b) << ix.dir_shift) - 1;  // #{key < b << shift} = ub(key, (b << shift) - 1)
+            const uint32_t stride = ix.n_chrom + 1;
+            vs = tree_upper_bound<C>(ix.S, ix.S, ix.tab, stride, ix.n_levels, ix.n_levels, c, x, n_c);
+            ve = tree_upper_bound<C>(ix.E, ix.E, ix.tab, stride, ix.n_levels, ix.n_levels, c, x, n_c);
+        }
+    }
+    dirS[e] = vs;
+    dirE[e] = ve;
+}
+
+// #keys <= x in the sorted leaf array a, given directory brackets: the answer lies in [lo, hi]
+template <typename C>
+__device__ __forceinline__ uint32_t bracket_upper_bound(const C* __restrict__ a, uint32_t lo, uint32_t hi, C x) {
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (a[mid] <= x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// Pass 1, directory flavour (default): one query per thread, no shared memory, no barriers.
+//   hi = ub(S, q.end), lo = ub(E, q.start - 1), each = directory lookup (2 adjacent u32) + short bracketed binary
+//   search on the leaf level; count = hi - lo.  Coordinate-sorted batches make neighbouring lanes hit the same
+//   directory sector and the same leaf lines (L1); scattered batches cost one L2 access per step.
+template <typename C, typename Q>
+__global__ void __launch_bounds__(kQueryThreads)
+intersect_count_dir_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
+                           const Q* __restrict__ qend, size_t nq, uint32_t* __restrict__ cnt_out,
+                           uint32_t* __restrict__ hi_out, unsigned long long* __restrict__ tile_total,
+                           uint32_t* __restrict__ err_flag) {
+    const size_t n_tiles = (nq + kQueryThreads - 1) / kQueryThreads;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t q = tile * kQueryThreads + threadIdx.x;
+        const bool in_range = q < nq;
+        uint32_t chrom = GG_NO_CHROM_DEV;
+        Q qs_raw = 0, qe_raw = 0;
+        if (in_range) {
+            chrom = qchrom[q];
+            qs_raw = qstart[q];
+            qe_raw = qend[q];
+        }
+        const bool bad = qs_raw > qe_raw;
+        if (bad) atomicOr(err_flag, 1u);
+        const bool ok = in_range && !bad && chrom < ix.n_chrom &&
+                        !(sizeof(Q) > sizeof(C) && qs_raw > static_cast<Q>(coord_max<C>::value));
+        uint32_t cnt = 0, hi = 0;
+        if (ok) {
+            const C qe = clamp_coord<C, Q>(qe_raw);
+            const C qs = static_cast<C>(qs_raw);
+            const uint32_t d0 = ix.dir_off[chrom], last_bin = ix.dir_off[chrom + 1] - d0 - 2;
+            const uint32_t leaf = ix.tab[chrom];
+            const C be = qe >> ix.dir_shift;
+            const uint32_t b1 = be > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(be);
+            hi = bracket_upper_bound<C>(ix.S + leaf, ix.dirS[d0 + b1], ix.dirS[d0 + b1 + 1], qe);
+            uint32_t lo = 0;
+            if (qs > 0) {
+                const C xe = static_cast<C>(qs - 1);
+                const C bs = xe >> ix.dir_shift;
+                const uint32_t b2 = bs > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(bs);
+                lo = bracket_upper_bound<C>(ix.E + leaf, ix.dirE[d0 + b2], ix.dirE[d0 + b2 + 1], xe);
+            }
+            cnt = hi - lo;
+        }
+        if (in_range) {
+            cnt_out[q] = cnt;
+            hi_out[q] = hi;
+        }
+        unsigned long long wsum = cnt;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        if (lane_id() == 0 && wsum != 0) atomicAdd(&tile_total[(tile * kQueryThreads + (threadIdx.x & ~31u)) / kScanTile], wsum);
+    }
 }
 
 // ---- CTA-cooperative search window (coordinate-sorted batches) ------------------------------------------

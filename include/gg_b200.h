@@ -150,8 +150,11 @@ gg_status gg_host_alloc(void** out, size_t bytes);
 void gg_host_free(void* p);
 
 /* ---- tuning knobs (defaults are chosen for B200; used by tests/bench to pin behaviour) ----------- */
-/* key: "chunk_queries" (host pipeline chunk, default 8388608), "stage_bytes" (shared-memory budget for
- * TMA-staged upper levels, default 65536), "count_ctas_per_sm", "emit_ctas_per_sm". */
+/* key: "chunk_queries" (host pipeline chunk, default 8388608); "count_mode" (0 = root directory + bracketed
+ * leaf search [default], 1 = tiered tree kernel: TMA-staged windows / warp bracket / per-lane descent);
+ * for mode 1: "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and
+ * "count_threads" (128..1024); "count_ctas_per_sm", "emit_ctas_per_sm" (0 = occupancy API); "timing" (0/1:
+ * record CUDA events around the kernels of the device-buffer calls for gg_last_batch_stats). */
 gg_status gg_set_option(gg_index* idx, const char* key, int64_t value);
 
 #ifdef __cplusplus

@@ -132,11 +132,13 @@ def test_invalid_query_is_rejected(gg, oracle):
 
 @pytest.mark.parametrize("opt", [("chunk_queries", 4096), ("chunk_queries", 20_000), ("stage_bytes", 0),
                                  ("stage_bytes", 16384), ("stage_bytes", 196608), ("count_threads", 128),
-                                 ("count_threads", 1024)])
+                                 ("count_threads", 1024), ("count_mode", 1), ("count_mode", 0)])
 def test_options_do_not_change_results(gg, oracle, opt):
     rng = np.random.default_rng(31)
     chrom, start, end = random_index(rng, 150_000, 24, span=400_000, nested=True)
     idx = gg.DeviceIndex(0)
+    if opt[0] in ("stage_bytes", "count_threads"):
+        idx.set_option("count_mode", 1)  # these knobs belong to the tiered tree kernel
     idx.set_option(*opt)
     idx.build(chrom, start, end, 24)
     q = random_queries(rng, 100_001, 24, span=400_000)
@@ -147,6 +149,26 @@ def test_options_do_not_change_results(gg, oracle, opt):
     exp_off, exp_hits = oracle_csr(chrom, start, end, 24, *q)
     off, hits = idx.intersect_batch(q[0], q[1].astype(np.uint32), q[2].astype(np.uint32))
     assert np.array_equal(off, exp_off) and np.array_equal(hits, exp_hits)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("wide", [False, True])
+def test_sorted_batches_take_the_bracket_paths(gg, oracle, mode, wide):
+    """Coordinate-sorted batches (the BAM-like case): root directory (mode 0) and TMA window / warp tiers (mode 1)."""
+    rng = np.random.default_rng(61 + mode)
+    chrom, start, end = random_index(rng, 200_000, 3, span=3_000_000, max_len=4000, nested=True, wide=wide)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("count_mode", mode)
+    idx.build(chrom, start, end, 3)
+    qc, qs, qe = random_queries(rng, 150_000, 3, span=3_000_000, max_len=300, wide=wide)
+    order = np.lexsort((qs, qc))
+    qc, qs, qe = qc[order], qs[order], qe[order]
+    qs[:300] = 0  # q.start == 0 edge (no end can be < 0)
+    qe[:300] = np.sort(qe[:300])
+    _check(idx, chrom, start, end, 3, (qc, qs, qe))
+    # dense queries on a tiny span: every tile fits one window; and a stride that breaks windows
+    sub = slice(0, 150_000, 7)
+    _check(idx, chrom, start, end, 3, (qc[sub], qs[sub], qe[sub]))
 
 
 def test_device_buffer_api(gg, oracle):

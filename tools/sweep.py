@@ -18,6 +18,7 @@ ap.add_argument("--threads", default="128,256,512,1024")
 ap.add_argument("--stage", default="0,16384,98304")
 ap.add_argument("--shuffled", action="store_true")
 ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--mode", type=int, default=0)
 args = ap.parse_args()
 
 dev = torch.device("cuda:0")
@@ -25,6 +26,7 @@ c, s, e = synth.hg38_intervals(args.intervals, 42)
 qc, qs, qe = synth.hg38_queries(args.queries, 150, 43, not args.shuffled)
 nq = len(qc)
 idx = DeviceIndex(0)
+idx.set_option("count_mode", args.mode)
 idx.build(c, s, e, 24, want_perm=False)
 d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
 d_s = torch.from_numpy(qs.astype(np.uint32).view(np.int32)).to(dev)
