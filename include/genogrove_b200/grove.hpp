@@ -1,0 +1,575 @@
+// genogrove_b200/grove.hpp — C++20 host facade of the B200 intersect path (header-only, links libgg_b200.so).
+//
+// Mirrors the part of genogrove's public API that sits on the grove<interval, T>::intersect hot path — same
+// names, argument meaning and error behaviour — so that code written against the reference compiles against
+// this header after swapping the namespace aliases:
+//
+//     namespace gdt = genogrove_b200::data_type;   // reference: genogrove::data_type
+//     namespace gst = genogrove_b200::structure;   // reference: genogrove::structure
+//
+// Reference interfaces mirrored (paths relative to the reference checkout):
+//   data_type::interval            include/genogrove/data_type/interval.hpp:54-221
+//   data_type::key<K, D>           include/genogrove/data_type/key.hpp:79-347
+//   data_type::query_result<K, D>  include/genogrove/data_type/query_result.hpp:59-118
+//   structure::sorted / bulk tags  include/genogrove/structure/grove/grove.hpp:56-67
+//   structure::grove<K, D>         include/genogrove/structure/grove/grove.hpp:143-336
+//     grove(int order)             grove.hpp:158-167   (order < 3 -> std::invalid_argument, default 3)
+//     insert_data(...) x4, insert  include/genogrove/structure/grove/grove_insert.ipp:19-43,68-127,160-196
+//     intersect(q) / (q, index)    include/genogrove/structure/grove/grove_query.ipp:16-43
+//     remove_key / compact         include/genogrove/structure/grove/grove_remove.ipp:24-98
+//   plus the NEW batch entry point grove::intersect_batch (millions of queries per call -> CSR).
+//
+// What lives where.  The host owns the keys (std::deque: stable key* identity, like grove.hpp:327) and, per
+// index name, the LEAF-CHAIN ORDER of key pointers — the order search_overlaps appends hits in
+// (query_engine.hpp:83-112).  The device holds a derived snapshot of that order (flattened B+ tree, built and
+// searched by the hand-written sm_100a kernels behind include/gg_b200.h); it is refreshed lazily after any
+// mutation.  Every overlap is computed on the GPU: there is no CPU search path in this header, and a missing
+// device surfaces as genogrove_b200::device_error from the constructor.
+//
+// Leaf-chain order per insert path (the only freedom is the order of keys with EQUAL (start, end)):
+//   insert_data(idx, k, d)               lower_bound insertion  -> equal keys in reverse insertion order
+//   insert_data(idx, vec, sorted, bulk)  input order (empty index: bottom-up build; else rightmost append)
+//   insert_data(idx, vec, bulk)          device radix sort, stable: equal keys keep input order (the reference
+//                                        runs an UNSTABLE std::sort here, grove_insert.ipp:167-168, so it does
+//                                        not define that order itself)
+//   insert_data(idx, k, d, sorted)       lower_bound inside the rightmost leaf, leaf split leaves one key right
+//                                        (grove_insert.ipp:316,501-531); rightmost-leaf bounds are tracked while
+//                                        the history is bulk/sorted-only and approximated by the whole chain
+//                                        after regular inserts or removals (exact whenever keys are distinct)
+#ifndef GENOGROVE_B200_GROVE_HPP
+#define GENOGROVE_B200_GROVE_HPP
+
+#include <algorithm>
+#include <concepts>
+#include <cstddef>
+#include <cstdint>
+#include <deque>
+#include <functional>
+#include <limits>
+#include <memory>
+#include <numeric>
+#include <ranges>
+#include <span>
+#include <stdexcept>
+#include <string>
+#include <string_view>
+#include <type_traits>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+#include "../gg_b200.h"
+
+namespace genogrove_b200 {
+
+/// Any failure of the CUDA library other than an invalid interval (which maps to std::invalid_argument).
+class device_error : public std::runtime_error {
+  public:
+    device_error(int status, const std::string& what) : std::runtime_error(what), status_(status) {}
+    [[nodiscard]] int status() const noexcept { return status_; }
+
+  private:
+    int status_;
+};
+
+namespace data_type {
+
+/// Closed interval [start, end] over size_t coordinates; adjacency counts as overlap.
+class interval {
+  public:
+    static constexpr std::size_t INVALID_POSITION = std::numeric_limits<std::size_t>::max();
+
+    constexpr interval() : start(INVALID_POSITION), end(INVALID_POSITION) {}
+    constexpr interval(std::size_t s, std::size_t e) : start(s), end(e) {
+        if (s > e) throw std::invalid_argument("interval: start must be <= end");
+    }
+
+    constexpr bool operator<(const interval& o) const { return start != o.start ? start < o.start : end < o.end; }
+    constexpr bool operator>(const interval& o) const { return start != o.start ? start > o.start : end > o.end; }
+    constexpr bool operator==(const interval& o) const { return start == o.start && end == o.end; }
+
+    [[nodiscard]] static constexpr bool overlaps(const interval& a, const interval& b) {
+        return (a.start > b.start ? a.start : b.start) <= (a.end < b.end ? a.end : b.end);
+    }
+    [[nodiscard]] static constexpr interval aggregate(const interval& a, const interval& b) {
+        return interval(a.start < b.start ? a.start : b.start, a.end > b.end ? a.end : b.end);
+    }
+
+    [[nodiscard]] std::string to_string() const { return "[" + std::to_string(start) + "," + std::to_string(end) + "]"; }
+    constexpr std::size_t get_start() const noexcept { return start; }
+    constexpr std::size_t get_end() const noexcept { return end; }
+    constexpr void set_range(std::size_t s, std::size_t e) {
+        if (s > e) throw std::invalid_argument("interval: start must be <= end");
+        start = s;
+        end = e;
+    }
+
+  private:
+    std::size_t start;
+    std::size_t end;
+};
+
+namespace detail {
+struct no_data {};
+}  // namespace detail
+
+/// Value + optional payload.  The ADDRESS of a key owned by a grove is its identity in query results.
+template <typename key_t, typename data_t = void>
+class key {
+    using stored_t = std::conditional_t<std::is_void_v<data_t>, detail::no_data, data_t>;
+
+  public:
+    key() requires std::default_initializable<key_t> && std::default_initializable<stored_t> : value{}, data{} {}
+    explicit key(key_t kvalue) requires std::default_initializable<stored_t> : value(std::move(kvalue)), data{} {}
+    template <typename D = data_t>
+    key(key_t kvalue, D&& dvalue) requires(!std::is_void_v<data_t>)
+        : value(std::move(kvalue)), data(std::forward<D>(dvalue)) {}
+
+    [[nodiscard]] const key_t& get_value() const noexcept { return value; }
+    void set_value(key_t v) { value = std::move(v); }
+
+    template <typename D = data_t>
+    [[nodiscard]] const D& get_data() const noexcept requires(!std::is_void_v<data_t>) { return data; }
+    template <typename D = data_t>
+    [[nodiscard]] D& get_data() noexcept requires(!std::is_void_v<data_t>) { return data; }
+    template <typename D = data_t>
+    void set_data(D d) requires(!std::is_void_v<data_t>) { data = std::move(d); }
+    [[nodiscard]] constexpr bool has_data() const noexcept { return !std::is_void_v<data_t>; }
+
+    [[nodiscard]] std::string to_string() const { return value.to_string(); }
+    bool operator<(const key& o) const { return value < o.value; }
+    bool operator>(const key& o) const { return value > o.value; }
+
+  private:
+    key_t value;
+    [[no_unique_address]] stored_t data;
+};
+
+/// Copy of the query + borrowed key pointers in leaf-chain order; does not own the keys.
+template <typename key_t, typename data_t = void>
+class query_result {
+  public:
+    explicit query_result(key_t q) : query(std::move(q)), keys{} {}
+    [[nodiscard]] const key_t& get_query() const noexcept { return query; }
+    [[nodiscard]] const std::vector<key<key_t, data_t>*>& get_keys() const { return keys; }
+    void add_key(key<key_t, data_t>* k) {
+        if (k == nullptr) throw std::invalid_argument("query_result::add_key: key must not be nullptr");
+        keys.push_back(k);
+    }
+    void reserve(std::size_t n) { keys.reserve(n); }
+
+  private:
+    key_t query;
+    std::vector<key<key_t, data_t>*> keys;
+};
+
+}  // namespace data_type
+
+namespace structure {
+
+namespace gdt = genogrove_b200::data_type;
+
+struct string_hash {
+    using is_transparent = void;
+    std::size_t operator()(std::string_view sv) const noexcept { return std::hash<std::string_view>{}(sv); }
+};
+
+struct sorted_t {};
+struct bulk_t {};
+inline constexpr sorted_t sorted{};
+inline constexpr bulk_t bulk{};
+
+/// Result of grove::intersect_batch: CSR over the batch.  Query q's hits are ranks()[offsets()[q] ..
+/// offsets()[q+1]) — leaf-chain ranks inside the query's index, ascending — and key(q, j) maps them back to the
+/// grove's key pointers.  Valid until the grove is mutated, queried again or destroyed (the rank array is the
+/// library's pinned result buffer).
+template <typename key_type, typename data_type>
+class batch_result {
+  public:
+    using key_ptr = gdt::key<key_type, data_type>*;
+
+    [[nodiscard]] std::size_t size() const noexcept { return offsets_.empty() ? 0 : offsets_.size() - 1; }
+    [[nodiscard]] std::uint64_t total_hits() const noexcept { return n_hits_; }
+    [[nodiscard]] const std::vector<std::uint64_t>& offsets() const noexcept { return offsets_; }
+    [[nodiscard]] std::span<const std::uint32_t> ranks() const noexcept { return {hits_, static_cast<std::size_t>(n_hits_)}; }
+    [[nodiscard]] std::span<const std::uint32_t> ranks(std::size_t q) const {
+        return {hits_ + offsets_[q], static_cast<std::size_t>(offsets_[q + 1] - offsets_[q])};
+    }
+    [[nodiscard]] std::size_t count(std::size_t q) const { return static_cast<std::size_t>(offsets_[q + 1] - offsets_[q]); }
+    [[nodiscard]] key_ptr key(std::size_t q, std::size_t j) const {
+        return (*chains_[q_index_[q]])[hits_[offsets_[q] + j]];
+    }
+    /// the reference-shaped view of one query of the batch
+    [[nodiscard]] std::vector<key_ptr> get_keys(std::size_t q) const {
+        std::vector<key_ptr> out;
+        out.reserve(count(q));
+        for (std::size_t j = 0; j < count(q); ++j) out.push_back(key(q, j));
+        return out;
+    }
+
+  private:
+    template <typename, typename, typename>
+    friend class grove;
+    std::vector<std::uint64_t> offsets_;
+    const std::uint32_t* hits_ = nullptr;
+    std::uint64_t n_hits_ = 0;
+    std::vector<std::uint32_t> q_index_;                       // copy of the per-query index ids
+    std::vector<const std::vector<key_ptr>*> chains_;          // index id -> chain (rank -> key*)
+};
+
+template <typename key_type, typename data_type = void, typename edge_data_type = void>
+class grove {
+    static_assert(std::is_same_v<key_type, gdt::interval>,
+                  "genogrove_b200::structure::grove accelerates grove<interval, T> only (SURVEY.md §8)");
+
+  public:
+    using key_t = gdt::key<key_type, data_type>;
+    using key_ptr = key_t*;
+    static constexpr std::uint32_t npos_index = GG_NO_CHROM;
+
+    explicit grove(int order, int device = 0) : order(order) {
+        if (order < 3) throw std::invalid_argument("grove order must be >= 3");
+        gg_index* h = nullptr;
+        gg_status st = gg_index_create(&h, device);
+        if (st != GG_OK) throw device_error(st, "gg_index_create: no usable CUDA device (there is no CPU fallback)");
+        dev.reset(h);
+    }
+    grove() : grove(3) {}
+    ~grove() = default;
+    grove(const grove&) = delete;
+    grove& operator=(const grove&) = delete;
+    grove(grove&&) noexcept = default;
+    grove& operator=(grove&&) noexcept = default;
+
+    [[nodiscard]] int get_order() const { return order; }
+    /// number of keys indexed in the tree (the reference's indexed_vertex_count, grove_graph.ipp:204)
+    [[nodiscard]] std::size_t indexed_vertex_count() const noexcept { return leaf_key_count; }
+    [[nodiscard]] std::size_t size() const noexcept { return leaf_key_count; }
+    [[nodiscard]] std::size_t key_storage_size() const noexcept { return key_storage.size(); }
+    [[nodiscard]] gg_index* device_handle() { sync(); return dev.get(); }
+
+    // ------------------------------------------------------------------------------------------ inserts
+    template <typename D = data_type>
+    key_ptr insert_data(std::string_view index, key_type key_value, D data_value, sorted_t)
+        requires(!std::is_void_v<data_type>) {
+        return insert_sorted(index, allocate_key(key_t(std::move(key_value), std::move(data_value))));
+    }
+    template <typename D = data_type>
+    key_ptr insert_data(std::string_view index, key_type key_value, D data_value) requires(!std::is_void_v<data_type>) {
+        return insert(index, key_t(std::move(key_value), std::move(data_value)));
+    }
+    key_ptr insert_data(std::string_view index, key_type key_value, sorted_t) requires(std::is_void_v<data_type>) {
+        return insert_sorted(index, allocate_key(key_t(std::move(key_value))));
+    }
+    key_ptr insert_data(std::string_view index, key_type key_value) requires(std::is_void_v<data_type>) {
+        return insert(index, key_t(std::move(key_value)));
+    }
+
+    /// regular insert: the chain position is lower_bound over the whole index (node.hpp:247-254 reached by
+    /// top-down routing), so a key lands BEFORE existing equal keys.  Positions are resolved lazily, in one
+    /// merge, before the next query.
+    key_ptr insert(std::string_view index, const key_t& k) {
+        chain_state& ch = chain_for(index);
+        key_ptr p = allocate_key(k);
+        ch.pending.push_back(p);
+        ch.leaf_known = false;
+        ++leaf_key_count;
+        dirty = true;
+        return p;
+    }
+
+    template <typename Container>
+    std::vector<key_ptr> insert_data(std::string_view index, const Container& data, sorted_t, bulk_t)
+        requires(!std::is_void_v<data_type> && std::ranges::forward_range<Container> && std::ranges::sized_range<Container>) {
+        std::vector<key_ptr> inserted;
+        if (std::ranges::empty(data)) return inserted;
+        inserted.reserve(std::ranges::size(data));
+        for (const auto& [key_value, data_value] : data) inserted.push_back(allocate_key(key_t(key_value, data_value)));
+        append_sorted_run(index, inserted, /*device_is_current=*/false);
+        return inserted;
+    }
+
+    /// unsorted bulk: the sort runs on the device (hand-written LSD radix sort of (start, end), stable), then the
+    /// sorted-bulk path.  Returns the key pointers in SORTED order, like the reference does.
+    template <typename Container>
+    std::vector<key_ptr> insert_data(std::string_view index, Container data, bulk_t)
+        requires(!std::is_void_v<data_type> && std::ranges::random_access_range<Container> && std::ranges::sized_range<Container>) {
+        const std::size_t n = std::ranges::size(data);
+        if (n == 0) return {};
+        std::vector<std::uint64_t> s(n), e(n);
+        for (std::size_t i = 0; i < n; ++i) {
+            s[i] = data[i].first.get_start();
+            e[i] = data[i].first.get_end();
+        }
+        const std::vector<std::uint32_t> zeros(n, 0u);
+        std::vector<std::uint32_t> perm(n);
+        const bool was_empty = indices.empty() && all_pending_empty();
+        check(gg_index_build(dev.get(), zeros.data(), s.data(), e.data(), nullptr, GG_TIE_INPUT_ORDER, n, 1, perm.data()));
+        dirty = true;  // the handle now holds a snapshot of this batch alone
+        std::vector<key_ptr> inserted;
+        inserted.reserve(n);
+        for (std::size_t r = 0; r < n; ++r) inserted.push_back(allocate_key(key_t(data[perm[r]].first, data[perm[r]].second)));
+        append_sorted_run(index, inserted, /*device_is_current=*/was_empty);
+        return inserted;
+    }
+
+    // ------------------------------------------------------------------------------------------ removal
+    bool remove_key(std::string_view index_name, key_ptr key_to_remove) {
+        if (key_to_remove == nullptr) return false;
+        auto it = indices.find(index_name);
+        if (it == indices.end()) return false;
+        chain_state& ch = it->second;
+        flush_pending(ch);
+        const key_type& v = key_to_remove->get_value();
+        auto lo = std::lower_bound(ch.chain.begin(), ch.chain.end(), v,
+                                   [](const key_ptr a, const key_type& b) { return a->get_value() < b; });
+        auto pos = ch.chain.end();
+        for (auto p = lo; p != ch.chain.end() && !((*p)->get_value() > v); ++p)
+            if (*p == key_to_remove) { pos = p; break; }
+        if (pos == ch.chain.end()) {  // chains that violate the sorted-append precondition are not globally sorted
+            pos = std::find(ch.chain.begin(), ch.chain.end(), key_to_remove);
+            if (pos == ch.chain.end()) return false;
+        }
+        ch.chain.erase(pos);
+        ch.leaf_known = false;
+        --leaf_key_count;
+        dirty = true;
+        if (ch.chain.empty()) indices.erase(it);  // the reference erases an emptied root (grove_remove.ipp:44-50)
+        return true;
+    }
+
+    /// The reference re-packs its key deque here and invalidates key pointers.  Nothing to reclaim on this side
+    /// beyond dropping unlinked keys' slots lazily; pointers handed out earlier stay valid.
+    void compact() {}
+
+    // ------------------------------------------------------------------------------------------ queries
+    [[nodiscard]] gdt::query_result<key_type, data_type> intersect(const key_type& query) {
+        gdt::query_result<key_type, data_type> result{query};
+        sync();
+        if (indices.empty()) return result;
+        // one query per index, in the host map's iteration order — the order the reference visits its roots in
+        scratch_c.clear();
+        for (const auto& [name, ch] : indices) scratch_c.push_back(ch.id);
+        scratch_s.assign(scratch_c.size(), query.get_start());
+        scratch_e.assign(scratch_c.size(), query.get_end());
+        scratch_off.resize(scratch_c.size() + 1);
+        const std::uint32_t* hits = nullptr;
+        std::uint64_t n_hits = 0;
+        check(gg_intersect_batch(dev.get(), scratch_c.data(), scratch_s.data(), scratch_e.data(), scratch_c.size(),
+                                 scratch_off.data(), &hits, &n_hits));
+        result.reserve(n_hits);
+        for (std::size_t j = 0; j < scratch_c.size(); ++j) {
+            const std::vector<key_ptr>& chain = *chain_by_id[scratch_c[j]];
+            for (std::uint64_t h = scratch_off[j]; h < scratch_off[j + 1]; ++h) result.add_key(chain[hits[h]]);
+        }
+        return result;
+    }
+
+    [[nodiscard]] gdt::query_result<key_type, data_type> intersect(const key_type& query, std::string_view index) {
+        gdt::query_result<key_type, data_type> result{query};
+        auto it = indices.find(index);
+        if (it == indices.end()) return result;  // unknown index: empty result, not an error
+        sync();
+        const std::uint32_t c = it->second.id;
+        const std::uint64_t s = query.get_start(), e = query.get_end();
+        std::uint64_t off[2] = {0, 0};
+        const std::uint32_t* hits = nullptr;
+        std::uint64_t n_hits = 0;
+        check(gg_intersect_batch(dev.get(), &c, &s, &e, 1, off, &hits, &n_hits));
+        result.reserve(n_hits);
+        const std::vector<key_ptr>& chain = it->second.chain;
+        for (std::uint64_t h = 0; h < n_hits; ++h) result.add_key(chain[hits[h]]);
+        return result;
+    }
+
+    /// Id of an index name in the device snapshot, npos_index (== GG_NO_CHROM, "no hits") when absent.  Ids are
+    /// stable while no index is created or emptied.
+    [[nodiscard]] std::uint32_t index_id(std::string_view index) {
+        auto it = indices.find(index);
+        if (it == indices.end()) return npos_index;
+        sync();
+        return it->second.id;
+    }
+
+    /// NEW: millions of queries in one call.  q_index[i] = index_id(name) of query i (npos_index -> no hits),
+    /// closed coordinates like interval; start > end in any query -> std::invalid_argument.
+    [[nodiscard]] batch_result<key_type, data_type> intersect_batch(const std::uint32_t* q_index, const std::uint64_t* q_start,
+                                                                    const std::uint64_t* q_end, std::size_t nq) {
+        sync();
+        batch_result<key_type, data_type> r;
+        r.offsets_.resize(nq + 1);
+        check(gg_intersect_batch(dev.get(), q_index, q_start, q_end, nq, r.offsets_.data(), &r.hits_, &r.n_hits_));
+        r.q_index_.assign(q_index, q_index + nq);
+        r.chains_ = chain_by_id;
+        return r;
+    }
+    [[nodiscard]] batch_result<key_type, data_type> intersect_batch(std::span<const key_type> queries, std::string_view index) {
+        const std::uint32_t c = index_id(index);
+        std::vector<std::uint32_t> qc(queries.size(), c);
+        std::vector<std::uint64_t> qs(queries.size()), qe(queries.size());
+        for (std::size_t i = 0; i < queries.size(); ++i) {
+            qs[i] = queries[i].get_start();
+            qe[i] = queries[i].get_end();
+        }
+        return intersect_batch(qc.data(), qs.data(), qe.data(), queries.size());
+    }
+
+    /// Leaf chain of one index as the device sees it (rank -> key*); empty when the index does not exist.
+    [[nodiscard]] const std::vector<key_ptr>& chain(std::string_view index) {
+        static const std::vector<key_ptr> none;
+        auto it = indices.find(index);
+        if (it == indices.end()) return none;
+        flush_pending(it->second);
+        return it->second.chain;
+    }
+
+  private:
+    struct chain_state {
+        std::vector<key_ptr> chain;    // leaf-chain order
+        std::vector<key_ptr> pending;  // regular inserts not yet merged into the chain, in insertion order
+        std::size_t leaf_begin = 0;    // first rank of the rightmost leaf (sorted-append emulation)
+        bool leaf_known = true;        // false once a path ran whose leaf boundaries are not tracked
+        std::uint32_t id = 0;          // chromosome id in the device snapshot
+    };
+    struct handle_deleter {
+        void operator()(gg_index* h) const noexcept { gg_index_destroy(h); }
+    };
+
+    void check(gg_status st) const {
+        if (st == GG_OK) return;
+        const std::string msg = gg_last_error(dev.get());
+        if (st == GG_ERR_INVALID_INTERVAL) throw std::invalid_argument(msg.empty() ? "interval: start must be <= end" : msg);
+        throw device_error(st, "gg_b200: " + (msg.empty() ? std::string("status ") + std::to_string(st) : msg));
+    }
+
+    key_ptr allocate_key(key_t k) {
+        key_storage.push_back(std::move(k));
+        return &key_storage.back();
+    }
+
+    chain_state& chain_for(std::string_view index) {
+        auto it = indices.find(index);
+        if (it != indices.end()) return it->second;
+        dirty = true;
+        return indices.emplace(std::string(index), chain_state{}).first->second;
+    }
+
+    bool all_pending_empty() const {
+        for (const auto& [n, ch] : indices)
+            if (!ch.pending.empty()) return false;
+        return true;
+    }
+
+    static bool value_less(const key_ptr a, const key_ptr b) { return a->get_value() < b->get_value(); }
+
+    /// Resolve the regular inserts since the last flush.  Sequential lower_bound insertion puts every new key in
+    /// front of all equal keys present at that moment, so the final order is: pending keys by (start, end) with
+    /// LATER insertions first among equals, merged into the chain with pending keys ahead of equal chain keys.
+    void flush_pending(chain_state& ch) {
+        if (ch.pending.empty()) return;
+        std::vector<key_ptr> p(ch.pending.rbegin(), ch.pending.rend());
+        std::stable_sort(p.begin(), p.end(), value_less);
+        std::vector<key_ptr> merged;
+        merged.reserve(ch.chain.size() + p.size());
+        // std::merge is stable with the FIRST range winning ties: pending first
+        std::merge(p.begin(), p.end(), ch.chain.begin(), ch.chain.end(), std::back_inserter(merged), value_less);
+        ch.chain.swap(merged);
+        ch.pending.clear();
+    }
+
+    /// position of a sorted append: lower_bound inside the rightmost leaf (node::insert_key_ptr on it)
+    std::size_t sorted_position(const chain_state& ch, const key_ptr k) const {
+        const std::size_t lo = ch.leaf_known ? ch.leaf_begin : 0;
+        return static_cast<std::size_t>(std::lower_bound(ch.chain.begin() + static_cast<std::ptrdiff_t>(lo), ch.chain.end(), k, value_less) -
+                                        ch.chain.begin());
+    }
+
+    key_ptr insert_sorted(std::string_view index, key_ptr k) {
+        chain_state& ch = chain_for(index);
+        flush_pending(ch);
+        ch.chain.insert(ch.chain.begin() + static_cast<std::ptrdiff_t>(sorted_position(ch, k)), k);
+        if (ch.leaf_known && ch.chain.size() - ch.leaf_begin == static_cast<std::size_t>(order))
+            ch.leaf_begin = ch.chain.size() - 1;  // overflowing rightmost leaf splits leaving one key on the right
+        ++leaf_key_count;
+        dirty = true;
+        return k;
+    }
+
+    /// sorted-bulk: bottom-up build on an empty index (chain = input order, rightmost leaf = last group of the
+    /// even distribution, grove.hpp:100-106), else the rightmost-append loop (grove_insert.ipp:106-126).
+    void append_sorted_run(std::string_view index, const std::vector<key_ptr>& run, bool device_is_current) {
+        const bool fresh_grove = indices.empty();
+        chain_state& ch = chain_for(index);
+        flush_pending(ch);
+        if (ch.chain.empty()) {
+            const std::size_t n = run.size(), cap = static_cast<std::size_t>(order - 1);
+            const std::size_t groups = n / cap + (n % cap != 0 ? 1 : 0);
+            ch.chain = run;
+            ch.leaf_begin = n - n / groups;
+            ch.leaf_known = true;
+        } else {
+            for (key_ptr k : run) {
+                ch.chain.insert(ch.chain.begin() + static_cast<std::ptrdiff_t>(sorted_position(ch, k)), k);
+                if (ch.leaf_known && ch.chain.size() - ch.leaf_begin == static_cast<std::size_t>(order))
+                    ch.leaf_begin = ch.chain.size() - 1;
+            }
+        }
+        leaf_key_count += run.size();
+        dirty = true;
+        if (device_is_current && fresh_grove) {  // the sort that ordered this batch already left its snapshot on the device
+            ch.id = 0;
+            chain_by_id.assign(1, &ch.chain);
+            dirty = false;
+        }
+    }
+
+    /// Re-flatten the host chains into the device snapshot (gg_index_upload_sorted) when anything changed.
+    void sync() {
+        if (!dirty) return;
+        std::size_t n = 0;
+        for (auto& [name, ch] : indices) {
+            flush_pending(ch);
+            n += ch.chain.size();
+        }
+        // ids in name order: deterministic and independent of hash-table history
+        std::vector<std::pair<std::string_view, chain_state*>> order_by_name;
+        order_by_name.reserve(indices.size());
+        for (auto& [name, ch] : indices) order_by_name.emplace_back(name, &ch);
+        std::sort(order_by_name.begin(), order_by_name.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        std::vector<std::uint32_t> c(n);
+        std::vector<std::uint64_t> s(n), e(n);
+        chain_by_id.clear();
+        std::size_t p = 0;
+        std::uint32_t id = 0;
+        for (auto& [name, chp] : order_by_name) {
+            chp->id = id;
+            chain_by_id.push_back(&chp->chain);
+            for (const key_ptr k : chp->chain) {
+                c[p] = id;
+                s[p] = k->get_value().get_start();
+                e[p] = k->get_value().get_end();
+                ++p;
+            }
+            ++id;
+        }
+        check(gg_index_upload_sorted(dev.get(), c.data(), s.data(), e.data(), n, std::max<std::uint32_t>(id, 1u)));
+        dirty = false;
+    }
+
+    int order;
+    std::unique_ptr<gg_index, handle_deleter> dev;
+    /// index name -> chain; same key type, hash and insert/erase history as the reference's root_nodes map
+    /// (grove.hpp:321), hence the same iteration order for intersect(query) across all indices
+    std::unordered_map<std::string, chain_state, string_hash, std::equal_to<>> indices;
+    std::vector<const std::vector<key_ptr>*> chain_by_id;
+    std::deque<key_t> key_storage;
+    std::size_t leaf_key_count = 0;
+    bool dirty = true;
+    std::vector<std::uint32_t> scratch_c;
+    std::vector<std::uint64_t> scratch_s, scratch_e, scratch_off;
+};
+
+}  // namespace structure
+}  // namespace genogrove_b200
+
+#endif  // GENOGROVE_B200_GROVE_HPP
