@@ -4,7 +4,8 @@
 Workload (BASELINE.json configs[3], the configuration the metric is quoted on): a 10M-interval hg38-shaped
 grove (24 chromosomes) and, PER GPU, 100M read-shaped (150 bp) queries, coordinate-sorted per chromosome
 (BAM-like); index replicated on every GPU, query batch sharded (weak scaling: per-GPU work is fixed).
-A step = one pass of the hot path (count -> exclusive scan -> emit) over the rank's 100M-query batch.
+A step = one pass of the hot path over the rank's 100M-query batch: ONE fused kernel (count -> decoupled
+look-back scan -> emit, genogrove_b200/csrc/fused.cuh); --two-phase times the count / scan / emit kernels.
 
   value : whole-job queries/s with queries and results resident in HBM (device-buffer C ABI).
   e2e   : the same metric through the host-buffer C ABI call (gg_intersect_batch, u64 coordinates as the
@@ -34,7 +35,7 @@ UNIT = "queries/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--intervals", type=int, default=10_000_000)
@@ -45,6 +46,10 @@ def parse_args():
     ap.add_argument("--cpu-order", type=int, default=32, help="B+ tree order of the reference grove (3 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--two-phase", action="store_true",
+                    help="time the count -> scan -> emit kernels (two-phase API) instead of the fused kernel")
+    ap.add_argument("--regs40", action="store_true", help="40-register build of the fused kernel")
+    ap.add_argument("--ctas-per-sm", type=int, default=0)
     return ap.parse_args()
 
 
@@ -62,60 +67,57 @@ def workload_config(args, world):
 
 # ----------------------------------------------------------------------------------------- clocks sampler
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Polls NVML (SM clock + clock event reasons) every few ms from a thread while the timed region runs."""
+    REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, period_s: float = 0.004):
         self.samples = []
-        self.proc = None
-        self.gpu_index = gpu_index
+        self.period = period_s
+        self.ok = False
+        self._stop = threading.Event()
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = gpu_index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if gpu_index < len(ids) and ids[gpu_index].isdigit():
+                    phys = int(ids[gpu_index])
+            self.N, self.h = N, N.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = float(N.nvmlDeviceGetMaxClockInfo(self.h, N.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as ex:  # noqa: BLE001
+            self.err = repr(ex)
+
+    def _poll(self):
+        N = self.N
+        while not self._stop.is_set():
+            try:
+                clk = float(N.nvmlDeviceGetClockInfo(self.h, N.NVML_CLOCK_SM))
+                try:
+                    rs = int(N.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:  # noqa: BLE001
+                    rs = int(N.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((time.time(), clk, rs))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu_index)],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+        if self.ok:
+            self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.samples.append((time.time(), line.strip()))
 
     def stop(self, t0, t1):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ts, line in self.samples:
-            if ts < t0 - 0.05 or ts > t1 + 0.05:
-                continue
-            f = [x.strip() for x in line.split(",")]
-            try:
-                sm.append(float(f[0]))
-                mx = float(f[1])
-                for nm, v in zip(names, f[2:6]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
-            except Exception:
-                pass
-        if not sm:  # region shorter than the sampling period: fall back to everything captured
-            for ts, line in self.samples:
-                f = [x.strip() for x in line.split(",")]
-                try:
-                    sm.append(float(f[0]))
-                    mx = float(f[1])
-                except Exception:
-                    pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "err", "?")]}
+        self._stop.set()
+        self.t.join(timeout=2)
+        inside = [(c, r) for ts, c, r in self.samples if t0 <= ts <= t1] or [(c, r) for _, c, r in self.samples]
+        reasons = sorted(nm for nm, bit in self.REASONS.items() if any(r & bit for _, r in inside))
+        return {"sm_mhz": float(np.median([c for c, _ in inside])) if inside else None, "sm_max_mhz": self.max_sm,
+                "reasons": reasons, "samples": len(inside)}
 
 
 # ----------------------------------------------------------------------------------------- reference arm
@@ -203,25 +205,39 @@ def main():
     d_e = torch.from_numpy(qe.astype(np.uint32).view(np.int32)).to(dev)
     d_off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
+    # sizing pass (untimed): a real caller sizes the hit buffer from the previous batch
     total = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), stream, sync_total=True)
     d_hits = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
     d_tot = torch.zeros(1, dtype=torch.int64, device=dev)
     d_all = torch.zeros(world, dtype=torch.int64, device=dev)
+    fused = not args.two_phase
+    if args.regs40:
+        idx.set_option("fused_regs40", 1)
+    if args.ctas_per_sm:
+        idx.set_option("fused_ctas_per_sm", args.ctas_per_sm)
+    idx.set_option("timing", 1)  # library CUDA events around its kernels, on the launching stream
+    kms = {"count": [], "scan": [], "emit": [], "fused": []}
 
-    def step(ev=None):
-        # pass 1 + scan; the host needs the hit total to size the output (a real caller allocates here)
-        if ev:
-            ev[0].record()
-        t = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), stream, sync_total=True)
-        assert t <= d_hits.numel()
-        if ev:
-            ev[1].record()
-        idx.emit_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(), stream)
-        if ev:
-            ev[2].record()
+    def step(record=False):
+        if fused:
+            # ONE kernel: count -> look-back scan -> emit; the host reads the hit total (8 B) after it
+            t = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(),
+                                 d_hits.data_ptr(), d_hits.numel(), stream, sync_total=True)
+        else:
+            # pass 1 + scan; the host needs the hit total to size the output (a real caller allocates here)
+            t = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), stream, sync_total=True)
+            assert t <= d_hits.numel()
+            idx.emit_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(), stream)
         if world > 1:  # the path's only collective: gather hit totals -> global CSR base
             d_tot.copy_(d_off[nq:nq + 1])
             dist.all_gather_into_tensor(d_all, d_tot)
+        if record:
+            torch.cuda.current_stream().synchronize()
+            bs = idx.batch_stats()
+            if fused:
+                kms["fused"].append(bs.emit_ms)
+            else:
+                kms["count"].append(bs.count_ms), kms["scan"].append(bs.scan_ms), kms["emit"].append(bs.emit_ms)
         return t
 
     def barrier():
@@ -234,14 +250,13 @@ def main():
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    time.sleep(0.25)
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    time.sleep(0.05)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t_wall0 = time.time()
     e0.record()
     for k in range(args.steps):
-        step(evs[k])
+        step(record=True)
     e1.record()
     barrier()
     t_wall1 = time.time()
@@ -251,18 +266,8 @@ def main():
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
     ms_per_step = float(t_ms.item()) / args.steps
-    count_scan_ms = float(np.mean([ev[0].elapsed_time(ev[1]) for ev in evs]))
-    emit_ms = float(np.mean([ev[1].elapsed_time(ev[2]) for ev in evs]))
-
-    # count vs scan split (library CUDA events on the same stream), outside the timed region
-    idx.set_option("timing", 1)
-    step()
-    torch.cuda.synchronize()
-    bs = idx.batch_stats()
     idx.set_option("timing", 0)
-    scan_share = bs.scan_ms / max(bs.count_ms + bs.scan_ms, 1e-9)
-    count_ms = count_scan_ms * (1 - scan_share)
-    scan_ms = count_scan_ms * scan_share
+    kernel_ms = {k: float(np.mean(v)) for k, v in kms.items() if v}
 
     totals = torch.tensor([total, nq], dtype=torch.int64, device=dev)
     if world > 1:
@@ -278,18 +283,30 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    bytes_count = 12 * nq + 8 * nq            # read (chrom,start,end) u32, write count u32 + hi u32
-    bytes_emit = 4 * total + 8 * (nq + 1) + 12 * nq  # write ranks, read offsets, chrom/start/hi
-    bytes_path = 12 * nq + 8 * (nq + 1) + 4 * total  # B_q
-    if emit_ms >= count_ms:
-        dom, dom_ms, dom_bytes = "intersect_emit_kernel", emit_ms, bytes_emit
+    bytes_path = 12 * nq + 8 * (nq + 1) + 4 * total  # B_q = read (chrom,start,end) u32, write offsets u64, ranks u32
+    if fused:
+        dom, dom_ms, dom_bytes = "intersect_fused_kernel", kernel_ms["fused"], bytes_path
+        launches_per_step = 1
     else:
-        dom, dom_ms, dom_bytes = "intersect_count_kernel", count_ms, bytes_count
+        bytes_count = 12 * nq + 8 * nq                   # read (chrom,start,end) u32, write count u32 + hi u32
+        bytes_emit = 4 * total + 8 * (nq + 1) + 12 * nq  # write ranks, read offsets, chrom/start/hi
+        if kernel_ms["emit"] >= kernel_ms["count"]:
+            dom, dom_ms, dom_bytes = "intersect_emit_kernel", kernel_ms["emit"], bytes_emit
+        else:
+            dom, dom_ms, dom_bytes = "intersect_count_dir_kernel", kernel_ms["count"], bytes_count
+        launches_per_step = 4
+    traffic = None
+    try:  # per-launch DRAM bytes of that kernel from the committed ncu --set full capture of this same command
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        key = dom + ("" if not args.shuffled else ":shuffled")
+        if key in tj and tj[key].get("queries") == nq:
+            traffic = tj[key]["dram_bytes_per_launch"]
+    except Exception:
+        pass
     achieved = dom_bytes / (dom_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
-                "algorithmic_bytes_per_launch": dom_bytes,
-                "kernel_ms": {"count": count_ms, "scan": scan_ms, "emit": emit_ms},
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_kind,
+                "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kernel_ms,
                 "path_achieved_gbs": bytes_path / (ms_per_step / 1e3) / 1e9,
                 "path_frac": bytes_path / (ms_per_step / 1e3) / 1e9 / peak}
 
@@ -338,7 +355,7 @@ def main():
                "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
                "config": workload_config(args, world), "hit_pairs_per_sec": job_hits / (ms_per_step / 1e3),
-               "hits_per_query": job_hits / job_q, "gpu_launches": 4 * args.steps, "clocks": clocks,
+               "hits_per_query": job_hits / job_q, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                "index": {"levels": ist.n_levels, "fanout": ist.fanout, "staged_levels": ist.staged_levels,
                          "coord_bytes": ist.coord_bytes, "device_mb": ist.device_bytes / 1e6,

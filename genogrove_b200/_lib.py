@@ -31,7 +31,7 @@ EXPORTS = (
     "gg_version", "gg_device_count", "gg_index_create", "gg_index_destroy", "gg_last_error",
     "gg_index_build", "gg_index_upload_sorted", "gg_index_get_stats", "gg_index_chrom_counts",
     "gg_intersect_batch", "gg_intersect_batch_u32", "gg_intersect_count", "gg_intersect_emit",
-    "gg_intersect_count_device", "gg_intersect_emit_device", "gg_last_batch_stats",
+    "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_last_batch_stats",
     "gg_host_alloc", "gg_host_free", "gg_set_option",
 )
 
@@ -92,6 +92,7 @@ def lib():
     L.gg_intersect_emit.argtypes = [vp, vp, C.c_uint64]
     L.gg_intersect_count_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, _u64p, vp]
     L.gg_intersect_emit_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, vp]
+    L.gg_intersect_fused_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_uint64, _u64p, vp]
     L.gg_last_batch_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.gg_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.gg_host_free.argtypes = [vp]

@@ -13,6 +13,7 @@
 
 #include "build.cuh"
 #include "common.cuh"
+#include "fused.cuh"
 #include "intersect.cuh"
 #include "radix_sort.cuh"
 #include "scan.cuh"
@@ -50,7 +51,8 @@ struct DeviceBuf {
 
 struct Slot {
     cudaStream_t st = nullptr;
-    DeviceBuf qc, qs, qe, cnt, hi, off, hits, scan;
+    DeviceBuf qc, qs, qe, cnt, hi, off, hits, scan, fscratch, err;
+    uint64_t launch_cap = 0;  // hit capacity the fused kernel of the current chunk was launched with
     cudaEvent_t ev_scan = nullptr, ev_total = nullptr, ev_done = nullptr;
     uint64_t* h_next_base = nullptr;  // pinned
     bool busy = false;
@@ -82,7 +84,7 @@ struct gg_index {
     gg_index_stats istats{};
 
     // ---- device-API scratch
-    DeviceBuf q_cnt, q_hi, scan_scratch, err_flag;
+    DeviceBuf q_cnt, q_hi, scan_scratch, err_flag, fused_scratch, fused_out;
     size_t counted_nq = 0;
     bool timing = false;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -108,6 +110,9 @@ struct gg_index {
     int64_t count_threads = kCountThreadsDefault;
     int64_t count_ctas_per_sm = 0;  // 0 = occupancy API
     int64_t emit_ctas_per_sm = 0;
+    int64_t fused_ctas_per_sm = 0;
+    int64_t fused_regs40 = 0;  // 1: the 40-register build of the fused kernel (6 CTAs/SM) instead of 32 registers (8 CTAs/SM)
+    int64_t host_mode = 0;   // host-buffer pipeline: 0 = one fused kernel per chunk, 1 = count -> scan -> emit kernels
     int64_t count_mode = 0;  // 0: root directory + bracketed search, 1: tiered tree kernel (TMA windows / warp / per-lane)
 
     gg_batch_stats bstats{};
@@ -250,6 +255,51 @@ gg_status dispatch_emit(gg_index* idx, const uint32_t* d_chrom, const void* d_st
     if (idx->coord_bytes == 8 && q_bytes == 4)
         return launch_emit<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
     return launch_emit<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+}
+
+// The one-kernel path (fused.cuh): scratch = [ticket][tile state], zeroed per launch.
+size_t fused_smem_bytes(const gg_index* idx, bool* tab_in_smem) {
+    size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
+    *tab_in_smem = tab_bytes <= 8 * 1024;  // many-contig groves read the offset table through L1 instead
+    return static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kFusedSlack) * 4 + (*tab_in_smem ? tab_bytes : 0) + 16;
+}
+
+template <typename C, typename Q>
+gg_status launch_fused(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, size_t nq,
+                       uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, const uint64_t* d_base,
+                       uint64_t* d_next_base, uint64_t* d_total, void* scratch, uint32_t* d_err, cudaStream_t st) {
+    auto kern = idx->fused_regs40 ? intersect_fused_kernel<C, Q, 6> : intersect_fused_kernel<C, Q, 8>;
+    bool tab_in_smem = true;
+    const size_t smem = fused_smem_bytes(idx, &tab_in_smem);
+    if (smem > 48 * 1024)
+        GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int per_sm = static_cast<int>(idx->fused_ctas_per_sm);
+    if (per_sm <= 0) {
+        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+        if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "fused kernel does not fit on an SM");
+    }
+    GG_CUDA(cudaMemsetAsync(scratch, 0, fused_scratch_bytes(nq), st));
+    const size_t tiles = fused_tiles(nq);
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+    uint32_t* ticket = static_cast<uint32_t*>(scratch);
+    uint64_t* state = reinterpret_cast<uint64_t*>(static_cast<char*>(scratch) + 16);
+    kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_off, d_hits, capacity, d_base,
+                                            d_next_base, d_total, ticket, state, d_err, tab_in_smem ? 1 : 0);
+    GG_CUDA(cudaGetLastError());
+    idx->bstats.kernel_launches++;
+    return GG_OK;
+}
+
+gg_status dispatch_fused(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, int q_bytes,
+                         size_t nq, uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, const uint64_t* d_base,
+                         uint64_t* d_next_base, uint64_t* d_total, void* scratch, uint32_t* d_err, cudaStream_t st) {
+    if (idx->coord_bytes == 4 && q_bytes == 4)
+        return launch_fused<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
+    if (idx->coord_bytes == 4 && q_bytes == 8)
+        return launch_fused<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
+    if (idx->coord_bytes == 8 && q_bytes == 4)
+        return launch_fused<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
+    return launch_fused<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
 }
 
 // ------------------------------------------------------------------------------------------ build
@@ -717,19 +767,92 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
         return GG_OK;
     };
 
+    // ---- one fused kernel per chunk (default): the hit capacity of a chunk is an estimate from the chunks before
+    // it; a chunk that overflows is re-run with the exact size (offsets are complete either way).
+    bool any_invalid = false;
+    double est_per_q = 8.0;
+    auto fstage_a = [&](size_t k) -> gg_status {
+        Slot& sl = idx->slots[k % kSlots];
+        if (sl.busy) {
+            GG_CUDA(cudaEventSynchronize(sl.ev_done));
+            sl.busy = false;
+        }
+        const size_t q0 = k * chunk, m = std::min(chunk, nq - q0);
+        GG_CUDA(sl.qc.ensure(m * 4));
+        GG_CUDA(sl.qs.ensure(m * sizeof(Q)));
+        GG_CUDA(sl.qe.ensure(m * sizeof(Q)));
+        GG_CUDA(sl.off.ensure((m + 1) * 8));
+        GG_CUDA(sl.fscratch.ensure(fused_scratch_bytes(m)));
+        GG_CUDA(sl.err.ensure(16));
+        const size_t want = static_cast<size_t>(est_per_q * 1.25 * static_cast<double>(m)) + 4096;
+        if (sl.hits.cap / 4 < want) GG_CUDA(sl.hits.ensure(want * 4));
+        sl.launch_cap = sl.hits.cap / 4;
+        GG_CUDA(cudaMemcpyAsync(sl.qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qs.p, q_start + q0, m * sizeof(Q), cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qe.p, q_end + q0, m * sizeof(Q), cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemsetAsync(sl.err.p, 0, 4, sl.st));
+        if (prev_scan) GG_CUDA(cudaStreamWaitEvent(sl.st, prev_scan, 0));  // d_base[k] is written by chunk k-1's kernel
+        uint64_t* d_base = idx->d_base.as<uint64_t>();
+        gg_status r = dispatch_fused(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, sizeof(Q), m, sl.off.as<uint64_t>(),
+                                     sl.hits.as<uint32_t>(), sl.launch_cap, d_base + k, d_base + k + 1, nullptr,
+                                     sl.fscratch.p, sl.err.as<uint32_t>(), sl.st);
+        if (r != GG_OK) return r;
+        GG_CUDA(cudaEventRecord(sl.ev_scan, sl.st));
+        prev_scan = sl.ev_scan;
+        GG_CUDA(cudaMemcpyAsync(sl.h_next_base, d_base + k + 1, 8, cudaMemcpyDeviceToHost, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.h_next_base + 1, sl.err.p, 4, cudaMemcpyDeviceToHost, sl.st));
+        GG_CUDA(cudaEventRecord(sl.ev_total, sl.st));
+        const size_t n_off = (k + 1 == n_chunks) ? m + 1 : m;
+        GG_CUDA(cudaMemcpyAsync(offsets + q0, sl.off.p, n_off * 8, cudaMemcpyDeviceToHost, sl.st));
+        sl.busy = true;
+        return GG_OK;
+    };
+    auto fstage_b = [&](size_t k) -> gg_status {
+        Slot& sl = idx->slots[k % kSlots];
+        const size_t q0 = k * chunk, m = std::min(chunk, nq - q0);
+        GG_CUDA(cudaEventSynchronize(sl.ev_total));
+        base[k + 1] = sl.h_next_base[0];
+        if (static_cast<uint32_t>(sl.h_next_base[1]) & 1u) any_invalid = true;
+        const uint64_t total = base[k + 1] - base[k];
+        est_per_q = std::max(1.0, static_cast<double>(base[k + 1]) / static_cast<double>(q0 + m));
+        if (total) {
+            if (total > sl.launch_cap) {  // estimate too small: exact re-run of this chunk (same base, same offsets)
+                GG_CUDA(cudaStreamSynchronize(sl.st));
+                GG_CUDA(sl.hits.ensure(total * 4));
+                sl.launch_cap = sl.hits.cap / 4;
+                gg_status r = dispatch_fused(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, sizeof(Q), m, sl.off.as<uint64_t>(),
+                                             sl.hits.as<uint32_t>(), sl.launch_cap, idx->d_base.as<uint64_t>() + k, nullptr,
+                                             nullptr, sl.fscratch.p, sl.err.as<uint32_t>(), sl.st);
+                if (r != GG_OK) return r;
+            }
+            if (base[k + 1] > idx->pinned_cap) {
+                for (int i = 0; i < kSlots; ++i)
+                    if (i != static_cast<int>(k % kSlots) && idx->slots[i].busy) GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
+                GG_CUDA(cudaStreamSynchronize(sl.st));
+                size_t est = static_cast<size_t>(est_per_q * 1.15 * static_cast<double>(nq)) + 4096;
+                gg_status r = ensure_pinned_hits(idx, std::max<size_t>(est, base[k + 1]), base[k]);
+                if (r != GG_OK) return r;
+            }
+            GG_CUDA(cudaMemcpyAsync(idx->pinned_hits + base[k], sl.hits.p, total * 4, cudaMemcpyDeviceToHost, sl.st));
+        }
+        GG_CUDA(cudaEventRecord(sl.ev_done, sl.st));
+        return GG_OK;
+    };
+    const bool fused_mode = idx->host_mode == 0;
+
     // software pipeline: A(0) A(1) B(0) A(2) B(1) ...
     const size_t lead = std::min<size_t>(kSlots - 1, n_chunks);
     for (size_t k = 0; k < lead; ++k) {
-        s = stage_a(k);
+        s = fused_mode ? fstage_a(k) : stage_a(k);
         if (s != GG_OK) return s;
     }
     for (size_t k = 0; k < n_chunks; ++k) {
         if (k + lead < n_chunks) {
             // the slot of chunk k+lead was last used by chunk k+lead-kSlots = k-1: done by now or waited in stage_a
-            s = stage_a(k + lead);
+            s = fused_mode ? fstage_a(k + lead) : stage_a(k + lead);
             if (s != GG_OK) return s;
         }
-        s = stage_b(k);
+        s = fused_mode ? fstage_b(k) : stage_b(k);
         if (s != GG_OK) return s;
     }
     for (int i = 0; i < kSlots; ++i) {
@@ -738,6 +861,7 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
     }
     s = check_query_error(idx, st0);
     if (s != GG_OK) return s;
+    if (any_invalid) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
     if (!idx->pinned_hits) {
         s = ensure_pinned_hits(idx, 1, 0);
         if (s != GG_OK) return s;
@@ -790,11 +914,11 @@ void gg_index_destroy(gg_index* idx) {
     if (!idx) return;
     cudaSetDevice(idx->device);
     cudaDeviceSynchronize();
-    for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
+    for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base})
         b->release();
     for (auto& s : idx->slots) {
-        for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan}) b->release();
+        for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan, &s.fscratch, &s.err}) b->release();
         if (s.st) cudaStreamDestroy(s.st);
         if (s.ev_scan) cudaEventDestroy(s.ev_scan);
         if (s.ev_total) cudaEventDestroy(s.ev_total);
@@ -906,6 +1030,47 @@ gg_status gg_intersect_emit_device(gg_index* idx, const uint32_t* d_chrom, const
     return GG_OK;
 }
 
+gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                    int coord_bytes, size_t nq, uint64_t* d_offsets, uint32_t* d_hits,
+                                    uint64_t capacity, uint64_t* total_hits, void* stream) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!d_offsets || (capacity && !d_hits) || (nq && (!d_chrom || !d_start || !d_end)))
+        return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
+    if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    GG_CUDA(idx->fused_scratch.ensure(fused_scratch_bytes(nq)));
+    GG_CUDA(idx->fused_out.ensure(16));
+    GG_CUDA(idx->err_flag.ensure(16));
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+    idx->bstats.n_chunks = 1;
+    idx->ev_count_valid = idx->ev_emit_valid = false;
+    idx->counted_nq = 0;  // the two-phase emit needs its own count pass
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[3], st));
+    gg_status s = dispatch_fused(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_offsets, d_hits, capacity, nullptr, nullptr,
+                                 idx->fused_out.as<uint64_t>(), idx->fused_scratch.p, idx->err_flag.as<uint32_t>(), st);
+    if (s != GG_OK) return s;
+    if (idx->timing) {
+        GG_CUDA(cudaEventRecord(idx->ev[4], st));
+        idx->ev_emit_valid = true;
+    }
+    if (total_hits) {
+        uint32_t flag = 0;
+        GG_CUDA(cudaMemcpyAsync(total_hits, idx->fused_out.p, 8, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        idx->bstats.n_hits = *total_hits;
+        if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+        if (flag & 2u) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
+    }
+    return GG_OK;
+}
+
 gg_status gg_intersect_count(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
                              size_t nq, uint64_t* offsets) {
     if (!idx) return GG_ERR_INVALID_ARG;
@@ -1007,6 +1172,9 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     } else if (k == "count_threads" && (value == 128 || value == 256 || value == 512 || value == 1024)) idx->count_threads = value;
     else if (k == "count_ctas_per_sm" && value >= 0 && value <= 32) idx->count_ctas_per_sm = value;
     else if (k == "emit_ctas_per_sm" && value >= 0 && value <= 32) idx->emit_ctas_per_sm = value;
+    else if (k == "fused_ctas_per_sm" && value >= 0 && value <= 32) idx->fused_ctas_per_sm = value;
+    else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
+    else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && (value == 0 || value == 1)) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;
     else return fail(idx, GG_ERR_INVALID_ARG, "unknown option or value out of range");

@@ -16,6 +16,8 @@
  *   gg_index_upload_sorted    <- the leaf chain left by insert / insert_sorted / remove_key / compact
  *                                grove_insert.ipp:182-274, 501-531; grove_remove.ipp:24-98
  *   gg_intersect_*            <- grove::intersect(query, index) -> detail::search_overlaps
+ *   (batch, fused_device,        [the host-buffer batch call and gg_intersect_fused_device run ONE fused kernel;
+ *    count/emit[_device])         count/emit are the two-phase form for callers that size the output first]
  *                                include/genogrove/structure/grove/grove_query.ipp:33-43
  *                                include/genogrove/structure/grove/query_engine.hpp:76-134
  *                                with query_result::add_key (data_type/query_result.hpp:108-113)
@@ -143,6 +145,15 @@ gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, cons
 gg_status gg_intersect_emit_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
                                    const void* d_end, int coord_bytes, size_t nq, const uint64_t* d_offsets,
                                    uint32_t* d_hits, void* stream);
+/* One-kernel variant (count -> decoupled look-back scan -> emit fused; every query read once, every offset and
+ * hit written once).  d_hits has room for `capacity` ranks — the caller's estimate, e.g. from the previous
+ * batch.  d_offsets[0..nq] is always complete; ranks that would land at or beyond `capacity` are not written.
+ * With total_hits (host pointer) the call waits, stores offsets[nq] and returns GG_ERR_CAPACITY when the
+ * batch produced more than `capacity` hits (re-run with a buffer of *total_hits ranks).  Without it the call
+ * only enqueues; compare d_offsets[nq] with the capacity yourself. */
+gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
+                                    const void* d_end, int coord_bytes, size_t nq, uint64_t* d_offsets,
+                                    uint32_t* d_hits, uint64_t capacity, uint64_t* total_hits, void* stream);
 gg_status gg_last_batch_stats(const gg_index* idx, gg_batch_stats* out);
 
 /* ---- pinned host memory helpers ------------------------------------------------------------------ */
@@ -150,7 +161,8 @@ gg_status gg_host_alloc(void** out, size_t bytes);
 void gg_host_free(void* p);
 
 /* ---- tuning knobs (defaults are chosen for B200; used by tests/bench to pin behaviour) ----------- */
-/* key: "chunk_queries" (host pipeline chunk, default 8388608); "count_mode" (0 = root directory + bracketed
+/* key: "chunk_queries" (host pipeline chunk, default 8388608); "host_mode" (host-buffer calls: 0 = one fused
+ * kernel per chunk [default], 1 = count -> scan -> emit kernels); "fused_ctas_per_sm"; "count_mode" (0 = root directory + bracketed
  * leaf search [default], 1 = tiered tree kernel: TMA-staged windows / warp bracket / per-lane descent);
  * for mode 1: "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and
  * "count_threads" (128..1024); "count_ctas_per_sm", "emit_ctas_per_sm" (0 = occupancy API); "timing" (0/1:

@@ -132,13 +132,16 @@ def test_invalid_query_is_rejected(gg, oracle):
 
 @pytest.mark.parametrize("opt", [("chunk_queries", 4096), ("chunk_queries", 20_000), ("stage_bytes", 0),
                                  ("stage_bytes", 16384), ("stage_bytes", 196608), ("count_threads", 128),
-                                 ("count_threads", 1024), ("count_mode", 1), ("count_mode", 0)])
+                                 ("count_threads", 1024), ("count_mode", 1), ("count_mode", 0), ("host_mode", 1),
+                                 ("host_mode", 0), ("fused_regs40", 1), ("fused_ctas_per_sm", 1)])
 def test_options_do_not_change_results(gg, oracle, opt):
     rng = np.random.default_rng(31)
     chrom, start, end = random_index(rng, 150_000, 24, span=400_000, nested=True)
     idx = gg.DeviceIndex(0)
+    if opt[0] in ("stage_bytes", "count_threads", "count_mode"):
+        idx.set_option("host_mode", 1)  # these knobs belong to the count -> scan -> emit kernels
     if opt[0] in ("stage_bytes", "count_threads"):
-        idx.set_option("count_mode", 1)  # these knobs belong to the tiered tree kernel
+        idx.set_option("count_mode", 1)  # ... and these to the tiered tree kernel
     idx.set_option(*opt)
     idx.build(chrom, start, end, 24)
     q = random_queries(rng, 100_001, 24, span=400_000)
@@ -159,6 +162,7 @@ def test_sorted_batches_take_the_bracket_paths(gg, oracle, mode, wide):
     chrom, start, end = random_index(rng, 200_000, 3, span=3_000_000, max_len=4000, nested=True, wide=wide)
     idx = gg.DeviceIndex(0)
     idx.set_option("count_mode", mode)
+    idx.set_option("host_mode", 1)
     idx.build(chrom, start, end, 3)
     qc, qs, qe = random_queries(rng, 150_000, 3, span=3_000_000, max_len=300, wide=wide)
     order = np.lexsort((qs, qc))
@@ -198,6 +202,96 @@ def test_device_buffer_api(gg, oracle):
         assert np.array_equal(d_hits.cpu().numpy().view(np.uint32)[:total], exp_hits)
         bs = idx.batch_stats()
         assert bs.count_ms > 0 and bs.emit_ms > 0 and bs.kernel_launches == 4
+
+
+def test_fused_device_api_and_capacity(gg, oracle):
+    """gg_intersect_fused_device: one kernel; exact capacity, generous capacity, and a too-small buffer
+    (GG_ERR_CAPACITY with complete offsets and nothing written at or beyond the capacity)."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(43)
+    chrom, start, end = random_index(rng, 80_000, 24, span=300_000, nested=True)
+    idx = gg.DeviceIndex(0)
+    idx.build(chrom, start, end, 24)
+    qc, qs, qe = random_queries(rng, 200_003, 24, span=300_000, extra_chrom=1)
+    order = np.lexsort((qs, qc))  # half sorted, half shuffled
+    h = len(qc) // 2
+    qc[:h], qs[:h], qe[:h] = qc[order][:h], qs[order][:h], qe[order][:h]
+    exp_off, exp_hits = oracle_csr(chrom, start, end, 24, qc, qs, qe)
+    total = int(exp_off[-1])
+    dev = torch.device("cuda:0")
+    stream = torch.cuda.current_stream().cuda_stream
+    for dt, nb in ((np.uint32, 4), (np.uint64, 8)):
+        d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
+        d_s = torch.from_numpy(qs.astype(dt).view(np.int32 if nb == 4 else np.int64)).to(dev)
+        d_e = torch.from_numpy(qe.astype(dt).view(np.int32 if nb == 4 else np.int64)).to(dev)
+        for cap in (total, total + 12345):
+            d_off = torch.zeros(len(qc) + 1, dtype=torch.int64, device=dev)
+            d_hits = torch.full((cap + 64,), -1, dtype=torch.int32, device=dev)
+            got = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
+                                   d_hits.data_ptr(), cap, stream, sync_total=True)
+            assert got == total
+            assert idx.batch_stats().kernel_launches == 1
+            assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
+            h_hits = d_hits.cpu().numpy()
+            assert np.array_equal(h_hits.view(np.uint32)[:total], exp_hits)
+            assert (h_hits[total:] == -1).all()
+        # too small: offsets complete, ranks below the capacity either correct or untouched, nothing beyond it
+        cap = total // 3
+        d_off = torch.zeros(len(qc) + 1, dtype=torch.int64, device=dev)
+        d_hits = torch.full((total + 64,), -1, dtype=torch.int32, device=dev)
+        with pytest.raises(gg.GGError) as ei:
+            idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
+                             d_hits.data_ptr(), cap, stream, sync_total=True)
+        assert ei.value.status == 7 and idx.last_total == total
+        assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
+        h_hits = d_hits.cpu().numpy()
+        assert (h_hits[cap:] == -1).all()
+        written = h_hits[:cap] != -1
+        assert written.sum() > 0.9 * cap
+        assert np.array_equal(h_hits[:cap][written].view(np.uint32), exp_hits[:cap][written])
+    # enqueue-only form on a side stream, two batches back to back on one handle
+    s2 = torch.cuda.Stream()
+    with torch.cuda.stream(s2):
+        d_off = torch.zeros(len(qc) + 1, dtype=torch.int64, device=dev)
+        d_hits = torch.empty(total, dtype=torch.int32, device=dev)
+        for _ in range(2):
+            idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 8, len(qc), d_off.data_ptr(),
+                             d_hits.data_ptr(), total, s2.cuda_stream)
+    s2.synchronize()
+    assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
+    assert np.array_equal(d_hits.cpu().numpy().view(np.uint32), exp_hits)
+
+
+def test_fused_host_pipeline_regrows_on_dense_chunks(gg, oracle):
+    """Host-buffer call, fused mode: chunks whose hit count exceeds the running estimate are re-run exactly;
+    very long hit lists (> 512 per warp tile) take the direct-to-global walk."""
+    rng = np.random.default_rng(47)
+    n = 40_000
+    start = np.sort(rng.integers(0, 100_000, n)).astype(np.uint64)
+    end = start + rng.integers(1, 3000, n).astype(np.uint64)   # ~600 hits per query
+    chrom = np.zeros(n, np.uint32)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("chunk_queries", 8192)
+    idx.build(chrom, start, end, 1)
+    nq = 30_000
+    qs = rng.integers(0, 200_000, nq).astype(np.uint64)  # second half of the span: no hits at all
+    qs[:10_000] = np.sort(qs[:10_000])
+    q = (np.zeros(nq, np.uint32), qs, qs + rng.integers(0, 50, nq).astype(np.uint64))
+    hits = _check(idx, chrom, start, end, 1, q)
+    assert hits > 50 * nq
+    assert idx.batch_stats().n_chunks == 4
+    _check(idx, chrom, start, end, 1, q)  # second call on warm buffers
+
+
+def test_many_contigs_offset_table_outside_shared_memory(gg, oracle):
+    # 5000 contigs x 2 levels: the level-offset table (40 KB) is read through L1 instead of shared memory
+    rng = np.random.default_rng(53)
+    n_chrom = 5000
+    chrom, start, end = random_index(rng, 200_000, n_chrom, span=50_000)
+    chrom[:2000] = 7  # one contig deep enough for a second level
+    idx = gg.DeviceIndex(0)
+    idx.build(chrom, start, end, n_chrom)
+    _check(idx, chrom, start, end, n_chrom, random_queries(rng, 60_000, n_chrom, span=50_000))
 
 
 def test_long_nested_intervals_use_max_end_pruning(gg, oracle):
