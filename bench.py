@@ -4,8 +4,10 @@
 Workload (BASELINE.json configs[3], the configuration the metric is quoted on): a 10M-interval hg38-shaped
 grove (24 chromosomes) and, PER GPU, 100M read-shaped (150 bp) queries, coordinate-sorted per chromosome
 (BAM-like); index replicated on every GPU, query batch sharded (weak scaling: per-GPU work is fixed).
-A step = one pass of the hot path over the rank's 100M-query batch: ONE fused kernel (count -> decoupled
-look-back scan -> emit, genogrove_b200/csrc/fused.cuh); --two-phase times the count / scan / emit kernels.
+A step = one pass of the hot path over the rank's 100M-query batch through the single-call device entry point
+(gg_intersect_fused_device): count (4 consecutive queries per thread) -> scan of the per-block totals -> emit_scan
+(offsets + hits), genogrove_b200/csrc/{intersect,emit_scan}.cuh.  --one-kernel times the one-kernel look-back form
+(fused.cuh), --two-phase the count / scan / emit kernels of the two-phase API.
 
   value : whole-job queries/s with queries and results resident in HBM (device-buffer C ABI).
   e2e   : the same metric through the host-buffer C ABI call (gg_intersect_batch, u64 coordinates as the
@@ -47,8 +49,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--two-phase", action="store_true",
-                    help="time the count -> scan -> emit kernels (two-phase API) instead of the fused kernel")
-    ap.add_argument("--regs40", action="store_true", help="40-register build of the fused kernel")
+                    help="time the count -> scan -> emit kernels (two-phase API) instead of the single-call path")
+    ap.add_argument("--one-kernel", action="store_true", help="single-call path as ONE kernel (decoupled look-back scan)")
+    ap.add_argument("--regs40", action="store_true", help="40-register build of the one-kernel form")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     return ap.parse_args()
 
@@ -211,6 +214,8 @@ def main():
     d_tot = torch.zeros(1, dtype=torch.int64, device=dev)
     d_all = torch.zeros(world, dtype=torch.int64, device=dev)
     fused = not args.two_phase
+    one_kernel = fused and args.one_kernel
+    idx.set_option("fused_kernel", 1 if one_kernel else 0)
     if args.regs40:
         idx.set_option("fused_regs40", 1)
     if args.ctas_per_sm:
@@ -234,7 +239,7 @@ def main():
         if record:
             torch.cuda.current_stream().synchronize()
             bs = idx.batch_stats()
-            if fused:
+            if one_kernel:
                 kms["fused"].append(bs.emit_ms)
             else:
                 kms["count"].append(bs.count_ms), kms["scan"].append(bs.scan_ms), kms["emit"].append(bs.emit_ms)
@@ -284,9 +289,17 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     bytes_path = 12 * nq + 8 * (nq + 1) + 4 * total  # B_q = read (chrom,start,end) u32, write offsets u64, ranks u32
-    if fused:
+    if one_kernel:
         dom, dom_ms, dom_bytes = "intersect_fused_kernel", kernel_ms["fused"], bytes_path
         launches_per_step = 1
+    elif fused:
+        bytes_count = 12 * nq + 8 * nq                   # read (chrom,start,end) u32, write count u32 + hi u32
+        bytes_emit = 4 * total + 8 * (nq + 1) + 16 * nq  # write ranks + offsets, read count, hi, chrom, start
+        if kernel_ms["emit"] >= kernel_ms["count"]:
+            dom, dom_ms, dom_bytes = "intersect_emit_scan_kernel", kernel_ms["emit"], bytes_emit
+        else:
+            dom, dom_ms, dom_bytes = "intersect_count_group_kernel", kernel_ms["count"], bytes_count
+        launches_per_step = 3
     else:
         bytes_count = 12 * nq + 8 * nq                   # read (chrom,start,end) u32, write count u32 + hi u32
         bytes_emit = 4 * total + 8 * (nq + 1) + 12 * nq  # write ranks, read offsets, chrom/start/hi

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgg_b200.so")
+LIB_PATH = os.environ.get("GG_B200_LIB") or os.path.join(_HERE, "libgg_b200.so")  # override: A/B builds of tools/
 
 NO_CHROM = 0xFFFFFFFF
 GG_OK = 0

@@ -42,61 +42,6 @@ __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
     return v;
 }
 
-// 8 consecutive keys from a 32-byte aligned address
-__device__ __forceinline__ void load8(const uint32_t* __restrict__ p, uint32_t (&e)[8]) {
-    const uint4 a = *reinterpret_cast<const uint4*>(p);
-    const uint4 b = *reinterpret_cast<const uint4*>(p + 4);
-    e[0] = a.x; e[1] = a.y; e[2] = a.z; e[3] = a.w;
-    e[4] = b.x; e[5] = b.y; e[6] = b.z; e[7] = b.w;
-}
-__device__ __forceinline__ void load8(const uint64_t* __restrict__ p, uint64_t (&e)[8]) {
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + 2 * k);
-        e[2 * k] = v.x;
-        e[2 * k + 1] = v.y;
-    }
-}
-
-// Backward walk of one query in aligned groups of 8 ranks (two independent 16-byte loads in flight per step).
-// Same contract as emit_walk_staged: hits go to shared memory back to front between s_begin and s_end; the walk
-// ends when the list is full.  Exactly count(q) ranks below hi pass the test, so the list fills exactly.
-template <typename C>
-__device__ __forceinline__ void emit_walk_staged8(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
-                                                  int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t s_begin,
-                                                  uint32_t s_end) {
-    const C* __restrict__ leaf_end = ix.M + tabp[chrom];
-    uint32_t r_hi = hi, sp = s_end;
-    C e[8];
-    if ((r_hi & 7u) != 0) {  // partial top group: ranks g8 .. hi-1
-        const uint32_t g8 = r_hi & ~7u, top = r_hi & 7u;
-        load8(leaf_end + g8, e);
-#pragma unroll
-        for (int k = 6; k >= 1; --k) {
-            if (top > static_cast<uint32_t>(k) && e[k] >= qs) { sp -= 4; sts32(sp, g8 + k); }
-        }
-        if (e[0] >= qs) { sp -= 4; sts32(sp, g8); }
-        r_hi = g8;
-    }
-    const bool has_levels = n_levels > 1;
-    while (sp > s_begin && r_hi != 0) {
-        if ((r_hi & (kFanout - 1)) == 0 && has_levels) {
-            const uint32_t span = emit_skip_span<C>(ix, tabp, stride, n_levels, chrom, qs, r_hi);
-            if (span) {
-                r_hi -= span;
-                continue;
-            }
-        }
-        const uint32_t g8 = r_hi - 8;
-        load8(leaf_end + g8, e);
-#pragma unroll
-        for (int k = 7; k >= 0; --k) {
-            if (e[k] >= qs) { sp -= 4; sts32(sp, g8 + k); }
-        }
-        r_hi = g8;
-    }
-}
-
 // kMinCtas: resident CTAs per SM the register allocation targets (8 -> 32 registers, 6 -> 40)
 template <typename C, typename Q, int kMinCtas>
 __global__ void __launch_bounds__(kQueryThreads, kMinCtas)

@@ -13,6 +13,7 @@
 
 #include "build.cuh"
 #include "common.cuh"
+#include "emit_scan.cuh"
 #include "fused.cuh"
 #include "intersect.cuh"
 #include "radix_sort.cuh"
@@ -22,6 +23,8 @@ using namespace gg;
 
 namespace {
 
+constexpr int kBatchQpt = 4;  // consecutive queries per thread of the grouped count kernel
+constexpr size_t kBatchBlockQ = 32 * kBatchQpt;  // = one warp's share: the granularity of the batch path's block totals
 constexpr int kSlots = 3;        // pipeline depth of the host-buffer path
 constexpr int kCountThreadsDefault = 256;
 
@@ -87,6 +90,7 @@ struct gg_index {
     DeviceBuf q_cnt, q_hi, scan_scratch, err_flag, fused_scratch, fused_out;
     size_t counted_nq = 0;
     bool timing = false;
+    bool in_device_call = false;  // gg_intersect_fused_device is running: its kernels are bracketed by ev[] when timing is on
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     bool ev_count_valid = false, ev_emit_valid = false;
 
@@ -111,9 +115,12 @@ struct gg_index {
     int64_t count_ctas_per_sm = 0;  // 0 = occupancy API
     int64_t emit_ctas_per_sm = 0;
     int64_t fused_ctas_per_sm = 0;
+    int64_t fused_kernel = 0;  // single-call path: 0 = count -> block scan -> emit_scan kernels, 1 = the one-kernel look-back form
+    int64_t emit_walk = 8;     // ranks per walk step of emit_scan: 8 (sorted batches) or 16 (scattered batches)
     int64_t fused_regs40 = 0;  // 1: the 40-register build of the fused kernel (6 CTAs/SM) instead of 32 registers (8 CTAs/SM)
     int64_t host_mode = 0;   // host-buffer pipeline: 0 = one fused kernel per chunk, 1 = count -> scan -> emit kernels
-    int64_t count_mode = 0;  // 0: root directory + bracketed search, 1: tiered tree kernel (TMA windows / warp / per-lane)
+    int64_t count_mode = 2;  // 2: directory + finger search, 4 consecutive queries per thread; 0: directory, one query
+                             // per thread; 1: tiered tree kernel (TMA windows / warp / per-lane)
 
     gg_batch_stats bstats{};
 };
@@ -141,6 +148,7 @@ gg_status fail(gg_index* idx, gg_status st, const char* what, cudaError_t e = cu
         if (e_ != cudaSuccess) return fail(idx, GG_ERR_CUDA, #call, e_); \
     } while (0)
 
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline unsigned blocks_for(size_t n, unsigned threads) { return static_cast<unsigned>(div_up(n ? n : 1, threads)); }
 
 template <typename C>
@@ -178,7 +186,20 @@ gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
                        uint64_t* d_off, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, void* scratch,
                        const uint64_t* d_base, cudaStream_t st, cudaEvent_t ev_after_count) {
     GG_CUDA(scan2_prepare_async(scratch, nq, st));
-    if (idx->count_mode == 0) {
+    if (idx->count_mode == 2) {
+        // 4 consecutive queries per thread (finger search): the default
+        const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end) && aligned16(d_cnt) && aligned16(d_hi);
+        auto kern = intersect_count_group_kernel<C, Q, kBatchQpt>;
+        int per_sm = static_cast<int>(idx->count_ctas_per_sm);
+        if (per_sm <= 0) {
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
+            if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
+        }
+        size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads) * kBatchQpt);
+        unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+        kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi,
+                                             scan2_tile_total(scratch), nullptr, d_err, vec_ok);
+    } else if (idx->count_mode == 0) {
         auto kern = intersect_count_dir_kernel<C, Q>;
         int per_sm = static_cast<int>(idx->count_ctas_per_sm);
         if (per_sm <= 0) {
@@ -290,16 +311,94 @@ gg_status launch_fused(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     return GG_OK;
 }
 
+// The single-call batch path (default): count (4 consecutive queries per thread, finger search) -> exclusive scan
+// of the per-block hit totals (one block = 128 queries, ~0.8 % of the batch) -> emit_scan (offsets + hits).
+// scratch layout: [block_total u64 x nb][block_prefix u64 x (nb + 1)][look-back state of the small scan]
+//                 [cnt u32 x nq][hi u32 x nq]
+inline size_t batch_blocks(size_t nq) { return div_up(nq, kBatchBlockQ); }
+inline size_t batch_ctl_bytes(size_t nq) {
+    const size_t nb = batch_blocks(nq) + 1;
+    return round_up(nb * 8, 256) + round_up((nb + 1) * 8, 256) + round_up(scan_state_bytes(nb), 256);
+}
+// one scratch buffer serves either flavour of the single-call path
+inline size_t single_scratch_bytes(size_t nq) {
+    return std::max(round_up(fused_scratch_bytes(nq), 256), batch_ctl_bytes(nq)) + 2 * round_up((nq ? nq : 1) * 4, 256);
+}
+
+template <typename C, typename Q>
+gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, size_t nq,
+                       uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, const uint64_t* d_base,
+                       uint64_t* d_next_base, uint64_t* d_total, void* scratch, uint32_t* d_err, cudaStream_t st) {
+    char* p = static_cast<char*>(scratch);
+    const size_t nb = batch_blocks(nq), nb1 = nb + 1;
+    unsigned long long* block_total = reinterpret_cast<unsigned long long*>(p);
+    uint64_t* block_prefix = reinterpret_cast<uint64_t*>(p + round_up(nb1 * 8, 256));
+    void* scan_state = p + round_up(nb1 * 8, 256) + round_up((nb1 + 1) * 8, 256);
+    char* tail = p + std::max(round_up(fused_scratch_bytes(nq), 256), batch_ctl_bytes(nq));
+    uint32_t* d_cnt = reinterpret_cast<uint32_t*>(tail);
+    uint32_t* d_hi = reinterpret_cast<uint32_t*>(tail + round_up((nq ? nq : 1) * 4, 256));
+    const bool tab_in_smem = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024;
+    if (nq) {
+        auto kern = intersect_count_group_kernel<C, Q, kBatchQpt>;
+        int per_sm = static_cast<int>(idx->count_ctas_per_sm);
+        if (per_sm <= 0) {
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
+            if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
+        }
+        const size_t tiles = div_up(nq, static_cast<size_t>(kQueryThreads) * kBatchQpt);
+        const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+        const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end);
+        kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi, nullptr, block_total,
+                                             d_err, vec_ok);
+        GG_CUDA(cudaGetLastError());
+        idx->bstats.kernel_launches++;
+    }
+    const bool timed = idx->timing && idx->in_device_call;
+    if (timed) GG_CUDA(cudaEventRecord(idx->ev[1], st));
+    GG_CUDA((exclusive_scan_async<uint64_t, uint64_t>(reinterpret_cast<const uint64_t*>(block_total), block_prefix, nb, scan_state,
+                                                       d_base, nullptr, st)));
+    idx->bstats.kernel_launches++;
+    if (timed) {
+        GG_CUDA(cudaEventRecord(idx->ev[2], st));
+        GG_CUDA(cudaEventRecord(idx->ev[3], st));
+    }
+    {
+        const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
+        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
+        void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
+                     uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int) =
+            idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16> : intersect_emit_scan_kernel<C, Q, 8>;
+        if (smem > 48 * 1024)
+            GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        int per_sm = static_cast<int>(idx->emit_ctas_per_sm);
+        if (per_sm <= 0) {
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+            if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "emit kernel does not fit on an SM");
+        }
+        const size_t ctas = div_up(std::max<size_t>(nb, 1), kQueryThreads / 32);
+        const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
+        kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix,
+                                                static_cast<uint32_t>(kBatchBlockQ), d_off, d_hits, capacity, d_next_base, d_total,
+                                                d_err, tab_in_smem ? 1 : 0);
+        GG_CUDA(cudaGetLastError());
+        idx->bstats.kernel_launches++;
+    }
+    return GG_OK;
+}
+
 gg_status dispatch_fused(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, int q_bytes,
                          size_t nq, uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, const uint64_t* d_base,
                          uint64_t* d_next_base, uint64_t* d_total, void* scratch, uint32_t* d_err, cudaStream_t st) {
-    if (idx->coord_bytes == 4 && q_bytes == 4)
-        return launch_fused<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
-    if (idx->coord_bytes == 4 && q_bytes == 8)
-        return launch_fused<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
-    if (idx->coord_bytes == 8 && q_bytes == 4)
-        return launch_fused<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, (const uint32_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
-    return launch_fused<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, (const uint64_t*)d_end, nq, d_off, d_hits, capacity, d_base, d_next_base, d_total, scratch, d_err, st);
+#define GG_SINGLE(C, Q)                                                                                                      \
+    (idx->fused_kernel ? launch_fused<C, Q>(idx, d_chrom, (const Q*)d_start, (const Q*)d_end, nq, d_off, d_hits, capacity,    \
+                                            d_base, d_next_base, d_total, scratch, d_err, st)                                \
+                       : launch_batch<C, Q>(idx, d_chrom, (const Q*)d_start, (const Q*)d_end, nq, d_off, d_hits, capacity,    \
+                                            d_base, d_next_base, d_total, scratch, d_err, st))
+    if (idx->coord_bytes == 4 && q_bytes == 4) return GG_SINGLE(uint32_t, uint32_t);
+    if (idx->coord_bytes == 4 && q_bytes == 8) return GG_SINGLE(uint32_t, uint64_t);
+    if (idx->coord_bytes == 8 && q_bytes == 4) return GG_SINGLE(uint64_t, uint32_t);
+    return GG_SINGLE(uint64_t, uint64_t);
+#undef GG_SINGLE
 }
 
 // ------------------------------------------------------------------------------------------ build
@@ -782,7 +881,7 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
         GG_CUDA(sl.qs.ensure(m * sizeof(Q)));
         GG_CUDA(sl.qe.ensure(m * sizeof(Q)));
         GG_CUDA(sl.off.ensure((m + 1) * 8));
-        GG_CUDA(sl.fscratch.ensure(fused_scratch_bytes(m)));
+        GG_CUDA(sl.fscratch.ensure(single_scratch_bytes(m)));
         GG_CUDA(sl.err.ensure(16));
         const size_t want = static_cast<size_t>(est_per_q * 1.25 * static_cast<double>(m)) + 4096;
         if (sl.hits.cap / 4 < want) GG_CUDA(sl.hits.ensure(want * 4));
@@ -1042,7 +1141,7 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
     if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
     GG_CUDA(cudaSetDevice(idx->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    GG_CUDA(idx->fused_scratch.ensure(fused_scratch_bytes(nq)));
+    GG_CUDA(idx->fused_scratch.ensure(single_scratch_bytes(nq)));
     GG_CUDA(idx->fused_out.ensure(16));
     GG_CUDA(idx->err_flag.ensure(16));
     idx->bstats = gg_batch_stats{};
@@ -1051,13 +1150,19 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
     idx->ev_count_valid = idx->ev_emit_valid = false;
     idx->counted_nq = 0;  // the two-phase emit needs its own count pass
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
-    if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[3], st));
+    if (idx->timing) {
+        GG_CUDA(cudaEventRecord(idx->ev[0], st));
+        GG_CUDA(cudaEventRecord(idx->ev[3], st));
+    }
+    idx->in_device_call = true;
     gg_status s = dispatch_fused(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_offsets, d_hits, capacity, nullptr, nullptr,
                                  idx->fused_out.as<uint64_t>(), idx->fused_scratch.p, idx->err_flag.as<uint32_t>(), st);
+    idx->in_device_call = false;
     if (s != GG_OK) return s;
     if (idx->timing) {
         GG_CUDA(cudaEventRecord(idx->ev[4], st));
         idx->ev_emit_valid = true;
+        idx->ev_count_valid = !idx->fused_kernel;  // count / block-scan / emit_scan times of the three-kernel form
     }
     if (total_hits) {
         uint32_t flag = 0;
@@ -1173,9 +1278,11 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "count_ctas_per_sm" && value >= 0 && value <= 32) idx->count_ctas_per_sm = value;
     else if (k == "emit_ctas_per_sm" && value >= 0 && value <= 32) idx->emit_ctas_per_sm = value;
     else if (k == "fused_ctas_per_sm" && value >= 0 && value <= 32) idx->fused_ctas_per_sm = value;
+    else if (k == "fused_kernel" && (value == 0 || value == 1)) idx->fused_kernel = value;
+    else if (k == "emit_walk" && (value == 8 || value == 16)) idx->emit_walk = value;
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
-    else if (k == "count_mode" && (value == 0 || value == 1)) idx->count_mode = value;
+    else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;
     else return fail(idx, GG_ERR_INVALID_ARG, "unknown option or value out of range");
     return GG_OK;

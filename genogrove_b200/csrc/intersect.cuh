@@ -209,14 +209,57 @@ __global__ void build_dir_kernel(IndexView<C> ix, uint32_t* __restrict__ dirS, u
     dirE[e] = ve;
 }
 
-// #keys <= x in the sorted leaf array a, given directory brackets: the answer lies in [lo, hi]
+// 8 consecutive keys from a 32-byte (u32) / 64-byte (u64) aligned address
+__device__ __forceinline__ void load8(const uint32_t* __restrict__ p, uint32_t (&e)[8]) {
+    const uint4 a = *reinterpret_cast<const uint4*>(p);
+    const uint4 b = *reinterpret_cast<const uint4*>(p + 4);
+    e[0] = a.x; e[1] = a.y; e[2] = a.z; e[3] = a.w;
+    e[4] = b.x; e[5] = b.y; e[6] = b.z; e[7] = b.w;
+}
+__device__ __forceinline__ void load8(const uint64_t* __restrict__ p, uint64_t (&e)[8]) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + 2 * k);
+        e[2 * k] = v.x;
+        e[2 * k + 1] = v.y;
+    }
+}
 template <typename C>
-__device__ __forceinline__ uint32_t bracket_upper_bound(const C* __restrict__ a, uint32_t lo, uint32_t hi, C x) {
-    while (lo < hi) {
+__device__ __forceinline__ uint32_t count_le8(const C (&e)[8], C x) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) c += (e[k] <= x) ? 1u : 0u;
+    return c;
+}
+
+// #keys <= x in the sorted leaf array a (32-key aligned, padded segment of one chromosome), given directory
+// brackets: the answer lies in [lo, hi].  Two flavours, same result.  grouped = true: directory bins hold ~8 keys,
+// so instead of the 3-4 DEPENDENT loads of a bisection the bracket is read as aligned groups of 8 keys (two 16-byte
+// loads in flight, 1-2 groups on average); wider brackets are first narrowed by bisection.  This wins when every
+// load is an L2 round trip (scattered batches: count pass 2.9 vs 3.7 ms on cfg4 shuffled) and loses when the loads
+// hit L1 (coordinate-sorted batches: 0.77 vs 0.69 ms), so callers choose per warp.  Keys below lo are <= x and keys at or above hi are > x (or padding).
+template <typename C>
+__device__ __forceinline__ uint32_t bracket_upper_bound(const C* __restrict__ a, uint32_t lo, uint32_t hi, C x,
+                                                        bool grouped = false) {
+    if (!grouped) {  // plain bisection: fewest instructions; the loads hit L1 when neighbouring lanes search nearby
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (a[mid] <= x) lo = mid + 1; else hi = mid;
+        }
+        return lo;
+    }
+    while (hi - lo > 16) {
         const uint32_t mid = (lo + hi) >> 1;
         if (a[mid] <= x) lo = mid + 1; else hi = mid;
     }
-    return lo;
+    uint32_t r = lo & ~7u;
+    for (uint32_t g = r; g < hi && r == g; g += 8) {  // stops at the first group that holds a key > x
+        C e[8];
+        load8(a + g, e);
+        r += count_le8<C>(e, x);
+    }
+    r = r > lo ? r : lo;  // (lo == hi with lo not a multiple of 8: no group was read)
+    return r < hi ? r : hi;
 }
 
 // Pass 1, directory flavour (default): one query per thread, no shared memory, no barriers.
@@ -270,6 +313,194 @@ intersect_count_dir_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
         if (lane_id() == 0 && wsum != 0) atomicAdd(&tile_total[(tile * kQueryThreads + (threadIdx.x & ~31u)) / kScanTile], wsum);
+    }
+}
+
+// ---- several consecutive queries per thread -------------------------------------------------------------
+// N consecutive elements from a 16-byte aligned address (N * sizeof(T) is 8 or a multiple of 16); streaming loads:
+// a query is read exactly once and must not push index lines out of L1/L2
+template <typename T, int N>
+__device__ __forceinline__ void load_vec_stream(const T* __restrict__ p, T (&v)[N]) {
+    constexpr int kBytes = N * static_cast<int>(sizeof(T));
+    if constexpr (kBytes == 8) {
+        union { uint2 u; T t[N]; } x;
+        x.u = __ldcs(reinterpret_cast<const uint2*>(p));
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] = x.t[i];
+    } else {
+        static_assert(kBytes % 16 == 0, "vector load needs a multiple of 16 bytes");
+        union { uint4 u[kBytes / 16]; T t[N]; } x;
+#pragma unroll
+        for (int k = 0; k < kBytes / 16; ++k) x.u[k] = __ldcs(reinterpret_cast<const uint4*>(p) + k);
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] = x.t[i];
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void store_vec_stream(uint64_t* __restrict__ p, const uint64_t (&v)[N]) {
+    static_assert(N % 2 == 0, "pairs of u64");
+#pragma unroll
+    for (int k = 0; k < N / 2; ++k) {
+        ulonglong2 x;
+        x.x = v[2 * k];
+        x.y = v[2 * k + 1];
+        __stcs(reinterpret_cast<ulonglong2*>(p) + k, x);
+    }
+}
+
+// Search state carried from one query of a thread to the next (see the header comment)
+template <typename C>
+struct Finger {
+    uint32_t pos = 0, bhi = 0, bin = 0;
+    C x = 0;
+    bool valid = false;
+};
+
+// #keys <= x in the sorted leaf array a of one chromosome; dir = that chromosome's directory row
+template <typename C>
+__device__ __forceinline__ uint32_t finger_upper_bound(const C* __restrict__ a, const uint32_t* __restrict__ dir,
+                                                       uint32_t last_bin, int shift, C x, Finger<C>& f, bool grouped) {
+    const C bx = x >> shift;
+    const uint32_t b = bx > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(bx);
+    uint32_t h;
+    if (f.valid && b == f.bin && x >= f.x) {
+        h = f.pos;  // ub(x) lies in [ub(previous x), bracket end]; neighbouring queries advance by 0-2 keys
+        int probes = 0;
+        while (h < f.bhi && a[h] <= x) {
+            ++h;
+            if (++probes == 4) {
+                h = bracket_upper_bound<C>(a, h, f.bhi, x, grouped);
+                break;
+            }
+        }
+    } else {
+        const uint32_t blo = dir[b];
+        f.bhi = dir[b + 1];
+        f.bin = b;
+        h = bracket_upper_bound<C>(a, blo, f.bhi, x, grouped);
+    }
+    f.pos = h;
+    f.x = x;
+    f.valid = true;
+    return h;
+}
+
+// Count pass for QPT consecutive queries of one thread: hi[j] = ub(S, q.end), cnt[j] = hi[j] - ub(E, q.start - 1),
+// qs[j] = q.start in index coordinates; queries that cannot hit (unknown chromosome, start beyond the index
+// domain, start > end) get zero.  Returns true when some query had start > end (interval.hpp:70-74).
+template <typename C, typename Q, int QPT>
+__device__ __forceinline__ bool count_group(const IndexView<C>& ix, const uint32_t* __restrict__ tabp,
+                                            const uint32_t (&chrom)[QPT], const Q (&qs_raw)[QPT], const Q (&qe_raw)[QPT],
+                                            uint32_t (&cnt)[QPT], uint32_t (&hi)[QPT], C (&qs)[QPT]) {
+    Finger<C> fs, fe;
+    uint32_t cur = GG_NO_CHROM_DEV, d0 = 0, last_bin = 0, leaf = 0;
+    bool any_bad = false;
+    const int shift = ix.dir_shift;
+    // Do the warp's lanes search the same neighbourhood (same chromosome, within 32 directory bins of lane 0)?
+    // Then the search loads hit L1 and plain bisection is cheapest; otherwise read the bracket as 8-key groups.
+    const Q e0 = qe_raw[0], e_lane0 = __shfl_sync(0xffffffffu, e0, 0);
+    const uint32_t c_lane0 = __shfl_sync(0xffffffffu, chrom[0], 0);  // (both shuffles before the &&: every lane takes part)
+    const bool same_area = (((e0 ^ e_lane0) >> (shift + 5)) == 0) & (chrom[0] == c_lane0);
+    const bool grouped = !__all_sync(0xffffffffu, same_area);
+#pragma unroll
+    for (int j = 0; j < QPT; ++j) {
+        const bool bad = qs_raw[j] > qe_raw[j];
+        any_bad |= bad;
+        const bool ok = !bad && chrom[j] < ix.n_chrom &&
+                        !(sizeof(Q) > sizeof(C) && qs_raw[j] > static_cast<Q>(coord_max<C>::value));
+        cnt[j] = 0;
+        hi[j] = 0;
+        qs[j] = 0;
+        if (ok) {
+            if (chrom[j] != cur) {
+                cur = chrom[j];
+                d0 = ix.dir_off[cur];
+                last_bin = ix.dir_off[cur + 1] - d0 - 2;
+                leaf = tabp[cur];
+                fs.valid = fe.valid = false;
+            }
+            const C qe = clamp_coord<C, Q>(qe_raw[j]);
+            qs[j] = static_cast<C>(qs_raw[j]);
+            hi[j] = finger_upper_bound<C>(ix.S + leaf, ix.dirS + d0, last_bin, shift, qe, fs, grouped);
+            uint32_t lo = 0;
+            if (qs[j] > 0)
+                lo = finger_upper_bound<C>(ix.E + leaf, ix.dirE + d0, last_bin, shift, static_cast<C>(qs[j] - 1), fe, grouped);
+            cnt[j] = hi[j] - lo;
+        }
+    }
+    return any_bad;
+}
+
+template <int N>
+__device__ __forceinline__ void store_vec_u32(uint32_t* __restrict__ p, const uint32_t (&v)[N]) {
+    if constexpr (N == 2) {
+        *reinterpret_cast<uint2*>(p) = make_uint2(v[0], v[1]);
+    } else {
+        static_assert(N % 4 == 0, "groups of four u32");
+#pragma unroll
+        for (int k = 0; k < N / 4; ++k)
+            reinterpret_cast<uint4*>(p)[k] = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    }
+}
+
+// Pass 1, QPT consecutive queries per thread (directory + finger search, see count_group): 16-byte vector loads of
+// the queries, 16-byte stores of cnt / hi, no shared memory, no barriers.  Same outputs as
+// intersect_count_dir_kernel (tile_total, for the two-phase API's scan), and / or block_total[b] = hits of the
+// b-th block of 32 * QPT consecutive queries (one warp's share; plain stores, no atomics) for the batch path,
+// whose emit kernel turns scanned block totals into offsets itself.  A warp's queries never straddle a scan tile.
+template <typename C, typename Q, int QPT>
+__global__ void __launch_bounds__(kQueryThreads)
+intersect_count_group_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
+                             const Q* __restrict__ qend, size_t nq, uint32_t* __restrict__ cnt_out,
+                             uint32_t* __restrict__ hi_out, unsigned long long* __restrict__ tile_total,
+                             unsigned long long* __restrict__ block_total, uint32_t* __restrict__ err_flag, int vec_ok) {
+    static_assert(kScanTile % (32 * QPT) == 0, "a warp's queries must stay inside one scan tile");
+    constexpr size_t kTileQ = static_cast<size_t>(kQueryThreads) * QPT;
+    const size_t n_tiles = (nq + kTileQ - 1) / kTileQ;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t q0 = tile * kTileQ + static_cast<size_t>(threadIdx.x) * QPT;
+        const bool vec = vec_ok && q0 + QPT <= nq;
+        uint32_t chrom[QPT];
+        Q qs_raw[QPT], qe_raw[QPT];
+        if (vec) {
+            load_vec_stream<uint32_t, QPT>(qchrom + q0, chrom);
+            load_vec_stream<Q, QPT>(qstart + q0, qs_raw);
+            load_vec_stream<Q, QPT>(qend + q0, qe_raw);
+        } else {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j) {
+                const bool in = q0 + j < nq;
+                chrom[j] = in ? qchrom[q0 + j] : GG_NO_CHROM_DEV;
+                qs_raw[j] = in ? qstart[q0 + j] : Q(0);
+                qe_raw[j] = in ? qend[q0 + j] : Q(0);
+            }
+        }
+        uint32_t cnt[QPT], hi[QPT];
+        C qs[QPT];
+        if (count_group<C, Q, QPT>(ix, ix.tab, chrom, qs_raw, qe_raw, cnt, hi, qs)) atomicOr(err_flag, 1u);
+        if (vec) {  // (cnt_out / hi_out are 16-byte aligned whenever vec_ok: the host checks)
+            store_vec_u32<QPT>(cnt_out + q0, cnt);
+            store_vec_u32<QPT>(hi_out + q0, hi);
+        } else {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j) {
+                if (q0 + j < nq) {
+                    cnt_out[q0 + j] = cnt[j];
+                    hi_out[q0 + j] = hi[j];
+                }
+            }
+        }
+        unsigned long long wsum = 0;
+#pragma unroll
+        for (int j = 0; j < QPT; ++j) wsum += cnt[j];
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        if (lane_id() == 0) {
+            const size_t wq0 = tile * kTileQ + static_cast<size_t>(threadIdx.x & ~31u) * QPT;  // the warp's first query
+            if (tile_total && wsum != 0) atomicAdd(&tile_total[wq0 / kScanTile], wsum);
+            if (block_total && wq0 < nq) block_total[wq0 / (32 * QPT)] = wsum;  // hits of block = 32 * QPT queries
+        }
     }
 }
 
@@ -553,6 +784,86 @@ __device__ __forceinline__ void emit_walk_staged(const IndexView<C>& ix, const u
         if (e1 >= qs) { sp -= 4; sts32(sp, g4 + 1); }
         if (e0 >= qs) { sp -= 4; sts32(sp, g4); }
         r_hi = g4;
+    }
+}
+
+// Backward walk of one query, up to 16 ranks per step: the aligned group of 8 that holds rank r_hi-1 and, when it
+// lies in the same 32-key node, the group below it — their four 16-byte loads are in flight together, which halves
+// the dependent-load chain of the walk (a typical cfg4 query walks ~32 ranks for its ~7 hits).  Same contract as
+// emit_walk_staged: hits go to shared memory back to front between s_begin and s_end; the walk ends when the list
+// is full.  Exactly count(q) ranks below hi pass the test, so the list fills exactly.
+template <typename C>
+__device__ __forceinline__ void emit_walk_staged16(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
+                                                  int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t s_begin,
+                                                  uint32_t s_end) {
+    const C* __restrict__ leaf_end = ix.M + tabp[chrom];
+    uint32_t r_hi = hi, sp = s_end;
+    C ea[8], eb[8];
+    const bool has_levels = n_levels > 1;
+    while (sp > s_begin && r_hi != 0) {
+        if ((r_hi & (kFanout - 1)) == 0 && has_levels) {
+            const uint32_t span = emit_skip_span<C>(ix, tabp, stride, n_levels, chrom, qs, r_hi);
+            if (span) {
+                r_hi -= span;
+                continue;
+            }
+        }
+        const uint32_t ga = (r_hi - 1) & ~7u;          // group holding rank r_hi - 1
+        const uint32_t top = r_hi - ga;                // 1..8: ranks of that group below r_hi
+        const bool two = (ga & (kFanout - 1)) != 0;    // the group below is in the same node
+        load8(leaf_end + ga, ea);
+        if (two) load8(leaf_end + ga - 8, eb);
+#pragma unroll
+        for (int k = 7; k >= 0; --k) {
+            if (static_cast<uint32_t>(k) < top && ea[k] >= qs) { sp -= 4; sts32(sp, ga + k); }
+        }
+        r_hi = ga;
+        if (two && sp > s_begin) {
+#pragma unroll
+            for (int k = 7; k >= 0; --k) {
+                if (eb[k] >= qs) { sp -= 4; sts32(sp, ga - 8 + k); }
+            }
+            r_hi = ga - 8;
+        }
+    }
+}
+
+// Backward walk of one query in aligned groups of 8 ranks (two independent 16-byte loads in flight per step); same
+// contract as emit_walk_staged16.  The faster of the two when neighbouring lanes walk the same lines (L1 hits:
+// coordinate-sorted batches); the 16-wide walk wins when every step is an L2 round trip (scattered batches).
+template <typename C>
+__device__ __forceinline__ void emit_walk_staged8(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
+                                                  int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t s_begin,
+                                                  uint32_t s_end) {
+    const C* __restrict__ leaf_end = ix.M + tabp[chrom];
+    uint32_t r_hi = hi, sp = s_end;
+    C ea[8];
+    const bool has_levels = n_levels > 1;
+    if ((r_hi & 7u) != 0) {  // partial top group: ranks g8 .. hi-1
+        const uint32_t g8 = r_hi & ~7u, top = r_hi & 7u;
+        load8(leaf_end + g8, ea);
+#pragma unroll
+        for (int k = 6; k >= 1; --k) {
+            if (top > static_cast<uint32_t>(k) && ea[k] >= qs) { sp -= 4; sts32(sp, g8 + k); }
+        }
+        if (ea[0] >= qs) { sp -= 4; sts32(sp, g8); }
+        r_hi = g8;
+    }
+    while (sp > s_begin && r_hi != 0) {
+        if ((r_hi & (kFanout - 1)) == 0 && has_levels) {
+            const uint32_t span = emit_skip_span<C>(ix, tabp, stride, n_levels, chrom, qs, r_hi);
+            if (span) {
+                r_hi -= span;
+                continue;
+            }
+        }
+        const uint32_t g8 = r_hi - 8;
+        load8(leaf_end + g8, ea);
+#pragma unroll
+        for (int k = 7; k >= 0; --k) {
+            if (ea[k] >= qs) { sp -= 4; sts32(sp, g8 + k); }
+        }
+        r_hi = g8;
     }
 }
 

@@ -132,7 +132,8 @@ def test_invalid_query_is_rejected(gg, oracle):
 
 @pytest.mark.parametrize("opt", [("chunk_queries", 4096), ("chunk_queries", 20_000), ("stage_bytes", 0),
                                  ("stage_bytes", 16384), ("stage_bytes", 196608), ("count_threads", 128),
-                                 ("count_threads", 1024), ("count_mode", 1), ("count_mode", 0), ("host_mode", 1),
+                                 ("count_threads", 1024), ("count_mode", 1), ("count_mode", 0), ("count_mode", 2), ("fused_kernel", 1), ("fused_kernel", 0),
+                                 ("emit_walk", 16), ("host_mode", 1),
                                  ("host_mode", 0), ("fused_regs40", 1), ("fused_ctas_per_sm", 1)])
 def test_options_do_not_change_results(gg, oracle, opt):
     rng = np.random.default_rng(31)
@@ -142,6 +143,8 @@ def test_options_do_not_change_results(gg, oracle, opt):
         idx.set_option("host_mode", 1)  # these knobs belong to the count -> scan -> emit kernels
     if opt[0] in ("stage_bytes", "count_threads"):
         idx.set_option("count_mode", 1)  # ... and these to the tiered tree kernel
+    if opt[0] in ("fused_regs40", "fused_ctas_per_sm"):
+        idx.set_option("fused_kernel", 1)  # knobs of the one-kernel form of the single-call path
     idx.set_option(*opt)
     idx.build(chrom, start, end, 24)
     q = random_queries(rng, 100_001, 24, span=400_000)
@@ -154,7 +157,7 @@ def test_options_do_not_change_results(gg, oracle, opt):
     assert np.array_equal(off, exp_off) and np.array_equal(hits, exp_hits)
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 2])
 @pytest.mark.parametrize("wide", [False, True])
 def test_sorted_batches_take_the_bracket_paths(gg, oracle, mode, wide):
     """Coordinate-sorted batches (the BAM-like case): root directory (mode 0) and TMA window / warp tiers (mode 1)."""
@@ -230,7 +233,7 @@ def test_fused_device_api_and_capacity(gg, oracle):
             got = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
                                    d_hits.data_ptr(), cap, stream, sync_total=True)
             assert got == total
-            assert idx.batch_stats().kernel_launches == 1
+            assert idx.batch_stats().kernel_launches == 3  # count, block scan, emit_scan
             assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
             h_hits = d_hits.cpu().numpy()
             assert np.array_equal(h_hits.view(np.uint32)[:total], exp_hits)
@@ -260,6 +263,56 @@ def test_fused_device_api_and_capacity(gg, oracle):
     s2.synchronize()
     assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
     assert np.array_equal(d_hits.cpu().numpy().view(np.uint32), exp_hits)
+
+
+@pytest.mark.parametrize("path", ["batch8", "batch16", "one_kernel"])
+def test_single_call_paths_sorted_unaligned_and_ragged(gg, oracle, path):
+    """The single-call device path (count, 4 consecutive queries per thread -> block scan -> emit_scan, with 8- and
+    16-rank walk steps) and its one-kernel look-back form on: coordinate-sorted batches (finger search from the
+    previous query of the thread), runs of identical queries, chromosome changes inside a thread's group, a
+    descending run, pointers that are not 16-byte aligned (scalar load path) and batch sizes that leave ragged
+    last tiles and blocks."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(71 + len(path))
+    chrom, start, end = random_index(rng, 120_000, 5, span=2_000_000, max_len=5000, nested=True, dup=True)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("fused_kernel", 1 if path == "one_kernel" else 0)
+    idx.set_option("emit_walk", 16 if path == "batch16" else 8)
+    idx.build(chrom, start, end, 5)
+    qc, qs, qe = random_queries(rng, 90_007, 5, span=2_000_000, max_len=400, extra_chrom=1)
+    order = np.lexsort((qs, qc))
+    qc, qs, qe = qc[order], qs[order], qe[order]
+    qs[1000:1400] = qs[1000]
+    qe[1000:1400] = qe[1000]          # identical queries
+    qc[5000:5003] = [4, 0, 4]         # chromosome flips inside a thread's consecutive group
+    qs[20_000:20_050] = 0             # start 0: no end can lie before it
+    qe[20_000:20_050] = np.sort(qe[20_000:20_050])
+    sl = slice(30_000, 30_400)        # a descending run (finger must not be used)
+    qs[sl], qe[sl] = qs[sl][::-1].copy(), qe[sl][::-1].copy()
+    bad = qs > qe
+    qe[bad] = qs[bad]
+    exp_off, exp_hits = oracle_csr(chrom, start, end, 5, qc, qs, qe)
+    dev = torch.device("cuda:0")
+    stream = torch.cuda.current_stream().cuda_stream
+    for nb, dt in ((4, np.uint32), (8, np.uint64)):
+        for shift in (0, 1):          # shift 1: every pointer 4 (or 8) bytes past a 16-byte boundary
+            for nq in (len(qc), 1, 127, 128, 129, 1023, 1024, 4099, 0):
+                off_np = exp_off[:nq + 1]
+                total = int(off_np[-1])
+                d_c = torch.zeros(nq + 4, dtype=torch.int32, device=dev)
+                d_s = torch.zeros(nq + 4, dtype=torch.int32 if nb == 4 else torch.int64, device=dev)
+                d_e = torch.zeros_like(d_s)
+                d_c[shift:shift + nq] = torch.from_numpy(qc[:nq].view(np.int32)).to(dev)
+                d_s[shift:shift + nq] = torch.from_numpy(qs[:nq].astype(dt).view(np.int32 if nb == 4 else np.int64)).to(dev)
+                d_e[shift:shift + nq] = torch.from_numpy(qe[:nq].astype(dt).view(np.int32 if nb == 4 else np.int64)).to(dev)
+                d_off = torch.zeros(nq + 4, dtype=torch.int64, device=dev)
+                d_hits = torch.full((total + 8,), -1, dtype=torch.int32, device=dev)
+                got = idx.fused_device(d_c[shift:].data_ptr(), d_s[shift:].data_ptr(), d_e[shift:].data_ptr(), nb, nq,
+                                       d_off[shift:].data_ptr(), d_hits.data_ptr(), total, stream, sync_total=True)
+                assert got == total
+                assert np.array_equal(d_off.cpu().numpy().view(np.uint64)[shift:shift + nq + 1], off_np)
+                h = d_hits.cpu().numpy()
+                assert np.array_equal(h.view(np.uint32)[:total], exp_hits[:total]) and (h[total:] == -1).all()
 
 
 def test_fused_host_pipeline_regrows_on_dense_chunks(gg, oracle):
