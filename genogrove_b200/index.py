@@ -147,7 +147,7 @@ class DeviceIndex:
 
     def fused_device(self, d_chrom: int, d_start: int, d_end: int, coord_bytes: int, nq: int, d_offsets: int,
                      d_hits: int, capacity: int, stream: int = 0, sync_total: bool = False):
-        """One fused kernel (count -> look-back scan -> emit).  Raises GG_ERR_CAPACITY (status 7) when sync_total
+        """Single-call path (count -> block-total scan -> emit_scan; one look-back kernel with option fused_kernel).  Raises GG_ERR_CAPACITY (status 7) when sync_total
         and the batch produced more than `capacity` hits; ``last_total`` then holds the needed size."""
         total = C.c_uint64(0)
         st = self._L.gg_intersect_fused_device(self._h, d_chrom, d_start, d_end, coord_bytes, nq, d_offsets, d_hits,

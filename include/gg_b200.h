@@ -16,8 +16,9 @@
  *   gg_index_upload_sorted    <- the leaf chain left by insert / insert_sorted / remove_key / compact
  *                                grove_insert.ipp:182-274, 501-531; grove_remove.ipp:24-98
  *   gg_intersect_*            <- grove::intersect(query, index) -> detail::search_overlaps
- *   (batch, fused_device,        [the host-buffer batch call and gg_intersect_fused_device run ONE fused kernel;
- *    count/emit[_device])         count/emit are the two-phase form for callers that size the output first]
+ *   (batch, fused_device,        [the host-buffer batch call and gg_intersect_fused_device are single calls that run
+ *    count/emit[_device])         count -> block-total scan -> emit_scan; count/emit are the two-phase form for
+ *                                 callers that size the output first]
  *                                include/genogrove/structure/grove/grove_query.ipp:33-43
  *                                include/genogrove/structure/grove/query_engine.hpp:76-134
  *                                with query_result::add_key (data_type/query_result.hpp:108-113)
@@ -85,8 +86,8 @@ typedef struct gg_batch_stats {
     uint32_t n_chunks;       /* pipeline chunks used by the host-buffer entry points */
     uint32_t kernel_launches;/* kernels launched by the last intersect call */
     double count_ms;         /* device time: count kernel (device-buffer calls with option "timing" on) */
-    double scan_ms;          /* device time: exclusive scan (tile-total scan + per-tile scan kernels) */
-    double emit_ms;          /* device time: emit kernel */
+    double scan_ms;          /* device time: exclusive scan (per-query scan of the two-phase API / block-total scan) */
+    double emit_ms;          /* device time: emit / emit_scan kernel (the whole kernel for "fused_kernel" = 1) */
     double total_ms;         /* device time first launch/copy -> last, host buffers included */
 } gg_batch_stats;
 
@@ -145,12 +146,14 @@ gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, cons
 gg_status gg_intersect_emit_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
                                    const void* d_end, int coord_bytes, size_t nq, const uint64_t* d_offsets,
                                    uint32_t* d_hits, void* stream);
-/* One-kernel variant (count -> decoupled look-back scan -> emit fused; every query read once, every offset and
- * hit written once).  d_hits has room for `capacity` ranks — the caller's estimate, e.g. from the previous
- * batch.  d_offsets[0..nq] is always complete; ranks that would land at or beyond `capacity` are not written.
- * With total_hits (host pointer) the call waits, stores offsets[nq] and returns GG_ERR_CAPACITY when the
- * batch produced more than `capacity` hits (re-run with a buffer of *total_hits ranks).  Without it the call
- * only enqueues; compare d_offsets[nq] with the capacity yourself. */
+/* Single-call variant: offsets and hits from one call, every query read once by the count pass (4 consecutive
+ * queries per thread), no per-query scan pass: count -> scan of the per-128-query block totals -> emit_scan (offsets +
+ * hits).  (Option "fused_kernel" = 1 runs the same thing as ONE kernel with a decoupled look-back scan.)
+ * d_hits has room for `capacity` ranks — the caller's estimate, e.g. from the previous batch.  d_offsets[0..nq] is
+ * always complete; ranks that would land at or beyond `capacity` are not written.  With total_hits (host pointer) the
+ * call waits, stores offsets[nq] and returns GG_ERR_CAPACITY when the batch produced more than `capacity` hits (re-run
+ * with a buffer of *total_hits ranks).  Without it the call only enqueues; compare d_offsets[nq] with the capacity
+ * yourself. */
 gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
                                     const void* d_end, int coord_bytes, size_t nq, uint64_t* d_offsets,
                                     uint32_t* d_hits, uint64_t capacity, uint64_t* total_hits, void* stream);
@@ -161,12 +164,15 @@ gg_status gg_host_alloc(void** out, size_t bytes);
 void gg_host_free(void* p);
 
 /* ---- tuning knobs (defaults are chosen for B200; used by tests/bench to pin behaviour) ----------- */
-/* key: "chunk_queries" (host pipeline chunk, default 8388608); "host_mode" (host-buffer calls: 0 = one fused
- * kernel per chunk [default], 1 = count -> scan -> emit kernels); "fused_ctas_per_sm"; "count_mode" (0 = root directory + bracketed
- * leaf search [default], 1 = tiered tree kernel: TMA-staged windows / warp bracket / per-lane descent);
- * for mode 1: "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and
- * "count_threads" (128..1024); "count_ctas_per_sm", "emit_ctas_per_sm" (0 = occupancy API); "timing" (0/1:
- * record CUDA events around the kernels of the device-buffer calls for gg_last_batch_stats). */
+/* key: "chunk_queries" (host pipeline chunk, default 8388608); "host_mode" (host-buffer calls: 0 = the single-call
+ * path per chunk with an estimated hit capacity [default], 1 = count, read the total, emit); "fused_kernel" (single-call
+ * path: 0 = count -> block scan -> emit_scan kernels [default], 1 = one kernel with a look-back scan; its knobs:
+ * "fused_ctas_per_sm", "fused_regs40"); "emit_walk" (ranks per walk step of emit_scan: 8 [default] or 16);
+ * "count_mode" (two-phase API: 2 = directory + finger search, 4 consecutive queries per thread [default], 0 = directory,
+ * one query per thread, 1 = tiered tree kernel: TMA-staged windows / warp bracket / per-lane descent; for mode 1:
+ * "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and "count_threads" (128..1024));
+ * "count_ctas_per_sm", "emit_ctas_per_sm" (0 = occupancy API); "timing" (0/1: record CUDA events around the kernels of
+ * the device-buffer calls for gg_last_batch_stats). */
 gg_status gg_set_option(gg_index* idx, const char* key, int64_t value);
 
 #ifdef __cplusplus
