@@ -6,5 +6,5 @@ reference's grove API (``grove.Grove``; the C++20 drop-in facade is include/geno
 synthetic workload generators of BASELINE.json (``synth``) and the multi-GPU sharding helpers (``shard``).
 There is no CPU implementation of the path anywhere in this package.
 """
-from .index import DeviceIndex, GGError, NO_CHROM, TIE_EXPLICIT, TIE_INPUT_ORDER, TIE_REVERSE_INPUT, PinnedArray  # noqa: F401
-from .grove import Grove, Interval, Key, QueryResult  # noqa: F401
+from .index import DeviceIndex, GGError, NO_CHROM, NO_RANK, TIE_EXPLICIT, TIE_INPUT_ORDER, TIE_REVERSE_INPUT, PinnedArray  # noqa: F401
+from .grove import FlankingQueryResult, Grove, Interval, Key, QueryResult  # noqa: F401

@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GG_B200_LIB") or os.path.join(_HERE, "libgg_b200.so")  # override: A/B builds of tools/
 
 NO_CHROM = 0xFFFFFFFF
+NO_RANK = 0xFFFFFFFF
 GG_OK = 0
 STATUS_NAMES = {
     0: "GG_OK",
@@ -33,6 +34,7 @@ EXPORTS = (
     "gg_intersect_batch", "gg_intersect_batch_u32", "gg_intersect_count", "gg_intersect_emit",
     "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_last_batch_stats",
     "gg_host_alloc", "gg_host_free", "gg_set_option",
+    "gg_flanking_batch", "gg_flanking_device",
 )
 
 
@@ -98,5 +100,7 @@ def lib():
     L.gg_host_free.argtypes = [vp]
     L.gg_host_free.restype = None
     L.gg_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.gg_flanking_batch.argtypes = [vp, vp, vp, vp, C.c_size_t, vp, vp]
+    L.gg_flanking_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_int, vp]
     _lib = L
     return L

@@ -1,0 +1,130 @@
+// flanking.cuh — batched nearest predecessor / successor ("flanking") queries on the flattened index.
+//
+// Replaces grove::flanking(query, index) -> detail::search_flanking
+// (include/genogrove/structure/grove/grove_flanking.ipp, include/genogrove/structure/grove/query_engine.hpp:238-311,
+// pruning rule flanking_could_descend :176-199) for interval keys with the default (always compatible) predicate.
+// The reference walks the tree depth-first in chain order and keeps
+//   predecessor: the non-overlapping key below the query with the LARGEST END, first one found on ties (:256-272)
+//   successor  : the non-overlapping key above the query that is smallest in (start, end), first one found (:273-281)
+// which on the flattened index is two searches and one gather, with no walk at all:
+//   successor   = chain rank ub(S, q.end)                       (first start past q.end; absent when == n_c)
+//   predecessor = ER[lb(E, v)],  v = E[ub(E, q.start - 1) - 1]  (largest end below q.start; ER = chain rank of each
+//                 sorted end, equal ends in chain order, so the first slot with end == v is the first one found)
+// Same directory + finger search as the count pass of intersect (intersect.cuh), QPT consecutive queries per thread.
+#pragma once
+#include "intersect.cuh"
+
+namespace gg {
+
+constexpr uint32_t kNoRank = 0xFFFFFFFFu;
+
+// inv[perm[g]] = g : concatenated chain rank of every input index (build-time helper for ER)
+__global__ void invert_perm_kernel(const uint32_t* __restrict__ perm, uint32_t* __restrict__ inv, size_t n) {
+    size_t g = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (g < n) inv[perm[g]] = static_cast<uint32_t>(g);
+}
+
+// ER[p - row0[0]] = per-chromosome chain rank of the interval whose end sits at sorted-end slot p (pads: kNoRank)
+__global__ void end_rank_kernel(const uint32_t* __restrict__ perm_end, const uint32_t* __restrict__ inv,
+                                const uint32_t* __restrict__ cbegin, const uint32_t* __restrict__ cnt,
+                                const uint32_t* __restrict__ row0, uint32_t n_chrom, uint32_t* __restrict__ ER) {
+    const uint32_t p = row0[0] + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= row0[n_chrom]) return;
+    uint32_t lo = 0, hi = n_chrom;
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (row0[mid] <= p) lo = mid; else hi = mid;
+    }
+    const uint32_t c = lo, r = p - row0[c];
+    ER[p - row0[0]] = r < cnt[c] ? inv[perm_end[cbegin[c] + r]] - cbegin[c] : kNoRank;
+}
+
+template <typename C, typename Q, int QPT>
+__global__ void __launch_bounds__(kQueryThreads)
+flanking_kernel(IndexView<C> ix, const uint32_t* __restrict__ ER, uint32_t er_base, const uint32_t* __restrict__ qchrom,
+                const Q* __restrict__ qstart, const Q* __restrict__ qend, size_t nq, uint32_t* __restrict__ pred_out,
+                uint32_t* __restrict__ succ_out, uint32_t* __restrict__ err_flag, int vec_ok) {
+    constexpr size_t kTileQ = static_cast<size_t>(kQueryThreads) * QPT;
+    const size_t n_tiles = (nq + kTileQ - 1) / kTileQ;
+    const int shift = ix.dir_shift;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t q0 = tile * kTileQ + static_cast<size_t>(threadIdx.x) * QPT;
+        const bool vec = vec_ok && q0 + QPT <= nq;
+        uint32_t chrom[QPT];
+        Q qs_raw[QPT], qe_raw[QPT];
+        if (vec) {
+            load_vec_stream<uint32_t, QPT>(qchrom + q0, chrom);
+            load_vec_stream<Q, QPT>(qstart + q0, qs_raw);
+            load_vec_stream<Q, QPT>(qend + q0, qe_raw);
+        } else {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j) {
+                const bool in = q0 + j < nq;
+                chrom[j] = in ? qchrom[q0 + j] : GG_NO_CHROM_DEV;
+                qs_raw[j] = in ? qstart[q0 + j] : Q(0);
+                qe_raw[j] = in ? qend[q0 + j] : Q(0);
+            }
+        }
+        // same per-warp choice of search flavour as count_group (results do not depend on it)
+        const Q e0 = qe_raw[0], e_lane0 = __shfl_sync(0xffffffffu, e0, 0);
+        const uint32_t c_lane0 = __shfl_sync(0xffffffffu, chrom[0], 0);
+        const bool same_area = (((e0 ^ e_lane0) >> (shift + 5)) == 0) & (chrom[0] == c_lane0);
+        const bool grouped = !__all_sync(0xffffffffu, same_area);
+
+        Finger<C> fs, fe;
+        uint32_t cur = GG_NO_CHROM_DEV, d0 = 0, last_bin = 0, leaf = 0, n_c = 0;
+        uint32_t pred[QPT], succ[QPT];
+        bool any_bad = false;
+#pragma unroll
+        for (int j = 0; j < QPT; ++j) {
+            pred[j] = succ[j] = kNoRank;
+            const bool bad = qs_raw[j] > qe_raw[j];
+            any_bad |= bad;
+            if (bad || chrom[j] >= ix.n_chrom) continue;  // unknown index -> empty result (grove_flanking.ipp)
+            if (chrom[j] != cur) {
+                cur = chrom[j];
+                d0 = ix.dir_off[cur];
+                last_bin = ix.dir_off[cur + 1] - d0 - 2;
+                leaf = ix.tab[cur];
+                n_c = ix.cnt[cur];
+                fs.valid = fe.valid = false;
+            }
+            // successor: first start past q.end (a query end beyond the index domain has none)
+            const uint32_t hi = finger_upper_bound<C>(ix.S + leaf, ix.dirS + d0, last_bin, shift, clamp_coord<C, Q>(qe_raw[j]), fs, grouped);
+            if (hi < n_c) succ[j] = hi;
+            // predecessor: largest end below q.start
+            if (qs_raw[j] == 0) continue;
+            const C x = clamp_coord<C, Q>(static_cast<Q>(qs_raw[j] - 1));
+            const uint32_t p = finger_upper_bound<C>(ix.E + leaf, ix.dirE + d0, last_bin, shift, x, fe, grouped);
+            if (p == 0) continue;
+            const C* __restrict__ ends = ix.E + leaf;
+            const C v = ends[p - 1];
+            uint32_t f = p - 1;
+            if (f != 0 && ends[f - 1] == v) {  // duplicated end value: its first slot is ub(E, v - 1) (slot 0 for v == 0)
+                if (v == 0) {
+                    f = 0;
+                } else {
+                    const C bx = static_cast<C>(v - 1) >> shift;
+                    const uint32_t b = bx > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(bx);
+                    f = bracket_upper_bound<C>(ends, ix.dirE[d0 + b], ix.dirE[d0 + b + 1], static_cast<C>(v - 1), grouped);
+                }
+            }
+            pred[j] = ER[leaf - er_base + f];
+        }
+        if (any_bad) atomicOr(err_flag, 1u);
+        if (vec) {
+            store_vec_u32<QPT>(pred_out + q0, pred);
+            store_vec_u32<QPT>(succ_out + q0, succ);
+        } else {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j) {
+                if (q0 + j < nq) {
+                    pred_out[q0 + j] = pred[j];
+                    succ_out[q0 + j] = succ[j];
+                }
+            }
+        }
+    }
+}
+
+}  // namespace gg

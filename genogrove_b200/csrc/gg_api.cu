@@ -14,6 +14,7 @@
 #include "build.cuh"
 #include "common.cuh"
 #include "emit_scan.cuh"
+#include "flanking.cuh"
 #include "fused.cuh"
 #include "intersect.cuh"
 #include "radix_sort.cuh"
@@ -79,6 +80,9 @@ struct gg_index {
     uint32_t staged_elems = 0;
     uint64_t total_elems = 0;
     DeviceBuf S, E, M, tab, cnt, dirS, dirE, dir_off;
+    DeviceBuf ER;           // chain rank of each sorted end (flanking.cuh), indexed by level-0 slot - er_base
+    uint32_t er_base = 0;   // = tab[0][0]
+    DeviceBuf cbegin;       // [n_chrom + 1] first concatenated chain rank of each chromosome
     int dir_shift = 0;
     uint64_t dir_entries = 0;
     std::vector<uint64_t> h_cnt;
@@ -96,6 +100,7 @@ struct gg_index {
 
     // ---- two-phase host API state
     DeviceBuf h2_qc, h2_qs, h2_qe, h2_off, h2_hits;
+    DeviceBuf fl_qc, fl_qs, fl_qe, fl_pred, fl_succ;  // gg_flanking_batch staging
     size_t h2_nq = 0;
     uint64_t h2_total = 0;
     bool h2_valid = false;
@@ -492,7 +497,8 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
 
     // temporaries (freed on every exit path by the guard)
     DeviceBuf d_chrom, d_start, d_end, d_tie, d_stats, d_perm, d_perm_alt, d_perm_end, d_perm_end_alt, d_keys_a, d_keys_b,
-        d_hist, d_scan, d_cbegin, d_s32, d_e32;
+        d_hist, d_scan, d_s32, d_e32, d_inv;
+    DeviceBuf& d_cbegin = idx->cbegin;  // kept: the flanking / stranded paths index per-rank side arrays with it
     struct Guard {
         std::vector<DeviceBuf*> bufs;
         std::vector<cudaEvent_t> evs;
@@ -502,7 +508,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
         }
     } guard;
     guard.bufs = {&d_chrom, &d_start, &d_end, &d_tie, &d_stats, &d_perm, &d_perm_alt, &d_perm_end, &d_perm_end_alt,
-                  &d_keys_a, &d_keys_b, &d_hist, &d_scan, &d_cbegin, &d_s32, &d_e32};
+                  &d_keys_a, &d_keys_b, &d_hist, &d_scan, &d_s32, &d_e32, &d_inv};
     guard.evs = {e0, e1, e2, e3};
 
     const size_t nn = n ? n : 1;
@@ -608,8 +614,9 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
         } else {
             iota_kernel<<<blocks_for(n, 256), 256, 0, st>>>(perm, n, 0);
         }
-        // ends sorted per chromosome (E family): sort input indices by (chrom, end)
-        iota_kernel<<<blocks_for(n, 256), 256, 0, st>>>(perm_end, n, 0);
+        // ends sorted per chromosome (E family): sort input indices by (chrom, end), starting from the chain order so
+        // that equal ends stay in chain order (the flanking predecessor is the FIRST key in the chain with that end)
+        GG_CUDA(cudaMemcpyAsync(perm_end, perm, n * 4, cudaMemcpyDeviceToDevice, st));
         if (wide)
             s = sort_by_field<uint64_t, uint64_t>(idx, d_end.as<uint64_t>(), coord_bits, d_keys_a.as<uint64_t>(), d_keys_b.as<uint64_t>(), perm_end, perm_end_alt, n, ws, st);
         else
@@ -634,6 +641,13 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
         pad_leaf_kernel<uint32_t><<<blocks_for(level0_elems, 256), 256, 0, st>>>(
             perm, perm_end, (const uint32_t*)src_s, (const uint32_t*)src_e, d_cbegin.as<uint32_t>(), idx->cnt.as<uint32_t>(),
             tab0, C, idx->S.as<uint32_t>(), idx->E.as<uint32_t>(), idx->M.as<uint32_t>());
+    // chain rank of every sorted end (ER) for the flanking path
+    idx->er_base = idx->h_tab[0];
+    GG_CUDA(idx->ER.ensure(static_cast<size_t>(level0_elems ? level0_elems : 1) * 4));
+    GG_CUDA(d_inv.ensure(nn * 4));
+    if (n) invert_perm_kernel<<<blocks_for(n, 256), 256, 0, st>>>(perm, d_inv.as<uint32_t>(), n);
+    end_rank_kernel<<<blocks_for(level0_elems, 256), 256, 0, st>>>(perm_end, d_inv.as<uint32_t>(), d_cbegin.as<uint32_t>(),
+                                                                   idx->cnt.as<uint32_t>(), tab0, C, idx->ER.as<uint32_t>());
     for (int l = 1; l < idx->n_levels; ++l) {
         const uint32_t* row = tab0 + static_cast<size_t>(l) * (C + 1);
         const uint32_t* row_below = tab0 + static_cast<size_t>(l - 1) * (C + 1);
@@ -706,7 +720,8 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     idx->istats.n_levels = idx->n_levels;
     idx->istats.fanout = kFanout;
     idx->istats.staged_levels = idx->n_levels - idx->stage_level;
-    idx->istats.device_bytes = 3 * fam_bytes + idx->h_tab.size() * 4 + static_cast<size_t>(C) * 4 + idx->dir_entries * 8;
+    idx->istats.device_bytes = 3 * fam_bytes + idx->h_tab.size() * 4 + static_cast<size_t>(C) * 4 + idx->dir_entries * 8 +
+                               static_cast<size_t>(level0_elems) * 4;
     idx->istats.sort_ms = ms_sort;
     idx->istats.levels_ms = ms_levels;
     idx->istats.total_ms = ms_total;
@@ -1014,7 +1029,8 @@ void gg_index_destroy(gg_index* idx) {
     cudaSetDevice(idx->device);
     cudaDeviceSynchronize();
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
-                         &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base})
+                         &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
+                         &idx->ER, &idx->cbegin, &idx->fl_qc, &idx->fl_qs, &idx->fl_qe, &idx->fl_pred, &idx->fl_succ})
         b->release();
     for (auto& s : idx->slots) {
         for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan, &s.fscratch, &s.err}) b->release();
@@ -1286,6 +1302,90 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "timing") idx->timing = value != 0;
     else return fail(idx, GG_ERR_INVALID_ARG, "unknown option or value out of range");
     return GG_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------ flanking
+
+namespace {
+template <typename C, typename Q>
+gg_status launch_flanking(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, size_t nq,
+                          uint32_t* d_pred, uint32_t* d_succ, uint32_t* d_err, cudaStream_t st) {
+    if (nq == 0) return GG_OK;
+    constexpr int QPT = 4;
+    const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end) && aligned16(d_pred) && aligned16(d_succ);
+    int per_sm = 0;
+    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, flanking_kernel<C, Q, QPT>, kQueryThreads, 0));
+    const size_t tiles = div_up(nq, static_cast<size_t>(kQueryThreads) * QPT);
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
+    flanking_kernel<C, Q, QPT><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->ER.as<uint32_t>(), idx->er_base, d_chrom,
+                                                              d_start, d_end, nq, d_pred, d_succ, d_err, vec_ok);
+    GG_CUDA(cudaGetLastError());
+    return GG_OK;
+}
+
+gg_status dispatch_flanking(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, int q_bytes,
+                            size_t nq, uint32_t* d_pred, uint32_t* d_succ, uint32_t* d_err, cudaStream_t st) {
+    if (idx->coord_bytes == 8)
+        return launch_flanking<uint64_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start),
+                                                   static_cast<const uint64_t*>(d_end), nq, d_pred, d_succ, d_err, st);
+    if (q_bytes == 8)
+        return launch_flanking<uint32_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start),
+                                                   static_cast<const uint64_t*>(d_end), nq, d_pred, d_succ, d_err, st);
+    return launch_flanking<uint32_t, uint32_t>(idx, d_chrom, static_cast<const uint32_t*>(d_start),
+                                               static_cast<const uint32_t*>(d_end), nq, d_pred, d_succ, d_err, st);
+}
+}  // namespace
+
+extern "C" {
+
+gg_status gg_flanking_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                             int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync, void* stream) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (nq && (!d_chrom || !d_start || !d_end || !d_pred || !d_succ)) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
+    if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    GG_CUDA(idx->err_flag.ensure(16));
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    gg_status s = dispatch_flanking(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_pred, d_succ, idx->err_flag.as<uint32_t>(), st);
+    if (s != GG_OK) return s;
+    return sync ? check_query_error(idx, st) : GG_OK;
+}
+
+gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                            size_t nq, uint32_t* pred, uint32_t* succ) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (nq && (!q_chrom || !q_start || !q_end || !pred || !succ)) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    GG_CUDA(idx->err_flag.ensure(16));
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    const size_t chunk = static_cast<size_t>(std::max<int64_t>(idx->chunk_queries, 1024));
+    const size_t cap = std::min(chunk, nq ? nq : 1);
+    GG_CUDA(idx->fl_qc.ensure(cap * 4));
+    GG_CUDA(idx->fl_qs.ensure(cap * 8));
+    GG_CUDA(idx->fl_qe.ensure(cap * 8));
+    GG_CUDA(idx->fl_pred.ensure(cap * 4));
+    GG_CUDA(idx->fl_succ.ensure(cap * 4));
+    for (size_t q0 = 0; q0 < nq; q0 += chunk) {
+        const size_t m = std::min(chunk, nq - q0);
+        GG_CUDA(cudaMemcpyAsync(idx->fl_qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->fl_qs.p, q_start + q0, m * 8, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->fl_qe.p, q_end + q0, m * 8, cudaMemcpyHostToDevice, st));
+        gg_status s = dispatch_flanking(idx, idx->fl_qc.as<uint32_t>(), idx->fl_qs.p, idx->fl_qe.p, 8, m,
+                                        idx->fl_pred.as<uint32_t>(), idx->fl_succ.as<uint32_t>(), idx->err_flag.as<uint32_t>(), st);
+        if (s != GG_OK) return s;
+        GG_CUDA(cudaMemcpyAsync(pred + q0, idx->fl_pred.p, m * 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(succ + q0, idx->fl_succ.p, m * 4, cudaMemcpyDeviceToHost, st));
+    }
+    return check_query_error(idx, st);  // synchronises the stream
 }
 
 }  // extern "C"

@@ -31,7 +31,7 @@ from typing import Any, Iterable, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from .index import DeviceIndex, NO_CHROM, TIE_INPUT_ORDER
+from .index import DeviceIndex, NO_CHROM, NO_RANK, TIE_INPUT_ORDER
 
 
 class Interval:
@@ -102,6 +102,22 @@ class QueryResult:
         if key is None:
             raise ValueError("query_result::add_key: key must not be nullptr")
         self.keys.append(key)
+
+
+class FlankingQueryResult:
+    """flanking_query_result<key_t, data_t>: borrowed nearest predecessor / successor, None when absent
+    (data_type/flanking_query_result.hpp)."""
+
+    __slots__ = ("predecessor", "successor")
+
+    def __init__(self, predecessor: Optional[Key] = None, successor: Optional[Key] = None):
+        self.predecessor, self.successor = predecessor, successor
+
+    def get_predecessor(self) -> Optional[Key]:
+        return self.predecessor
+
+    def get_successor(self) -> Optional[Key]:
+        return self.successor
 
 
 class _Chain:
@@ -264,6 +280,23 @@ class Grove:
         """The new batch entry point: CSR (offsets u64[Q+1], per-chromosome chain ranks u32[H])."""
         self._sync()
         return self._dev.intersect_batch(chrom_ids, starts, ends)
+
+    def flanking(self, query: Interval, index: str) -> FlankingQueryResult:
+        """grove::flanking(query, index) with the default predicate (grove_flanking.ipp): a flanking batch of one."""
+        self._sync()
+        cid = self.chrom_id(index)
+        if cid == NO_CHROM:
+            return FlankingQueryResult()
+        pred, succ = self._dev.flanking_batch(np.array([cid], np.uint32), np.array([query.start], np.uint64),
+                                              np.array([query.end], np.uint64))
+        keys = self._chains[self._names[cid]].keys
+        return FlankingQueryResult(None if int(pred[0]) == NO_RANK else keys[int(pred[0])],
+                                   None if int(succ[0]) == NO_RANK else keys[int(succ[0])])
+
+    def flanking_batch(self, chrom_ids, starts, ends):
+        """Batch form: (pred u32[Q], succ u32[Q]) per-chromosome chain ranks, NO_RANK when absent."""
+        self._sync()
+        return self._dev.flanking_batch(chrom_ids, starts, ends)
 
     def keys_at(self, chrom_id: int, ranks: Iterable[int]) -> List[Key]:
         keys = self._chains[self._names[chrom_id]].keys

@@ -10,7 +10,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import GGError, IndexStats, BatchStats, NO_CHROM, TIE_EXPLICIT, TIE_INPUT_ORDER, TIE_REVERSE_INPUT  # noqa: F401
+from ._lib import GGError, IndexStats, BatchStats, NO_CHROM, NO_RANK, TIE_EXPLICIT, TIE_INPUT_ORDER, TIE_REVERSE_INPUT  # noqa: F401
 
 
 def _ptr(a):
@@ -155,3 +155,18 @@ class DeviceIndex:
         self.last_total = int(total.value) if sync_total else None
         self._check(st)
         return self.last_total
+
+    # ------------------------------------------------------------------ flanking (nearest predecessor / successor)
+    def flanking_batch(self, q_chrom, q_start, q_end):
+        """gg_flanking_batch: (pred u32[Q], succ u32[Q]) per-chromosome chain ranks, NO_RANK when absent."""
+        qc, a, b = _arr(q_chrom, np.uint32), _arr(q_start, np.uint64), _arr(q_end, np.uint64)
+        nq = len(qc)
+        pred = np.empty(nq, dtype=np.uint32)
+        succ = np.empty(nq, dtype=np.uint32)
+        self._check(self._L.gg_flanking_batch(self._h, _ptr(qc), _ptr(a), _ptr(b), nq, _ptr(pred), _ptr(succ)))
+        return pred, succ
+
+    def flanking_device(self, d_chrom: int, d_start: int, d_end: int, coord_bytes: int, nq: int, d_pred: int,
+                        d_succ: int, stream: int = 0, sync: bool = True):
+        self._check(self._L.gg_flanking_device(self._h, d_chrom, d_start, d_end, coord_bytes, nq, d_pred, d_succ,
+                                               1 if sync else 0, stream or None))

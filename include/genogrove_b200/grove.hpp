@@ -163,6 +163,22 @@ class query_result {
     std::vector<key<key_t, data_t>*> keys;
 };
 
+/// Nearest non-overlapping predecessor / successor of a flanking query; borrowed pointers, nullptr when absent
+/// (same members as genogrove's data_type/flanking_query_result.hpp).
+template <typename key_t, typename data_t = void>
+class flanking_query_result {
+  public:
+    flanking_query_result() = default;
+    [[nodiscard]] key<key_t, data_t>* get_predecessor() const noexcept { return predecessor; }
+    [[nodiscard]] key<key_t, data_t>* get_successor() const noexcept { return successor; }
+    void set_predecessor(key<key_t, data_t>* k) noexcept { predecessor = k; }
+    void set_successor(key<key_t, data_t>* k) noexcept { successor = k; }
+
+  private:
+    key<key_t, data_t>* predecessor = nullptr;
+    key<key_t, data_t>* successor = nullptr;
+};
+
 }  // namespace data_type
 
 namespace structure {
@@ -412,6 +428,30 @@ class grove {
             qe[i] = queries[i].get_end();
         }
         return intersect_batch(qc.data(), qs.data(), qe.data(), queries.size());
+    }
+
+    /// grove::flanking(query, index) with the default (always compatible) predicate, grove_flanking.ipp: nearest
+    /// non-overlapping predecessor (largest end below query.start, first such key in the chain) and successor (first
+    /// key starting past query.end).  One gg_flanking_batch call of one query.
+    [[nodiscard]] gdt::flanking_query_result<key_type, data_type> flanking(const key_type& query, std::string_view index) {
+        gdt::flanking_query_result<key_type, data_type> result{};
+        auto it = indices.find(index);
+        if (it == indices.end()) return result;  // null root: empty pair
+        sync();
+        const std::uint32_t c = it->second.id;
+        const std::uint64_t s = query.get_start(), e = query.get_end();
+        std::uint32_t pred = GG_NO_RANK, succ = GG_NO_RANK;
+        check(gg_flanking_batch(dev.get(), &c, &s, &e, 1, &pred, &succ));
+        if (pred != GG_NO_RANK) result.set_predecessor(it->second.chain[pred]);
+        if (succ != GG_NO_RANK) result.set_successor(it->second.chain[succ]);
+        return result;
+    }
+
+    /// NEW: batch form.  pred[i] / succ[i] = chain rank in index q_index[i] (see chain()), GG_NO_RANK when absent.
+    void flanking_batch(const std::uint32_t* q_index, const std::uint64_t* q_start, const std::uint64_t* q_end, std::size_t nq,
+                        std::uint32_t* pred, std::uint32_t* succ) {
+        sync();
+        check(gg_flanking_batch(dev.get(), q_index, q_start, q_end, nq, pred, succ));
     }
 
     /// Leaf chain of one index as the device sees it (rank -> key*); empty when the index does not exist.

@@ -23,6 +23,11 @@
  *                                include/genogrove/structure/grove/query_engine.hpp:76-134
  *                                with query_result::add_key (data_type/query_result.hpp:108-113)
  *                                replaced by CSR output: offsets[Q+1] (u64) + hits[H] (u32 ranks)
+ *   gg_flanking_*             <- grove::flanking(query, index) -> detail::search_flanking
+ *                                include/genogrove/structure/grove/grove_flanking.ipp
+ *                                include/genogrove/structure/grove/query_engine.hpp:176-199, 238-311
+ *                                flanking_query_result (data_type/flanking_query_result.hpp) replaced by two
+ *                                u32 chain ranks per query (GG_NO_RANK = null pointer)
  *   q_chrom (u32 id)          <- grove::get_root(index) hash lookup, grove.hpp:234-236; an id of
  *                                GG_NO_CHROM (or >= n_chrom) yields zero hits, like an unknown index
  *                                name does in grove_query.ipp:37-39
@@ -45,6 +50,7 @@ extern "C" {
 
 #define GG_B200_VERSION 100 /* 0.1.0 */
 #define GG_NO_CHROM 0xFFFFFFFFu
+#define GG_NO_RANK 0xFFFFFFFFu /* "no such key": absent predecessor / successor of a flanking query */
 
 typedef struct gg_index gg_index;
 
@@ -158,6 +164,22 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
                                     const void* d_end, int coord_bytes, size_t nq, uint64_t* d_offsets,
                                     uint32_t* d_hits, uint64_t capacity, uint64_t* total_hits, void* stream);
 gg_status gg_last_batch_stats(const gg_index* idx, gg_batch_stats* out);
+
+/* ---- batched flanking (nearest predecessor / successor) ------------------------------------------ */
+/* Replaces grove::flanking(query, index) -> detail::search_flanking for interval keys with the default
+ * predicate (include/genogrove/structure/grove/grove_flanking.ipp; query_engine.hpp:238-311):
+ *   succ[i] = chain rank of the first key (in leaf-chain order) whose start > q.end,
+ *   pred[i] = chain rank of the first key in the chain among those with the largest end < q.start
+ *             (nested intervals: the largest END wins, not the sort-order maximum, query_engine.hpp:256-272),
+ * GG_NO_RANK when there is none (also for q_chrom == GG_NO_CHROM / unknown id: empty result, like the
+ * reference's null root).  Overlapping keys are never reported.  Host buffers, nq entries each. */
+gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start,
+                            const uint64_t* q_end, size_t nq, uint32_t* pred, uint32_t* succ);
+/* Device buffers (d_start / d_end element width = coord_bytes as for the intersect calls).  sync != 0: wait and
+ * report GG_ERR_INVALID_INTERVAL for a query with start > end; sync == 0: enqueue only. */
+gg_status gg_flanking_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                             int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync,
+                             void* stream);
 
 /* ---- pinned host memory helpers ------------------------------------------------------------------ */
 gg_status gg_host_alloc(void** out, size_t bytes);

@@ -76,6 +76,9 @@ def oracle_lib():
         L.orc_chain_stable_sort.argtypes = [_u64p, _u64p, C.c_size_t, _u32p]
         L.orc_flat_intersect_batch.argtypes = [_u64p, _u64p, _u64p, C.c_uint32, _u32p, _u64p, _u64p,
                                                C.c_size_t, _u64p, _u64p, _u32p]
+        L.orc_tree_search_flanking.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _u64p]
+        L.orc_flat_flanking_batch.argtypes = [_u64p, _u64p, _u64p, C.c_uint32, _u32p, _u64p, _u64p, C.c_size_t,
+                                              _u32p, _u32p]
         _oracle = L
     return _oracle
 
@@ -107,6 +110,7 @@ def ref_lib():
             getattr(L, name).restype = C.c_int
         L.ref_distribute_evenly.argtypes = [C.c_uint64, C.c_uint64, _u64p]
         L.ref_hardware_threads.restype = C.c_int
+        L.ref_flanking_batch.argtypes = [C.c_void_p, _u32p, _u64p, _u64p, C.c_size_t, _u32p, _u32p]
         _ref = L
     return _ref
 
@@ -140,6 +144,13 @@ class OracleTree:
             if k <= cap:
                 return out[:k]
             cap = k
+
+    def flanking(self, qs: int, qe: int):
+        """(predecessor rank, successor rank) by the restated search_flanking; None when absent."""
+        out = np.zeros(2, dtype=np.uint64)
+        self._L.orc_tree_search_flanking(self._t, qs, qe, _p64(out))
+        none = 0xFFFFFFFFFFFFFFFF
+        return tuple(None if int(v) == none else int(v) for v in out)
 
     def __del__(self):
         if getattr(self, "_t", None):
@@ -184,6 +195,23 @@ def flat_intersect_batch(start, end, coff, qchrom, qs, qe):
     L.orc_flat_intersect_batch(_p64(s), _p64(e), _p64(co), len(co) - 1, _p32(qc), _p64(a), _p64(b), nq,
                                None, _p64(offsets), _p32(out))
     return offsets, out[: int(offsets[-1])]
+
+
+NO_RANK = 0xFFFFFFFF
+
+
+def flat_flanking_batch(start, end, coff, qchrom, qs, qe):
+    """Flat flanking oracle over concatenated per-chromosome chains: (pred u32[Q], succ u32[Q]) per-chromosome
+    chain ranks, NO_RANK when absent."""
+    L = oracle_lib()
+    s, e, co = _u64(start), _u64(end), _u64(coff)
+    qc, a, b = _u32(qchrom), _u64(qs), _u64(qe)
+    nq = len(qc)
+    pred = np.zeros(nq, dtype=np.uint32)
+    succ = np.zeros(nq, dtype=np.uint32)
+    L.orc_flat_flanking_batch(_p64(s), _p64(e), _p64(co), len(co) - 1, _p32(qc), _p64(a), _p64(b), nq,
+                              _p32(pred), _p32(succ))
+    return pred, succ
 
 
 # ----------------------------------------------------------------------------- the real reference
@@ -237,6 +265,14 @@ class RefGrove:
         self._L.ref_intersect_batch(self._g, _p32(qc), _p64(a), _p64(b), nq, threads, None, _p64(offsets),
                                     _p32(ids), C.byref(chk))
         return offsets, ids[: int(offsets[-1])], secs
+
+    def flanking_batch(self, qchrom, qs, qe):
+        """grove.flanking(q, chrom) per query: (pred ids, succ ids), NO_RANK when absent."""
+        qc, a, b = _u32(qchrom), _u64(qs), _u64(qe)
+        pred = np.zeros(len(qc), dtype=np.uint32)
+        succ = np.zeros(len(qc), dtype=np.uint32)
+        self._L.ref_flanking_batch(self._g, _p32(qc), _p64(a), _p64(b), len(qc), _p32(pred), _p32(succ))
+        return pred, succ
 
     def hardware_threads(self) -> int:
         return int(self._L.ref_hardware_threads())

@@ -301,3 +301,114 @@ void orc_flat_intersect_batch(const uint64_t* start, const uint64_t* end, const 
     }
     free(pmax);
 }
+
+/* ---------------------------------------------------------------- flanking (nearest predecessor / successor) */
+
+/* detail::flanking_could_descend, interval branch  (query_engine.hpp:176-199).  have_* / best_* = the
+ * state's current predecessor end and successor start. */
+static int flank_could_descend(uint64_t as, uint64_t ae, uint64_t qs, uint64_t qe, int have_pred,
+                               uint64_t pred_end, int have_succ, uint64_t succ_start) {
+    int could_pred = as < qs;
+    if (could_pred && have_pred) could_pred = ae > pred_end;
+    int could_succ = ae > qe;
+    if (could_succ && have_succ) could_succ = as < succ_start;
+    return could_pred || could_succ;
+}
+
+typedef struct {
+    int have_pred, have_succ;
+    uint64_t pred, succ; /* chain ranks */
+} flank_state;
+
+/* detail::search_flanking (query_engine.hpp:238-311) on the array tree; default predicate (always
+ * compatible, grove_flanking.ipp).  In the reference children 0..k-1 are pruned with the node's own
+ * separator keys and the last child with subtree_range(child) (:296-307): both are the child's full
+ * bounding box, which is what rs/re hold for every child here. */
+static void flank_rec(const orc_tree* t, int l, size_t node, uint64_t qs, uint64_t qe, flank_state* st) {
+    if (l == 0) {
+        const orc_level* L = &t->lv[0];
+        for (size_t r = L->first[node]; r < L->first[node + 1]; ++r) {
+            uint64_t ks = t->start[r], ke = t->end[r];
+            if (orc_overlaps(ks, ke, qs, qe)) continue;            /* :254 */
+            if (orc_less(ks, ke, qs, qe)) {                        /* :256-272: largest END wins, strictly */
+                if (!st->have_pred || ke > t->end[st->pred]) {
+                    st->have_pred = 1;
+                    st->pred = r;
+                }
+            } else if (orc_greater(ks, ke, qs, qe)) {              /* :273-281: smallest key wins, strictly */
+                if (!st->have_succ || orc_less(ks, ke, t->start[st->succ], t->end[st->succ])) {
+                    st->have_succ = 1;
+                    st->succ = r;
+                }
+            }
+        }
+        return;
+    }
+    const orc_level* P = &t->lv[l];
+    const orc_level* C = &t->lv[l - 1];
+    for (size_t c = P->first[node]; c < P->first[node + 1]; ++c) { /* :287-309 */
+        if (flank_could_descend(C->rs[c], C->re[c], qs, qe, st->have_pred,
+                                st->have_pred ? t->end[st->pred] : 0, st->have_succ,
+                                st->have_succ ? t->start[st->succ] : 0))
+            flank_rec(t, l - 1, c, qs, qe, st);
+    }
+}
+
+#define ORC_NO_RANK 0xFFFFFFFFFFFFFFFFull
+/* out2[0] = predecessor chain rank, out2[1] = successor chain rank (ORC_NO_RANK when absent). */
+void orc_tree_search_flanking(const orc_tree* t, uint64_t qs, uint64_t qe, uint64_t* out2) {
+    flank_state st = {0, 0, 0, 0};
+    if (t) flank_rec(t, t->n_levels - 1, 0, qs, qe, &st); /* null root -> empty result (grove_flanking.ipp) */
+    out2[0] = st.have_pred ? st.pred : ORC_NO_RANK;
+    out2[1] = st.have_succ ? st.succ : ORC_NO_RANK;
+}
+
+/* Flat statement of the same answer over concatenated chains (what the device computes):
+ *   successor   = first chain rank with start > q.end
+ *   predecessor = first chain rank among those whose end is the largest end < q.start
+ * pred/succ receive per-chromosome ranks, 0xFFFFFFFF when absent (also for an unknown chromosome). */
+typedef struct { uint64_t end; uint64_t rank; } end_rank;
+static int cmp_end_rank(const void* a, const void* b) {
+    const end_rank* x = (const end_rank*)a;
+    const end_rank* y = (const end_rank*)b;
+    if (x->end != y->end) return x->end < y->end ? -1 : 1;
+    return x->rank < y->rank ? -1 : (x->rank > y->rank ? 1 : 0);
+}
+void orc_flat_flanking_batch(const uint64_t* start, const uint64_t* end, const uint64_t* coff,
+                             uint32_t n_chrom, const uint32_t* qchrom, const uint64_t* qs,
+                             const uint64_t* qe, size_t nq, uint32_t* pred, uint32_t* succ) {
+    uint64_t n = coff[n_chrom];
+    end_rank* er = (end_rank*)malloc((n ? n : 1) * sizeof(end_rank));
+    for (uint32_t c = 0; c < n_chrom; ++c) {
+        for (uint64_t r = coff[c]; r < coff[c + 1]; ++r) {
+            er[r].end = end[r];
+            er[r].rank = r - coff[c];
+        }
+        qsort(er + coff[c], coff[c + 1] - coff[c], sizeof(end_rank), cmp_end_rank);
+    }
+    for (size_t i = 0; i < nq; ++i) {
+        pred[i] = succ[i] = 0xFFFFFFFFu;
+        if (qchrom[i] >= n_chrom || qs[i] > qe[i]) continue;
+        uint64_t b = coff[qchrom[i]], t = coff[qchrom[i] + 1];
+        uint64_t lo = b, hi = t;
+        while (lo < hi) { /* first rank with start > q.end */
+            uint64_t mid = lo + (hi - lo) / 2;
+            if (start[mid] <= qe[i]) lo = mid + 1; else hi = mid;
+        }
+        if (lo < t) succ[i] = (uint32_t)(lo - b);
+        lo = b; hi = t;
+        while (lo < hi) { /* number of ends < q.start */
+            uint64_t mid = lo + (hi - lo) / 2;
+            if (er[mid].end < qs[i]) lo = mid + 1; else hi = mid;
+        }
+        if (lo > b) {
+            uint64_t v = er[lo - 1].end, l2 = b, h2 = lo;
+            while (l2 < h2) { /* first (end == v): smallest chain rank with that end */
+                uint64_t mid = l2 + (h2 - l2) / 2;
+                if (er[mid].end < v) l2 = mid + 1; else h2 = mid;
+            }
+            pred[i] = (uint32_t)er[l2].rank;
+        }
+    }
+    free(er);
+}

@@ -14,6 +14,7 @@
 //   grove::insert_data(idx, vec, bulk)                 grove_insert.ipp:160-172
 //   grove::intersect(q, idx) / intersect(q)            grove_query.ipp:16-43
 //   grove::remove_key(idx, key*)                       grove_remove.ipp:24-62
+//   grove::flanking(q, idx)                            grove_flanking.ipp -> detail::search_flanking query_engine.hpp:238-311
 #include <atomic>
 #include <chrono>
 #include <cstdint>
@@ -156,6 +157,19 @@ double ref_intersect_batch(ref_grove* r, const uint32_t* qchrom, const uint64_t*
     for (auto v : sums) s += v;
     if (checksum) *checksum = s;
     return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// Batch of grove.flanking(q, chrom): payload id of the nearest predecessor / successor, 0xFFFFFFFF when absent
+// (null pointer in flanking_query_result, also for an unknown index name).
+void ref_flanking_batch(ref_grove* r, const uint32_t* qchrom, const uint64_t* qs, const uint64_t* qe, size_t nq,
+                        uint32_t* pred_ids, uint32_t* succ_ids) {
+    static const std::string missing = "\x01<no such index>";
+    for (size_t i = 0; i < nq; ++i) {
+        gdt::interval q(qs[i], qe[i]);
+        auto res = r->g.flanking(q, qchrom[i] == 0xFFFFFFFFu ? missing : r->name(qchrom[i]));
+        pred_ids[i] = res.get_predecessor() ? res.get_predecessor()->get_data() : 0xFFFFFFFFu;
+        succ_ids[i] = res.get_successor() ? res.get_successor()->get_data() : 0xFFFFFFFFu;
+    }
 }
 
 // known-answer helpers for interval arithmetic (interval.hpp:87-105,140-157)

@@ -500,6 +500,80 @@ void scenario_random(trace_t& t) {
     }
 }
 
+// flanking (nearest predecessor / successor): grove_flanking_test.cpp:20-117 restated + random groves with duplicated
+// and nested keys through three insert paths; the trace carries the payloads, so ties must resolve the same way
+template <typename A>
+void scenario_flanking(trace_t& t) {
+    using interval = typename A::interval;
+    auto line = [&](const char* tag, auto& g, std::size_t a, std::size_t b, const char* index) {
+        auto nn = g.flanking(interval(a, b), index);
+        std::ostringstream os;
+        os << tag << " q=[" << a << ',' << b << "] pred=";
+        if (nn.get_predecessor()) os << nn.get_predecessor()->get_data(); else os << "null";
+        os << " succ=";
+        if (nn.get_successor()) os << nn.get_successor()->get_data(); else os << "null";
+        t.push_back(os.str());
+        return nn;
+    };
+    {
+        typename A::template grove<int> g(8);
+        auto nn = line("flank_empty", g, 100, 200, "chr1");
+        CHECK(nn.get_predecessor() == nullptr && nn.get_successor() == nullptr);
+        auto* far_pred = g.insert_data("chr1", interval(50, 60), 2, A::sorted);
+        g.insert_data("chr1", interval(100, 350), 1, A::sorted);
+        auto* far_succ = g.insert_data("chr1", interval(500, 600), 3, A::sorted);
+        nn = line("flank_skip_overlap", g, 300, 400, "chr1");
+        CHECK(nn.get_predecessor() == far_pred && nn.get_successor() == far_succ);
+        nn = line("flank_missing_index", g, 300, 400, "chr2");
+        CHECK(nn.get_predecessor() == nullptr && nn.get_successor() == nullptr);
+    }
+    {
+        typename A::template grove<int> g(8);
+        auto* outer = g.insert_data("chr1", interval(50, 100), 1, A::sorted);
+        g.insert_data("chr1", interval(80, 90), 2, A::sorted);
+        auto nn = line("flank_nested", g, 200, 300, "chr1");
+        CHECK(nn.get_predecessor() == outer);
+        auto* lhs = g.insert_data("chr1", interval(120, 199), 3, A::sorted);
+        auto* rhs = g.insert_data("chr1", interval(301, 400), 4, A::sorted);
+        nn = line("flank_abutting", g, 200, 300, "chr1");
+        CHECK(nn.get_predecessor() == lhs && nn.get_successor() == rhs);
+    }
+    {
+        typename A::template grove<int> g(4);
+        for (std::size_t i = 0; i < 16; ++i) g.insert_data("chr1", interval(i * 100, i * 100 + 20), int(i), A::sorted);
+        auto nn = line("flank_multi_leaf", g, 440, 460, "chr1");
+        CHECK(nn.get_predecessor() && nn.get_predecessor()->get_value().get_end() == 420u);
+        CHECK(nn.get_successor() && nn.get_successor()->get_value().get_start() == 500u);
+    }
+    std::mt19937_64 rng(777);
+    for (int round = 0; round < 6; ++round) {
+        const int order = round % 3 == 0 ? 3 : (round % 3 == 1 ? 8 : 40);
+        typename A::template grove<int> g(order);
+        items_t items;
+        const int n = 400 + 300 * round;
+        for (int i = 0; i < n; ++i) {
+            std::size_t s = (rng() % 30000) / 16 * 16;
+            std::size_t len = (rng() % 40 == 0) ? 5000 + rng() % 9000 : (rng() % 300) / 32 * 32;
+            items.push_back({{s, s + len}, i});
+        }
+        const mode m = round % 3 == 0 ? mode::regular : (round % 3 == 1 ? mode::sorted_bulk : mode::sorted_single);
+        load<A>(g, "c", m == mode::regular ? items : sorted_copy(items), m);
+        for (int k = 0; k < 250; ++k) {
+            std::size_t a = rng() % 46000, b = a + rng() % 500;
+            auto nn = line("flank_rand", g, a, b, "c");
+            // brute force on the test's own data: largest end below a, smallest start above b
+            std::size_t best_end = 0, best_start = 0;
+            bool hp = false, hs = false;
+            for (const auto& [iv, id] : items) {
+                if (iv.second < a && (!hp || iv.second > best_end)) { hp = true; best_end = iv.second; }
+                if (iv.first > b && (!hs || iv.first < best_start)) { hs = true; best_start = iv.first; }
+            }
+            CHECK((nn.get_predecessor() != nullptr) == hp && (!hp || nn.get_predecessor()->get_value().get_end() == best_end));
+            CHECK((nn.get_successor() != nullptr) == hs && (!hs || nn.get_successor()->get_value().get_start() == best_start));
+        }
+    }
+}
+
 template <typename A>
 trace_t run_scenarios() {
     trace_t t;
@@ -512,6 +586,7 @@ trace_t run_scenarios() {
     scenario_order_pinned<A>(t);
     scenario_tie_order<A>(t);
     scenario_random<A>(t);
+    scenario_flanking<A>(t);
     return t;
 }
 
