@@ -35,6 +35,7 @@ EXPORTS = (
     "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_last_batch_stats",
     "gg_host_alloc", "gg_host_free", "gg_set_option",
     "gg_flanking_batch", "gg_flanking_device",
+    "gg_index_set_strands", "gg_intersect_batch_stranded", "gg_intersect_stranded_device",
 )
 
 
@@ -100,6 +101,9 @@ def lib():
     L.gg_host_free.argtypes = [vp]
     L.gg_host_free.restype = None
     L.gg_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.gg_index_set_strands.argtypes = [vp, vp, C.c_size_t]
+    L.gg_intersect_batch_stranded.argtypes = [vp, vp, vp, vp, vp, C.c_size_t, vp, C.POINTER(_u32p), _u64p]
+    L.gg_intersect_stranded_device.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_uint64, _u64p, vp]
     L.gg_flanking_batch.argtypes = [vp, vp, vp, vp, C.c_size_t, vp, vp]
     L.gg_flanking_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_int, vp]
     _lib = L

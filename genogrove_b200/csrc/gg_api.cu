@@ -19,6 +19,7 @@
 #include "intersect.cuh"
 #include "radix_sort.cuh"
 #include "scan.cuh"
+#include "strand.cuh"
 
 using namespace gg;
 
@@ -101,6 +102,10 @@ struct gg_index {
     // ---- two-phase host API state
     DeviceBuf h2_qc, h2_qs, h2_qe, h2_off, h2_hits;
     DeviceBuf fl_qc, fl_qs, fl_qe, fl_pred, fl_succ;  // gg_flanking_batch staging
+    DeviceBuf strand;        // u8 per concatenated chain rank ('+', '-', '.', '*'), gg_index_set_strands
+    bool has_strand = false;
+    DeviceBuf sq_qc, sq_qs, sq_qe, sq_str, sq_off, sq_hits;  // gg_intersect_batch_stranded staging
+    DeviceBuf s_cnt, s_hi, s_scan, s_total;                   // stranded path scratch (device calls too)
     size_t h2_nq = 0;
     uint64_t h2_total = 0;
     bool h2_valid = false;
@@ -481,6 +486,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     if (!idx) return GG_ERR_INVALID_ARG;
     idx->err.clear();
     idx->built = false;
+    idx->has_strand = false;
     idx->h2_valid = false;
     if (n_chrom == 0 || n_chrom == GG_NO_CHROM) return fail(idx, GG_ERR_INVALID_ARG, "n_chrom must be in [1, 2^32-2]");
     if (n > 0 && (!chrom || !start || !end)) return fail(idx, GG_ERR_INVALID_ARG, "null input array");
@@ -1030,7 +1036,8 @@ void gg_index_destroy(gg_index* idx) {
     cudaDeviceSynchronize();
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
-                         &idx->ER, &idx->cbegin, &idx->fl_qc, &idx->fl_qs, &idx->fl_qe, &idx->fl_pred, &idx->fl_succ})
+                         &idx->ER, &idx->cbegin, &idx->strand, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
+                         &idx->s_cnt, &idx->s_hi, &idx->s_scan, &idx->s_total, &idx->fl_qc, &idx->fl_qs, &idx->fl_qe, &idx->fl_pred, &idx->fl_succ})
         b->release();
     for (auto& s : idx->slots) {
         for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan, &s.fscratch, &s.err}) b->release();
@@ -1386,6 +1393,199 @@ gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64
         GG_CUDA(cudaMemcpyAsync(succ + q0, idx->fl_succ.p, m * 4, cudaMemcpyDeviceToHost, st));
     }
     return check_query_error(idx, st);  // synchronises the stream
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------ stranded intersect
+
+namespace {
+template <typename C, typename Q>
+gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, const uint8_t* d_strand,
+                          size_t nq, uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, uint64_t hits_base,
+                          const uint64_t* d_base, uint64_t* d_total, uint32_t* d_err, bool emit_only, cudaStream_t st) {
+    const size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads));
+    if (!emit_only) {
+        int per_sm = 0;
+        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, strand_count_kernel<C, Q>, kQueryThreads, 0));
+        const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
+        if (nq)
+            strand_count_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(),
+                                                                     idx->cbegin.as<uint32_t>(), d_chrom, d_start, d_end, d_strand,
+                                                                     nq, idx->s_cnt.as<uint32_t>(), idx->s_hi.as<uint32_t>(), d_err);
+        GG_CUDA(cudaGetLastError());
+        GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(idx->s_cnt.as<uint32_t>(), d_off, nq, idx->s_scan.p, d_base, d_total, st)));
+        idx->bstats.kernel_launches += 2;
+        return GG_OK;
+    }
+    int per_sm = 0;
+    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, strand_emit_kernel<C, Q>, kQueryThreads, 0));
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
+    if (nq)
+        strand_emit_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(), idx->cbegin.as<uint32_t>(),
+                                                                d_chrom, d_start, d_strand, nq, idx->s_hi.as<uint32_t>(), d_off, d_hits,
+                                                                hits_base, capacity);
+    GG_CUDA(cudaGetLastError());
+    idx->bstats.kernel_launches += 1;
+    return GG_OK;
+}
+
+gg_status dispatch_stranded(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                            const uint8_t* d_strand, int q_bytes, size_t nq, uint64_t* d_off, uint32_t* d_hits,
+                            uint64_t capacity, uint64_t hits_base, const uint64_t* d_base, uint64_t* d_total, uint32_t* d_err,
+                            bool emit_only, cudaStream_t st) {
+    if (idx->coord_bytes == 8)
+        return launch_stranded<uint64_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start), static_cast<const uint64_t*>(d_end),
+                                                   d_strand, nq, d_off, d_hits, capacity, hits_base, d_base, d_total, d_err, emit_only, st);
+    if (q_bytes == 8)
+        return launch_stranded<uint32_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start), static_cast<const uint64_t*>(d_end),
+                                                   d_strand, nq, d_off, d_hits, capacity, hits_base, d_base, d_total, d_err, emit_only, st);
+    return launch_stranded<uint32_t, uint32_t>(idx, d_chrom, static_cast<const uint32_t*>(d_start), static_cast<const uint32_t*>(d_end),
+                                               d_strand, nq, d_off, d_hits, capacity, hits_base, d_base, d_total, d_err, emit_only, st);
+}
+
+gg_status ensure_strand_scratch(gg_index* idx, size_t nq) {
+    const size_t m = nq ? nq : 1;
+    GG_CUDA(idx->s_cnt.ensure(m * 4));
+    GG_CUDA(idx->s_hi.ensure(m * 4));
+    GG_CUDA(idx->s_scan.ensure(scan_state_bytes(m)));
+    GG_CUDA(idx->s_total.ensure(16));
+    GG_CUDA(idx->err_flag.ensure(16));
+    return GG_OK;
+}
+
+gg_status strand_query_error(gg_index* idx, uint32_t flag) {
+    if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+    if (flag & 4u) return fail(idx, GG_ERR_INVALID_ARG, "genomic_coordinate: strand must be one of '+', '-', '.', '*'");
+    return GG_OK;
+}
+}  // namespace
+
+extern "C" {
+
+gg_status gg_index_set_strands(gg_index* idx, const uint8_t* strand, size_t n) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (n != idx->n || (n && !strand)) return fail(idx, GG_ERR_INVALID_ARG, "strand array must hold one byte per indexed interval");
+    for (size_t i = 0; i < n; ++i) {
+        const uint8_t c = strand[i];
+        if (c != '+' && c != '-' && c != '.' && c != '*')
+            return fail(idx, GG_ERR_INVALID_ARG, "genomic_coordinate: strand must be one of '+', '-', '.', '*'");
+    }
+    GG_CUDA(cudaSetDevice(idx->device));
+    GG_CUDA(idx->strand.ensure(n ? n : 1));
+    if (n) GG_CUDA(cudaMemcpyAsync(idx->strand.p, strand, n, cudaMemcpyHostToDevice, idx->stream));
+    GG_CUDA(cudaStreamSynchronize(idx->stream));
+    idx->has_strand = true;
+    return GG_OK;
+}
+
+gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                       const uint8_t* d_strand, int coord_bytes, size_t nq, uint64_t* d_offsets,
+                                       uint32_t* d_hits, uint64_t capacity, uint64_t* total_hits, void* stream) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!idx->has_strand) return fail(idx, GG_ERR_NOT_BUILT, "index has no strands (gg_index_set_strands)");
+    if (!d_offsets || (capacity && !d_hits) || (nq && (!d_chrom || !d_start || !d_end || !d_strand)))
+        return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
+    if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    gg_status s = ensure_strand_scratch(idx, nq);
+    if (s != GG_OK) return s;
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+    idx->bstats.n_chunks = 1;
+    idx->counted_nq = 0;
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, 0, nullptr,
+                          idx->s_total.as<uint64_t>(), idx->err_flag.as<uint32_t>(), false, st);
+    if (s != GG_OK) return s;
+    s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, 0, nullptr,
+                          nullptr, nullptr, true, st);
+    if (s != GG_OK) return s;
+    if (total_hits) {
+        uint32_t flag = 0;
+        GG_CUDA(cudaMemcpyAsync(total_hits, idx->s_total.p, 8, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        idx->bstats.n_hits = *total_hits;
+        s = strand_query_error(idx, flag);
+        if (s != GG_OK) return s;
+        if (*total_hits > capacity) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
+    }
+    return GG_OK;
+}
+
+gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                                      const uint8_t* q_strand, size_t nq, uint64_t* offsets, const uint32_t** hits,
+                                      uint64_t* n_hits) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!idx->has_strand) return fail(idx, GG_ERR_NOT_BUILT, "index has no strands (gg_index_set_strands)");
+    if (!offsets || !hits || !n_hits || (nq && (!q_chrom || !q_start || !q_end || !q_strand)))
+        return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    idx->h2_valid = false;
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+    const size_t chunk = static_cast<size_t>(std::max<int64_t>(idx->chunk_queries, 1024));
+    const size_t cap_q = std::min(chunk, nq ? nq : 1);
+    gg_status s = ensure_strand_scratch(idx, cap_q);
+    if (s != GG_OK) return s;
+    GG_CUDA(idx->sq_qc.ensure(cap_q * 4));
+    GG_CUDA(idx->sq_qs.ensure(cap_q * 8));
+    GG_CUDA(idx->sq_qe.ensure(cap_q * 8));
+    GG_CUDA(idx->sq_str.ensure(cap_q));
+    GG_CUDA(idx->sq_off.ensure((cap_q + 1) * 8));
+    GG_CUDA(idx->d_base.ensure(16));
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    GG_CUDA(cudaMemsetAsync(idx->d_base.p, 0, 8, st));
+    uint64_t base = 0;
+    offsets[0] = 0;
+    for (size_t q0 = 0; q0 < nq; q0 += chunk) {
+        const size_t m = std::min(chunk, nq - q0);
+        GG_CUDA(cudaMemcpyAsync(idx->sq_qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->sq_qs.p, q_start + q0, m * 8, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->sq_qe.p, q_end + q0, m * 8, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaMemcpyAsync(idx->sq_str.p, q_strand + q0, m, cudaMemcpyHostToDevice, st));
+        s = dispatch_stranded(idx, idx->sq_qc.as<uint32_t>(), idx->sq_qs.p, idx->sq_qe.p, idx->sq_str.as<uint8_t>(), 8, m,
+                              idx->sq_off.as<uint64_t>(), nullptr, 0, base, idx->d_base.as<uint64_t>(), idx->s_total.as<uint64_t>(),
+                              idx->err_flag.as<uint32_t>(), false, st);
+        if (s != GG_OK) return s;
+        uint64_t total = 0;
+        uint32_t flag = 0;
+        GG_CUDA(cudaMemcpyAsync(&total, idx->s_total.p, 8, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(offsets + q0, idx->sq_off.p, (m + 1) * 8, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        s = strand_query_error(idx, flag);
+        if (s != GG_OK) return s;
+        GG_CUDA(idx->sq_hits.ensure((total ? total : 1) * 4));
+        s = ensure_pinned_hits(idx, base + total, base);
+        if (s != GG_OK) return s;
+        s = dispatch_stranded(idx, idx->sq_qc.as<uint32_t>(), idx->sq_qs.p, idx->sq_qe.p, idx->sq_str.as<uint8_t>(), 8, m,
+                              idx->sq_off.as<uint64_t>(), idx->sq_hits.as<uint32_t>(), total, base, nullptr, nullptr, nullptr, true, st);
+        if (s != GG_OK) return s;
+        if (total) GG_CUDA(cudaMemcpyAsync(idx->pinned_hits + base, idx->sq_hits.p, total * 4, cudaMemcpyDeviceToHost, st));
+        base += total;
+        GG_CUDA(cudaMemcpyAsync(idx->d_base.p, &base, 8, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        idx->bstats.n_chunks++;
+    }
+    if (nq == 0) {
+        s = ensure_pinned_hits(idx, 1, 0);
+        if (s != GG_OK) return s;
+    }
+    *hits = idx->pinned_hits;
+    *n_hits = base;
+    idx->bstats.n_hits = base;
+    return GG_OK;
 }
 
 }  // extern "C"

@@ -170,3 +170,33 @@ class DeviceIndex:
                         d_succ: int, stream: int = 0, sync: bool = True):
         self._check(self._L.gg_flanking_device(self._h, d_chrom, d_start, d_end, coord_bytes, nq, d_pred, d_succ,
                                                1 if sync else 0, stream or None))
+
+    # ------------------------------------------------------------------ strand-aware intersect (genomic_coordinate)
+    def set_strands(self, strands):
+        """One strand byte (b'+-.*') per indexed interval in chain order (chromosomes concatenated in id order)."""
+        a = _arr(np.frombuffer(strands, dtype=np.uint8) if isinstance(strands, (bytes, bytearray)) else strands, np.uint8)
+        self._check(self._L.gg_index_set_strands(self._h, _ptr(a), len(a)))
+
+    def intersect_batch_stranded(self, q_chrom, q_start, q_end, q_strand):
+        """gg_intersect_batch_stranded: (offsets u64[Q+1], hits u32[H])."""
+        qc, a, b = _arr(q_chrom, np.uint32), _arr(q_start, np.uint64), _arr(q_end, np.uint64)
+        st = _arr(np.frombuffer(q_strand, dtype=np.uint8) if isinstance(q_strand, (bytes, bytearray)) else q_strand, np.uint8)
+        nq = len(qc)
+        offsets = np.empty(nq + 1, dtype=np.uint64)
+        hp = C.POINTER(C.c_uint32)()
+        nh = C.c_uint64(0)
+        self._check(self._L.gg_intersect_batch_stranded(self._h, _ptr(qc), _ptr(a), _ptr(b), _ptr(st), nq, _ptr(offsets),
+                                                        C.byref(hp), C.byref(nh)))
+        n_hits = int(nh.value)
+        if n_hits == 0:
+            return offsets, np.zeros(0, dtype=np.uint32)
+        return offsets, np.ctypeslib.as_array(hp, shape=(n_hits,)).copy()
+
+    def stranded_device(self, d_chrom: int, d_start: int, d_end: int, d_strand: int, coord_bytes: int, nq: int,
+                        d_offsets: int, d_hits: int, capacity: int, stream: int = 0, sync_total: bool = True):
+        total = C.c_uint64(0)
+        st = self._L.gg_intersect_stranded_device(self._h, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets,
+                                                  d_hits, int(capacity), C.byref(total) if sync_total else None, stream or None)
+        self.last_total = int(total.value) if sync_total else None
+        self._check(st)
+        return self.last_total

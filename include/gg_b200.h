@@ -28,6 +28,8 @@
  *                                include/genogrove/structure/grove/query_engine.hpp:176-199, 238-311
  *                                flanking_query_result (data_type/flanking_query_result.hpp) replaced by two
  *                                u32 chain ranks per query (GG_NO_RANK = null pointer)
+ *   gg_index_set_strands,     <- grove<genomic_coordinate, T>::intersect: genomic_coordinate::overlaps / operator<
+ *   gg_intersect_*stranded*      include/genogrove/data_type/genomic_coordinate.hpp:97-110, 156-160
  *   q_chrom (u32 id)          <- grove::get_root(index) hash lookup, grove.hpp:234-236; an id of
  *                                GG_NO_CHROM (or >= n_chrom) yields zero hits, like an unknown index
  *                                name does in grove_query.ipp:37-39
@@ -180,6 +182,27 @@ gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64
 gg_status gg_flanking_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
                              int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync,
                              void* stream);
+
+/* ---- strand-aware intersect (genomic_coordinate keys) --------------------------------------------- */
+/* Replaces grove<genomic_coordinate, T>::intersect(query, index): hits must overlap in coordinates AND have an equal
+ * strand, '*' on either side matching anything (include/genogrove/data_type/genomic_coordinate.hpp:156-160); same
+ * traversal as the interval path (query_engine.hpp:76-134), so the hit list is the interval hit list filtered by
+ * strand, in leaf-chain order.  The chain of genomic_coordinate keys is ordered by (start, end, strand) with
+ * '*' < '.' < '+' < '-' (genomic_coordinate.hpp:97-110): build the index with GG_TIE_EXPLICIT and the strand's order
+ * (0..3) in the high bits of tie_key, or upload a chain the host ordered.
+ * gg_index_set_strands attaches one strand byte ('+', '-', '.', '*') per indexed interval, in CHAIN order with the
+ * chromosomes concatenated in id order (the order rank_to_input lists); it must follow every build / upload. */
+gg_status gg_index_set_strands(gg_index* idx, const uint8_t* strand, size_t n);
+/* Host buffers; as gg_intersect_batch plus q_strand[nq].  A strand byte outside "+-.*" -> GG_ERR_INVALID_ARG (the
+ * reference's std::invalid_argument, genomic_coordinate.hpp:78-81). */
+gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start,
+                                      const uint64_t* q_end, const uint8_t* q_strand, size_t nq, uint64_t* offsets,
+                                      const uint32_t** hits, uint64_t* n_hits);
+/* Device buffers; contract of gg_intersect_fused_device (capacity / total_hits / GG_ERR_CAPACITY) plus d_strand. */
+gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
+                                       const void* d_end, const uint8_t* d_strand, int coord_bytes, size_t nq,
+                                       uint64_t* d_offsets, uint32_t* d_hits, uint64_t capacity,
+                                       uint64_t* total_hits, void* stream);
 
 /* ---- pinned host memory helpers ------------------------------------------------------------------ */
 gg_status gg_host_alloc(void** out, size_t bytes);

@@ -79,6 +79,11 @@ def oracle_lib():
         L.orc_tree_search_flanking.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _u64p]
         L.orc_flat_flanking_batch.argtypes = [_u64p, _u64p, _u64p, C.c_uint32, _u32p, _u64p, _u64p, C.c_size_t,
                                               _u32p, _u32p]
+        L.orc_strand_order.argtypes = [C.c_int]
+        L.orc_gc_less.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_uint64, C.c_uint64]
+        L.orc_gc_overlaps.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_uint64, C.c_uint64]
+        L.orc_flat_intersect_batch_stranded.argtypes = [_u64p, _u64p, C.c_void_p, _u64p, C.c_uint32, _u32p, _u64p, _u64p,
+                                                        C.c_void_p, C.c_size_t, _u64p, _u64p, _u32p]
         _oracle = L
     return _oracle
 
@@ -110,6 +115,16 @@ def ref_lib():
             getattr(L, name).restype = C.c_int
         L.ref_distribute_evenly.argtypes = [C.c_uint64, C.c_uint64, _u64p]
         L.ref_hardware_threads.restype = C.c_int
+        L.ref_gc_create.argtypes = [C.c_int]
+        L.ref_gc_create.restype = C.c_void_p
+        L.ref_gc_destroy.argtypes = [C.c_void_p]
+        L.ref_gc_insert.argtypes = [C.c_void_p, C.c_uint32, C.c_char, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int]
+        L.ref_gc_insert_bulk.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, _u64p, _u64p, _u32p, C.c_size_t, C.c_int]
+        L.ref_gc_intersect.argtypes = [C.c_void_p, C.c_uint32, C.c_char, C.c_uint64, C.c_uint64, _u32p, C.c_size_t]
+        L.ref_gc_intersect.restype = C.c_size_t
+        for name in ("ref_gc_less", "ref_gc_overlaps"):
+            getattr(L, name).argtypes = [C.c_char, C.c_uint64, C.c_uint64, C.c_char, C.c_uint64, C.c_uint64]
+            getattr(L, name).restype = C.c_int
         L.ref_flanking_batch.argtypes = [C.c_void_p, _u32p, _u64p, _u64p, C.c_size_t, _u32p, _u32p]
         _ref = L
     return _ref
@@ -212,6 +227,79 @@ def flat_flanking_batch(start, end, coff, qchrom, qs, qe):
     L.orc_flat_flanking_batch(_p64(s), _p64(e), _p64(co), len(co) - 1, _p32(qc), _p64(a), _p64(b), nq,
                               _p32(pred), _p32(succ))
     return pred, succ
+
+
+STRAND_ORDER = {"*": 0, ".": 1, "+": 2, "-": 3}
+
+
+def _u8(a):
+    if isinstance(a, (bytes, bytearray, str)):
+        a = np.frombuffer(a.encode() if isinstance(a, str) else bytes(a), dtype=np.uint8)
+    return np.ascontiguousarray(a, dtype=np.uint8)
+
+
+def flat_intersect_batch_stranded(start, end, strand, coff, qchrom, qs, qe, qstrand):
+    """Flat oracle for genomic_coordinate keys: chains (start, end, strand byte) concatenated per chromosome.
+    Returns (offsets u64[Q+1], per-chromosome ranks u32[H])."""
+    L = oracle_lib()
+    s, e, co, st = _u64(start), _u64(end), _u64(coff), _u8(strand)
+    qc, a, b, qst = _u32(qchrom), _u64(qs), _u64(qe), _u8(qstrand)
+    nq = len(qc)
+    counts = np.zeros(nq, dtype=np.uint64)
+    args = (_p64(s), _p64(e), st.ctypes.data, _p64(co), len(co) - 1, _p32(qc), _p64(a), _p64(b), qst.ctypes.data, nq)
+    L.orc_flat_intersect_batch_stranded(*args, _p64(counts), None, None)
+    offsets = np.zeros(nq + 1, dtype=np.uint64)
+    np.cumsum(counts, out=offsets[1:])
+    out = np.zeros(max(int(offsets[-1]), 1), dtype=np.uint32)
+    L.orc_flat_intersect_batch_stranded(*args, None, _p64(offsets), _p32(out))
+    return offsets, out[: int(offsets[-1])]
+
+
+def gc_chain(start, end, strand, mode: str = "stable"):
+    """Leaf-chain order of genomic_coordinate keys: ascending (start, end, strand order); equal keys in input order
+    (mode 'stable': sorted bulk) or reverse input order (mode 'regular': one insert_data per record)."""
+    s, e, st = _u64(start), _u64(end), _u8(strand)
+    so = np.array([STRAND_ORDER[chr(c)] for c in st], dtype=np.int64) if len(st) else np.zeros(0, np.int64)
+    idx = np.arange(len(s), dtype=np.int64)
+    return np.lexsort(((-idx if mode == "regular" else idx), so, e, s)).astype(np.uint32)
+
+
+class RefGcGrove:
+    """The unmodified reference grove<genomic_coordinate, uint32_t> (payload = id)."""
+
+    def __init__(self, order: int = 3):
+        self._L = ref_lib()
+        self._g = self._L.ref_gc_create(order)
+        if not self._g:
+            raise ValueError("grove order must be >= 3")
+
+    def insert(self, chrom: int, strand: str, start: int, end: int, id_: int, sorted_: bool = False) -> None:
+        if self._L.ref_gc_insert(self._g, chrom, strand.encode(), start, end, id_, 1 if sorted_ else 0) != 0:
+            raise ValueError("genomic_coordinate: invalid strand or start > end")
+
+    def insert_bulk(self, chrom: int, strand, start, end, ids, presorted: bool = True) -> None:
+        st, s, e, i = _u8(strand), _u64(start), _u64(end), _u32(ids)
+        if self._L.ref_gc_insert_bulk(self._g, chrom, st.tobytes(), _p64(s), _p64(e), _p32(i), len(s), int(presorted)) != 0:
+            raise ValueError("genomic_coordinate: invalid strand or start > end")
+
+    def intersect(self, chrom: int, strand: str, qs: int, qe: int) -> np.ndarray:
+        cap = 64
+        while True:
+            out = np.zeros(cap, dtype=np.uint32)
+            k = self._L.ref_gc_intersect(self._g, chrom, strand.encode(), qs, qe, _p32(out), cap)
+            if k == 2**64 - 1:
+                raise ValueError("genomic_coordinate: invalid strand or start > end")
+            if k <= cap:
+                return out[:k]
+            cap = k
+
+    def close(self):
+        if getattr(self, "_g", None):
+            self._L.ref_gc_destroy(self._g)
+            self._g = None
+
+    def __del__(self):
+        self.close()
 
 
 # ----------------------------------------------------------------------------- the real reference

@@ -412,3 +412,75 @@ void orc_flat_flanking_batch(const uint64_t* start, const uint64_t* end, const u
     }
     free(er);
 }
+
+/* ---------------------------------------------------------------- genomic_coordinate (strand-aware keys) */
+
+/* strand order '*' < '.' < '+' < '-' (genomic_coordinate.hpp:97-110); -1 for an invalid strand byte (:78-81) */
+int orc_strand_order(int s) {
+    switch (s) {
+        case '*': return 0;
+        case '.': return 1;
+        case '+': return 2;
+        case '-': return 3;
+        default: return -1;
+    }
+}
+/* genomic_coordinate::operator< (:97-110) */
+int orc_gc_less(int sa, uint64_t as, uint64_t ae, int sb, uint64_t bs, uint64_t be) {
+    if (as != bs) return as < bs;
+    if (ae != be) return ae < be;
+    return orc_strand_order(sa) < orc_strand_order(sb);
+}
+/* genomic_coordinate::overlaps (:156-160) */
+int orc_gc_overlaps(int sa, uint64_t as, uint64_t ae, int sb, uint64_t bs, uint64_t be) {
+    if (as > be || bs > ae) return 0;
+    if (sa == '*' || sb == '*') return 1;
+    return sa == sb;
+}
+
+/* Flat statement of grove<genomic_coordinate,T>::intersect over concatenated chains (chain order = (start, end,
+ * strand order), ties by insert path): search_overlaps (query_engine.hpp:76-134) skips a child only when it lies
+ * before the query or its aggregate strand cannot match, then walks leaves to the first one starting past q.end,
+ * so the hits are the spatial hits filtered by strand compatibility, ascending in chain rank.
+ * Pass 1: out == NULL, fills counts.  Pass 2: writes per-chromosome ranks at offsets[i]. */
+void orc_flat_intersect_batch_stranded(const uint64_t* start, const uint64_t* end, const uint8_t* strand,
+                                       const uint64_t* coff, uint32_t n_chrom, const uint32_t* qchrom,
+                                       const uint64_t* qs, const uint64_t* qe, const uint8_t* qstrand, size_t nq,
+                                       uint64_t* counts, const uint64_t* offsets, uint32_t* out) {
+    /* pmax (prefix max of end) only bounds the scan from the left, as in orc_flat_intersect_batch */
+    uint64_t n = coff[n_chrom];
+    uint64_t* pmax = (uint64_t*)malloc((n ? n : 1) * sizeof(uint64_t));
+    for (uint32_t c = 0; c < n_chrom; ++c) {
+        uint64_t m = 0;
+        for (uint64_t r = coff[c]; r < coff[c + 1]; ++r) {
+            if (end[r] > m) m = end[r];
+            pmax[r] = m;
+        }
+    }
+    for (size_t i = 0; i < nq; ++i) {
+        uint64_t cnt = 0;
+        if (qchrom[i] < n_chrom && qs[i] <= qe[i] && orc_strand_order(qstrand[i]) >= 0) {
+            uint64_t b = coff[qchrom[i]], t = coff[qchrom[i] + 1];
+            uint64_t lo = b, hi = t;
+            while (lo < hi) { /* first rank with start > q.end */
+                uint64_t mid = lo + (hi - lo) / 2;
+                if (start[mid] <= qe[i]) lo = mid + 1; else hi = mid;
+            }
+            uint64_t ub = lo;
+            lo = b; hi = ub;
+            while (lo < hi) { /* first rank whose prefix max end reaches q.start */
+                uint64_t mid = lo + (hi - lo) / 2;
+                if (pmax[mid] < qs[i]) lo = mid + 1; else hi = mid;
+            }
+            uint32_t* dst = out ? out + offsets[i] : NULL;
+            for (uint64_t r = lo; r < ub; ++r) {
+                if (orc_gc_overlaps(strand[r], start[r], end[r], qstrand[i], qs[i], qe[i])) {
+                    if (dst) dst[cnt] = (uint32_t)(r - b);
+                    cnt++;
+                }
+            }
+        }
+        if (counts) counts[i] = cnt;
+    }
+    free(pmax);
+}

@@ -14,6 +14,7 @@
 //   grove::insert_data(idx, vec, bulk)                 grove_insert.ipp:160-172
 //   grove::intersect(q, idx) / intersect(q)            grove_query.ipp:16-43
 //   grove::remove_key(idx, key*)                       grove_remove.ipp:24-62
+//   grove<genomic_coordinate, uint32_t> (ref_gc_*)     same entry points; genomic_coordinate.hpp:97-110, 156-160
 //   grove::flanking(q, idx)                            grove_flanking.ipp -> detail::search_flanking query_engine.hpp:238-311
 #include <atomic>
 #include <chrono>
@@ -24,6 +25,7 @@
 #include <utility>
 #include <vector>
 
+#include <genogrove/data_type/genomic_coordinate.hpp>
 #include <genogrove/data_type/interval.hpp>
 #include <genogrove/structure/grove/grove.hpp>
 
@@ -170,6 +172,65 @@ void ref_flanking_batch(ref_grove* r, const uint32_t* qchrom, const uint64_t* qs
         pred_ids[i] = res.get_predecessor() ? res.get_predecessor()->get_data() : 0xFFFFFFFFu;
         succ_ids[i] = res.get_successor() ? res.get_successor()->get_data() : 0xFFFFFFFFu;
     }
+}
+
+// ---- grove<genomic_coordinate, uint32_t>: the strand-aware key type (one chromosome namespace as above)
+using gc_grove_t = gst::grove<gdt::genomic_coordinate, uint32_t>;
+struct ref_gc_grove {
+    gc_grove_t g;
+    explicit ref_gc_grove(int order) : g(order) {}
+};
+ref_gc_grove* ref_gc_create(int order) {
+    try {
+        return new ref_gc_grove(order);
+    } catch (...) {
+        return nullptr;
+    }
+}
+void ref_gc_destroy(ref_gc_grove* r) { delete r; }
+// mode: 0 regular insert, 1 sorted insert; returns 1 on std::invalid_argument (bad strand / start > end)
+int ref_gc_insert(ref_gc_grove* r, uint32_t chrom, char strand, uint64_t start, uint64_t end, uint32_t id, int mode) {
+    try {
+        gdt::genomic_coordinate k(strand, start, end);
+        const std::string name = "chr" + std::to_string(chrom);
+        if (mode == REF_SORTED) r->g.insert_data(name, k, id, gst::sorted);
+        else r->g.insert_data(name, k, id);
+        return 0;
+    } catch (const std::invalid_argument&) {
+        return 1;
+    }
+}
+int ref_gc_insert_bulk(ref_gc_grove* r, uint32_t chrom, const char* strand, const uint64_t* start, const uint64_t* end,
+                       const uint32_t* id, size_t n, int presorted) {
+    try {
+        std::vector<std::pair<gdt::genomic_coordinate, uint32_t>> v;
+        v.reserve(n);
+        for (size_t i = 0; i < n; ++i) v.emplace_back(gdt::genomic_coordinate(strand[i], start[i], end[i]), id[i]);
+        const std::string name = "chr" + std::to_string(chrom);
+        if (presorted) r->g.insert_data(name, v, gst::sorted, gst::bulk);
+        else r->g.insert_data(name, std::move(v), gst::bulk);
+        return 0;
+    } catch (const std::invalid_argument&) {
+        return 1;
+    }
+}
+// returns #hits (may exceed cap), or SIZE_MAX on std::invalid_argument from the query's constructor
+size_t ref_gc_intersect(ref_gc_grove* r, uint32_t chrom, char strand, uint64_t qs, uint64_t qe, uint32_t* out, size_t cap) {
+    try {
+        gdt::genomic_coordinate q(strand, qs, qe);
+        auto res = r->g.intersect(q, "chr" + std::to_string(chrom));
+        const auto& keys = res.get_keys();
+        for (size_t i = 0; i < keys.size() && i < cap; ++i) out[i] = keys[i]->get_data();
+        return keys.size();
+    } catch (const std::invalid_argument&) {
+        return static_cast<size_t>(-1);
+    }
+}
+int ref_gc_less(char sa, uint64_t as, uint64_t ae, char sb, uint64_t bs, uint64_t be) {
+    return gdt::genomic_coordinate(sa, as, ae) < gdt::genomic_coordinate(sb, bs, be) ? 1 : 0;
+}
+int ref_gc_overlaps(char sa, uint64_t as, uint64_t ae, char sb, uint64_t bs, uint64_t be) {
+    return gdt::genomic_coordinate::overlaps(gdt::genomic_coordinate(sa, as, ae), gdt::genomic_coordinate(sb, bs, be)) ? 1 : 0;
 }
 
 // known-answer helpers for interval arithmetic (interval.hpp:87-105,140-157)
