@@ -109,6 +109,60 @@ class interval {
     std::size_t end;
 };
 
+/// Stranded closed interval: strand in {'+', '-', '.', '*'}, ordered by (start, end, strand) with '*' < '.' < '+' < '-';
+/// overlaps = coordinates overlap AND (equal strands OR either one is the wildcard '*').  Same members and semantics
+/// as genogrove's data_type/genomic_coordinate.hpp:62-260.
+class genomic_coordinate {
+  public:
+    constexpr genomic_coordinate() : strand('.'), start(0), end(0) {}
+    constexpr genomic_coordinate(char strand_, std::size_t s, std::size_t e) : strand(strand_), start(s), end(e) {
+        if (!valid_strand(strand_)) throw std::invalid_argument("genomic_coordinate: strand must be one of '+', '-', '.', '*'");
+        if (s > e) throw std::invalid_argument("genomic_coordinate: start must be <= end");
+    }
+    static constexpr bool is_interval = true;
+
+    /// rank of a strand in the sort order: '*' 0, '.' 1, '+' 2, '-' 3
+    [[nodiscard]] static constexpr unsigned strand_rank(char c) noexcept { return c == '*' ? 0u : c == '.' ? 1u : c == '+' ? 2u : 3u; }
+    constexpr bool operator<(const genomic_coordinate& o) const {
+        if (start != o.start) return start < o.start;
+        if (end != o.end) return end < o.end;
+        return strand_rank(strand) < strand_rank(o.strand);
+    }
+    constexpr bool operator>(const genomic_coordinate& o) const { return o < *this; }
+    constexpr bool operator==(const genomic_coordinate& o) const { return strand == o.strand && start == o.start && end == o.end; }
+
+    [[nodiscard]] static constexpr bool overlaps(const genomic_coordinate& a, const genomic_coordinate& b) {
+        if (a.start > b.end || b.start > a.end) return false;
+        if (a.strand == '*' || b.strand == '*') return true;
+        return a.strand == b.strand;
+    }
+    [[nodiscard]] static constexpr genomic_coordinate aggregate(const genomic_coordinate& a, const genomic_coordinate& b) {
+        return genomic_coordinate(a.strand == b.strand ? a.strand : '*', a.start < b.start ? a.start : b.start,
+                                  a.end > b.end ? a.end : b.end);
+    }
+    [[nodiscard]] std::string to_string() const {
+        return std::string(1, strand) + ":" + std::to_string(start) + "-" + std::to_string(end);
+    }
+    constexpr char get_strand() const noexcept { return strand; }
+    constexpr std::size_t get_start() const noexcept { return start; }
+    constexpr std::size_t get_end() const noexcept { return end; }
+    constexpr void set_strand(char c) {
+        if (!valid_strand(c)) throw std::invalid_argument("genomic_coordinate: strand must be one of '+', '-', '.', '*'");
+        strand = c;
+    }
+    constexpr void set_range(std::size_t s, std::size_t e) {
+        if (s > e) throw std::invalid_argument("genomic_coordinate: start must be <= end");
+        start = s;
+        end = e;
+    }
+
+  private:
+    static constexpr bool valid_strand(char c) noexcept { return c == '+' || c == '-' || c == '.' || c == '*'; }
+    char strand;
+    std::size_t start;
+    std::size_t end;
+};
+
 namespace detail {
 struct no_data {};
 }  // namespace detail
@@ -235,8 +289,11 @@ class batch_result {
 
 template <typename key_type, typename data_type = void, typename edge_data_type = void>
 class grove {
-    static_assert(std::is_same_v<key_type, gdt::interval>,
-                  "genogrove_b200::structure::grove accelerates grove<interval, T> only (SURVEY.md §8)");
+    static_assert(std::is_same_v<key_type, gdt::interval> || std::is_same_v<key_type, gdt::genomic_coordinate>,
+                  "genogrove_b200::structure::grove accelerates grove<interval, T> and grove<genomic_coordinate, T> (SURVEY.md §8)");
+    /// genomic_coordinate keys: one strand byte per chain rank rides along the device snapshot and every query
+    /// carries its strand (gg_index_set_strands / gg_intersect_batch_stranded)
+    static constexpr bool stranded = std::is_same_v<key_type, gdt::genomic_coordinate>;
 
   public:
     using key_t = gdt::key<key_type, data_type>;
@@ -320,12 +377,18 @@ class grove {
         const std::vector<std::uint32_t> zeros(n, 0u);
         std::vector<std::uint32_t> perm(n);
         const bool was_empty = indices.empty() && all_pending_empty();
-        check(gg_index_build(dev.get(), zeros.data(), s.data(), e.data(), nullptr, GG_TIE_INPUT_ORDER, n, 1, perm.data()));
+        if constexpr (stranded) {  // third sort key: the strand's rank (genomic_coordinate.hpp:97-110), then input order
+            std::vector<std::uint64_t> tie(n);
+            for (std::size_t i = 0; i < n; ++i) tie[i] = key_type::strand_rank(data[i].first.get_strand());
+            check(gg_index_build(dev.get(), zeros.data(), s.data(), e.data(), tie.data(), GG_TIE_EXPLICIT, n, 1, perm.data()));
+        } else {
+            check(gg_index_build(dev.get(), zeros.data(), s.data(), e.data(), nullptr, GG_TIE_INPUT_ORDER, n, 1, perm.data()));
+        }
         dirty = true;  // the handle now holds a snapshot of this batch alone
         std::vector<key_ptr> inserted;
         inserted.reserve(n);
         for (std::size_t r = 0; r < n; ++r) inserted.push_back(allocate_key(key_t(data[perm[r]].first, data[perm[r]].second)));
-        append_sorted_run(index, inserted, /*device_is_current=*/was_empty);
+        append_sorted_run(index, inserted, /*device_is_current=*/was_empty && !stranded);
         return inserted;
     }
 
@@ -371,8 +434,14 @@ class grove {
         scratch_off.resize(scratch_c.size() + 1);
         const std::uint32_t* hits = nullptr;
         std::uint64_t n_hits = 0;
-        check(gg_intersect_batch(dev.get(), scratch_c.data(), scratch_s.data(), scratch_e.data(), scratch_c.size(),
-                                 scratch_off.data(), &hits, &n_hits));
+        if constexpr (stranded) {
+            const std::vector<std::uint8_t> qst(scratch_c.size(), static_cast<std::uint8_t>(query.get_strand()));
+            check(gg_intersect_batch_stranded(dev.get(), scratch_c.data(), scratch_s.data(), scratch_e.data(), qst.data(),
+                                              scratch_c.size(), scratch_off.data(), &hits, &n_hits));
+        } else {
+            check(gg_intersect_batch(dev.get(), scratch_c.data(), scratch_s.data(), scratch_e.data(), scratch_c.size(),
+                                     scratch_off.data(), &hits, &n_hits));
+        }
         result.reserve(n_hits);
         for (std::size_t j = 0; j < scratch_c.size(); ++j) {
             const std::vector<key_ptr>& chain = *chain_by_id[scratch_c[j]];
@@ -391,7 +460,12 @@ class grove {
         std::uint64_t off[2] = {0, 0};
         const std::uint32_t* hits = nullptr;
         std::uint64_t n_hits = 0;
-        check(gg_intersect_batch(dev.get(), &c, &s, &e, 1, off, &hits, &n_hits));
+        if constexpr (stranded) {
+            const std::uint8_t qst = static_cast<std::uint8_t>(query.get_strand());
+            check(gg_intersect_batch_stranded(dev.get(), &c, &s, &e, &qst, 1, off, &hits, &n_hits));
+        } else {
+            check(gg_intersect_batch(dev.get(), &c, &s, &e, 1, off, &hits, &n_hits));
+        }
         result.reserve(n_hits);
         const std::vector<key_ptr>& chain = it->second.chain;
         for (std::uint64_t h = 0; h < n_hits; ++h) result.add_key(chain[hits[h]]);
@@ -410,11 +484,25 @@ class grove {
     /// NEW: millions of queries in one call.  q_index[i] = index_id(name) of query i (npos_index -> no hits),
     /// closed coordinates like interval; start > end in any query -> std::invalid_argument.
     [[nodiscard]] batch_result<key_type, data_type> intersect_batch(const std::uint32_t* q_index, const std::uint64_t* q_start,
-                                                                    const std::uint64_t* q_end, std::size_t nq) {
+                                                                    const std::uint64_t* q_end, std::size_t nq)
+        requires(!stranded) {
         sync();
         batch_result<key_type, data_type> r;
         r.offsets_.resize(nq + 1);
         check(gg_intersect_batch(dev.get(), q_index, q_start, q_end, nq, r.offsets_.data(), &r.hits_, &r.n_hits_));
+        r.q_index_.assign(q_index, q_index + nq);
+        r.chains_ = chain_by_id;
+        return r;
+    }
+    /// genomic_coordinate keys: the same plus one strand byte ('+', '-', '.', '*') per query
+    [[nodiscard]] batch_result<key_type, data_type> intersect_batch(const std::uint32_t* q_index, const std::uint64_t* q_start,
+                                                                    const std::uint64_t* q_end, const std::uint8_t* q_strand,
+                                                                    std::size_t nq)
+        requires(stranded) {
+        sync();
+        batch_result<key_type, data_type> r;
+        r.offsets_.resize(nq + 1);
+        check(gg_intersect_batch_stranded(dev.get(), q_index, q_start, q_end, q_strand, nq, r.offsets_.data(), &r.hits_, &r.n_hits_));
         r.q_index_.assign(q_index, q_index + nq);
         r.chains_ = chain_by_id;
         return r;
@@ -427,13 +515,20 @@ class grove {
             qs[i] = queries[i].get_start();
             qe[i] = queries[i].get_end();
         }
-        return intersect_batch(qc.data(), qs.data(), qe.data(), queries.size());
+        if constexpr (stranded) {
+            std::vector<std::uint8_t> qst(queries.size());
+            for (std::size_t i = 0; i < queries.size(); ++i) qst[i] = static_cast<std::uint8_t>(queries[i].get_strand());
+            return intersect_batch(qc.data(), qs.data(), qe.data(), qst.data(), queries.size());
+        } else {
+            return intersect_batch(qc.data(), qs.data(), qe.data(), queries.size());
+        }
     }
 
     /// grove::flanking(query, index) with the default (always compatible) predicate, grove_flanking.ipp: nearest
     /// non-overlapping predecessor (largest end below query.start, first such key in the chain) and successor (first
     /// key starting past query.end).  One gg_flanking_batch call of one query.
-    [[nodiscard]] gdt::flanking_query_result<key_type, data_type> flanking(const key_type& query, std::string_view index) {
+    [[nodiscard]] gdt::flanking_query_result<key_type, data_type> flanking(const key_type& query, std::string_view index)
+        requires(!stranded) {
         gdt::flanking_query_result<key_type, data_type> result{};
         auto it = indices.find(index);
         if (it == indices.end()) return result;  // null root: empty pair
@@ -449,7 +544,8 @@ class grove {
 
     /// NEW: batch form.  pred[i] / succ[i] = chain rank in index q_index[i] (see chain()), GG_NO_RANK when absent.
     void flanking_batch(const std::uint32_t* q_index, const std::uint64_t* q_start, const std::uint64_t* q_end, std::size_t nq,
-                        std::uint32_t* pred, std::uint32_t* succ) {
+                        std::uint32_t* pred, std::uint32_t* succ)
+        requires(!stranded) {
         sync();
         check(gg_flanking_batch(dev.get(), q_index, q_start, q_end, nq, pred, succ));
     }
@@ -593,6 +689,13 @@ class grove {
             ++id;
         }
         check(gg_index_upload_sorted(dev.get(), c.data(), s.data(), e.data(), n, std::max<std::uint32_t>(id, 1u)));
+        if constexpr (stranded) {
+            std::vector<std::uint8_t> st(n);
+            p = 0;
+            for (const auto* chain_ptr : chain_by_id)
+                for (const key_ptr k : *chain_ptr) st[p++] = static_cast<std::uint8_t>(k->get_value().get_strand());
+            check(gg_index_set_strands(dev.get(), st.data(), n));
+        }
         dirty = false;
     }
 

@@ -25,6 +25,7 @@
 #include "genogrove_b200/grove.hpp"
 
 #ifdef WITH_REFERENCE
+#include <genogrove/data_type/genomic_coordinate.hpp>
 #include <genogrove/data_type/interval.hpp>
 #include <genogrove/structure/grove/grove.hpp>
 #endif
@@ -62,6 +63,9 @@ struct facade_api {
     using query_result = genogrove_b200::data_type::query_result<interval, D>;
     static constexpr auto sorted = genogrove_b200::structure::sorted;
     static constexpr auto bulk = genogrove_b200::structure::bulk;
+    using genomic_coordinate = genogrove_b200::data_type::genomic_coordinate;
+    template <typename D>
+    using gc_grove = genogrove_b200::structure::grove<genomic_coordinate, D>;
 };
 #ifdef WITH_REFERENCE
 struct reference_api {
@@ -75,6 +79,9 @@ struct reference_api {
     using query_result = genogrove::data_type::query_result<interval, D>;
     static constexpr auto sorted = genogrove::structure::sorted;
     static constexpr auto bulk = genogrove::structure::bulk;
+    using genomic_coordinate = genogrove::data_type::genomic_coordinate;
+    template <typename D>
+    using gc_grove = genogrove::structure::grove<genomic_coordinate, D>;
 };
 #endif
 
@@ -574,6 +581,83 @@ void scenario_flanking(trace_t& t) {
     }
 }
 
+// genomic_coordinate keys (strand-aware overlap): genomic_coordinate_grove_test.cpp:150-266 restated + random groves
+// through regular / sorted / sorted-bulk / unsorted-bulk inserts; traces carry payloads in result order
+template <typename A>
+void scenario_stranded(trace_t& t) {
+    using gc = typename A::genomic_coordinate;
+    auto line = [&](const char* tag, auto& g, char st, std::size_t a, std::size_t b, const char* index) {
+        auto r = g.intersect(gc(st, a, b), index);
+        std::ostringstream os;
+        os << tag << " q=" << r.get_query().to_string() << " ->";
+        for (auto* k : r.get_keys()) os << ' ' << k->get_data();
+        t.push_back(os.str());
+        std::vector<int> v;
+        for (auto* k : r.get_keys()) v.push_back(k->get_data());
+        return v;
+    };
+    {
+        typename A::template gc_grove<int> g(3);
+        g.insert_data("chr1", gc('+', 10, 30), 10);
+        g.insert_data("chr1", gc('+', 40, 60), 70);
+        g.insert_data("chr1", gc('+', 80, 100), 90);
+        g.insert_data("chr1", gc('-', 10, 30), 20);
+        g.insert_data("chr1", gc('-', 50, 90), 50);
+        g.insert_data("chr1", gc('-', 100, 120), 71);
+        g.insert_data("chr1", gc('.', 10, 30), 30);
+        g.insert_data("chr1", gc('.', 25, 85), 40);
+        CHECK(line("gc_plus", g, '+', 15, 85, "chr1") == std::vector<int>({10, 70, 90}));
+        CHECK(line("gc_minus", g, '-', 15, 55, "chr1") == std::vector<int>({20, 50}));
+        CHECK(line("gc_dot", g, '.', 15, 55, "chr1") == std::vector<int>({30, 40}));
+        CHECK(line("gc_wild", g, '*', 0, 200, "chr1").size() == 8u);
+        CHECK(line("gc_missing", g, '*', 0, 200, "chr2").empty());
+        CHECK_THROWS(gc('x', 1, 2), std::invalid_argument);
+        CHECK_THROWS(gc('+', 3, 2), std::invalid_argument);
+    }
+    {
+        typename A::template gc_grove<int> g(5);
+        std::vector<std::pair<gc, int>> data = {{gc('*', 10, 20), 10}, {gc('.', 10, 20), 20}, {gc('+', 10, 20), 30}, {gc('-', 10, 20), 40}};
+        g.insert_data("chr1", data, A::sorted, A::bulk);
+        CHECK(line("gc_bulk_order", g, '*', 10, 20, "chr1") == std::vector<int>({10, 20, 30, 40}));
+        CHECK(line("gc_bulk_plus", g, '+', 10, 20, "chr1") == std::vector<int>({10, 30}));  // '*' keys match any query strand
+    }
+    std::mt19937_64 rng(4242);
+    const char sym[4] = {'+', '-', '.', '*'};
+    for (int round = 0; round < 8; ++round) {
+        const int order = round % 4 == 0 ? 3 : (round % 4 == 1 ? 6 : (round % 4 == 2 ? 32 : 4));
+        typename A::template gc_grove<int> g(order);
+        std::vector<std::pair<gc, int>> items;
+        const int n = 300 + 250 * round;
+        for (int i = 0; i < n; ++i) {
+            std::size_t s = (rng() % 20000) / 8 * 8;
+            std::size_t len = (rng() % 50 == 0) ? 4000 + rng() % 6000 : (rng() % 256) / 32 * 32;
+            // distinct full keys in the unsorted-bulk rounds (the reference's std::sort leaves equal keys in no defined order)
+            if (round % 4 == 3) s = static_cast<std::size_t>(i) * 8 + (rng() % 2) * 20000;
+            items.push_back({gc(sym[rng() % (round % 2 ? 4 : 3)], s, s + len), i});
+        }
+        auto sorted_items = items;
+        std::stable_sort(sorted_items.begin(), sorted_items.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        if (round % 4 == 0) {
+            for (const auto& [k, d] : items) g.insert_data("c", k, d);
+        } else if (round % 4 == 1) {
+            for (const auto& [k, d] : sorted_items) g.insert_data("c", k, d, A::sorted);
+        } else if (round % 4 == 2) {
+            g.insert_data("c", sorted_items, A::sorted, A::bulk);
+        } else {
+            g.insert_data("c", items, A::bulk);
+        }
+        for (int k = 0; k < 200; ++k) {
+            const std::size_t a = rng() % 42000, b = a + (rng() % 25 == 0 ? rng() % 8000 : rng() % 400);
+            const char st = sym[rng() % 4];
+            auto got = line("gc_rand", g, st, a, b, "c");
+            std::multiset<int> want;
+            for (const auto& [kk, d] : items)
+                if (gc::overlaps(kk, gc(st, a, b))) want.insert(d);
+            CHECK(std::multiset<int>(got.begin(), got.end()) == want);
+        }
+    }
+}
+
 template <typename A>
 trace_t run_scenarios() {
     trace_t t;
@@ -587,6 +671,7 @@ trace_t run_scenarios() {
     scenario_tie_order<A>(t);
     scenario_random<A>(t);
     scenario_flanking<A>(t);
+    scenario_stranded<A>(t);
     return t;
 }
 
