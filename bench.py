@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--cpu-order", type=int, default=32, help="B+ tree order of the reference grove (3 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the flanking / stranded side measurements")
     ap.add_argument("--two-phase", action="store_true",
                     help="time the count -> scan -> emit kernels (two-phase API) instead of the single-call path")
     ap.add_argument("--one-kernel", action="store_true", help="single-call path as ONE kernel (decoupled look-back scan)")
@@ -323,6 +324,51 @@ def main():
                 "path_achieved_gbs": bytes_path / (ms_per_step / 1e3) / 1e9,
                 "path_frac": bytes_path / (ms_per_step / 1e3) / 1e9 / peak}
 
+    # ---- side measurements (not the headline): the two other query kinds on the same index and batch, device-resident
+    extras = None
+    if not args.no_extras:
+        ex_steps = 10
+        d_pred = torch.empty(nq, dtype=torch.int32, device=dev)
+        d_succ = torch.empty(nq, dtype=torch.int32, device=dev)
+
+        def timed(fn, n):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(n):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b) / n
+
+        fl_ms = timed(lambda: idx.flanking_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_pred.data_ptr(),
+                                                  d_succ.data_ptr(), stream, sync=False), ex_steps)
+        del d_pred, d_succ
+        rs = np.random.default_rng(7)
+        idx.set_strands(np.frombuffer(b"+-.", dtype=np.uint8)[rs.integers(0, 3, ist.n_intervals)])
+        d_str = torch.from_numpy(np.frombuffer(b"+-", dtype=np.uint8)[rs.integers(0, 2, nq)]).to(dev)
+        st_total = [0]
+
+        def stranded_step():
+            st_total[0] = idx.stranded_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), d_str.data_ptr(), 4, nq,
+                                              d_off.data_ptr(), d_hits.data_ptr(), d_hits.numel(), stream, sync_total=True)
+
+        st_ms = timed(stranded_step, ex_steps)
+        del d_str
+        fl_bytes = 20 * nq  # read (chrom,start,end) u32, write pred + succ u32
+        st_bytes = 13 * nq + 8 * (nq + 1) + 4 * st_total[0]
+        extras = {"flanking": {"queries_per_sec": nq * world / (fl_ms / 1e3), "ms_per_step": fl_ms, "kernel": "flanking_kernel",
+                               "algorithmic_bytes": fl_bytes, "achieved_gbs": fl_bytes / (fl_ms / 1e3) / 1e9,
+                               "frac": fl_bytes / (fl_ms / 1e3) / 1e9 / peak},
+                  "stranded": {"queries_per_sec": nq * world / (st_ms / 1e3), "ms_per_step": st_ms,
+                               "kernels": "strand_count_kernel + exclusive_scan_kernel + strand_emit_kernel",
+                               "hits_per_query": st_total[0] / nq, "algorithmic_bytes": st_bytes,
+                               "achieved_gbs": st_bytes / (st_ms / 1e3) / 1e9, "frac": st_bytes / (st_ms / 1e3) / 1e9 / peak,
+                               "strands": "index: uniform over + - . ; queries: uniform over + -"},
+                  "note": "per-rank device time, same index and query batch as the headline; steps=%d" % ex_steps}
+
     # ---- e2e: host-buffer C ABI call (u64 coordinates, pinned buffers), H2D + D2H inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -369,7 +415,7 @@ def main():
                "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
                "config": workload_config(args, world), "hit_pairs_per_sec": job_hits / (ms_per_step / 1e3),
                "hits_per_query": job_hits / job_q, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
-               "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+               "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "extras": extras,
                "index": {"levels": ist.n_levels, "fanout": ist.fanout, "staged_levels": ist.staged_levels,
                          "coord_bytes": ist.coord_bytes, "device_mb": ist.device_bytes / 1e6,
                          "build_sort_ms": ist.sort_ms, "build_levels_ms": ist.levels_ms, "build_total_ms": ist.total_ms}}

@@ -1,0 +1,94 @@
+"""tools/gg_isec.bin — the batched `genogrove intersect` for BED files.
+Known answers restate tests/cli/intersect-test.cpp:86-118 with the content of tests/cli/data/{target,query}.bed;
+the larger case is checked against the flat oracle (hits printed in leaf-chain order, queries in file order)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle as O
+from helpers import chrom_offsets
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "tools", "gg_isec.bin")
+
+
+def test_isec_binary_is_built():
+    assert os.path.exists(BIN), "run __graft_entry__.build()"
+
+
+def _run(args, expect_rc=0):
+    r = subprocess.run([BIN] + args, capture_output=True, text=True, timeout=600)
+    assert r.returncode == expect_rc, r.stderr
+    return r
+
+
+@pytest.mark.gpu
+def test_isec_reference_cli_known_answer(tmp_path):
+    t = tmp_path / "target.bed"
+    q = tmp_path / "query.bed"
+    t.write_text("chr1\t100\t500\nchr1\t600\t900\nchr2\t200\t400\n")
+    q.write_text("chr1\t150\t250\nchr1\t850\t950\nchr2\t500\t600\n")
+    r = _run(["-q", str(q), "-t", str(t)])
+    assert r.stdout == "chr1\t100\t500\nchr1\t600\t900\n"  # chr2:500-600 does not overlap chr2:200-400
+    out = tmp_path / "o.bed"
+    _run(["-q", str(q), "-t", str(t), "-o", str(out), "-k", "5"])
+    assert out.read_text() == r.stdout
+    # half-open BED: [100,500) and [500,600) do not overlap; [499,500) does
+    q.write_text("# comment\ntrack name=x\nchr1\t500\t600\nchr1\t499\t500\nchrUn\t0\t10\n")
+    assert _run(["-q", str(q), "-t", str(t)]).stdout == "chr1\t100\t500\n"
+
+
+@pytest.mark.gpu
+def test_isec_errors(tmp_path):
+    t = tmp_path / "t.bed"
+    t.write_text("chr1\t100\t500\n")
+    bad = tmp_path / "bad.bed"
+    bad.write_text("chr1\t10\t10\n")
+    assert "Start coordinate is greater than or equal" in _run(["-q", str(bad), "-t", str(t)], 1).stderr
+    bad.write_text("chr1\tx\t10\n")
+    assert "Invalid coordinate format" in _run(["-q", str(bad), "-t", str(t)], 1).stderr
+    assert "order must be at least 3" in _run(["-q", str(t), "-t", str(t), "-k", "2"], 1).stderr
+    assert "Failed to open" in _run(["-q", str(tmp_path / "missing.bed"), "-t", str(t)], 1).stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sorted_target", [False, True])
+def test_isec_matches_oracle(tmp_path, sorted_target):
+    rng = np.random.default_rng(11 + sorted_target)
+    n, nq, n_chrom = 20000, 30000, 5
+    chrom = rng.integers(0, n_chrom, n).astype(np.uint32)
+    s = rng.integers(0, 500_000, n).astype(np.uint64)
+    e = s + rng.integers(1, 3000, n).astype(np.uint64)  # half-open end
+    # distinct (chrom, start, end): the print does not tell equal records apart anyway
+    key = np.unique(np.stack([chrom, s, e], 1), axis=0)
+    rng.shuffle(key)
+    chrom, s, e = key[:, 0].astype(np.uint32), key[:, 1], key[:, 2]
+    if sorted_target:
+        o = np.lexsort((e, s, chrom))
+        chrom, s, e = chrom[o], s[o], e[o]
+    names = [f"chr{c + 1}" for c in range(n_chrom)]
+    t = tmp_path / "t.bed"
+    t.write_text("".join(f"{names[c]}\t{a}\t{b}\n" for c, a, b in zip(chrom, s, e)))
+    qc = rng.integers(0, n_chrom + 1, nq)
+    qs = rng.integers(0, 510_000, nq).astype(np.uint64)
+    qe = qs + rng.integers(1, 2000, nq).astype(np.uint64)
+    qn = names + ["chrMissing"]
+    q = tmp_path / "q.bed"
+    q.write_text("".join(f"{qn[c]}\t{a}\t{b}\n" for c, a, b in zip(qc, qs, qe)))
+    got = _run(["-q", str(q), "-t", str(t)] + (["-s"] if sorted_target else [])).stdout
+    # oracle: closed coordinates [start, end - 1]; chain order = (start, end)
+    perm = np.lexsort((e, s, chrom))
+    coff = chrom_offsets(chrom, n_chrom)
+    qcc = np.where(qc < n_chrom, qc, O.NO_CHROM).astype(np.uint32)
+    off, ranks = O.flat_intersect_batch(s[perm], e[perm] - np.uint64(1), coff, qcc, qs, qe - np.uint64(1))
+    lines = []
+    for k in range(nq):
+        if qc[k] >= n_chrom:
+            continue
+        base = int(coff[qc[k]])
+        for r in ranks[int(off[k]):int(off[k + 1])]:
+            i = perm[base + int(r)]
+            lines.append(f"{names[chrom[i]]}\t{s[i]}\t{e[i]}\n")
+    assert got == "".join(lines)

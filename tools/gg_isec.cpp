@@ -1,0 +1,156 @@
+// gg_isec — batched `genogrove intersect` for BED files on the B200 path.
+//
+// Mirrors the reference CLI's target-file mode (cli/src/intersect.cpp:39-58,196-221 with the BED handlers
+// cli/src/handlers/bed.cpp:11-38, cli/include/handlers/bed.hpp:50-62): every target record is inserted as
+// interval(start, end - 1) under its chromosome name (BED is 0-based half-open, the grove is closed), every query
+// record asks intersect(interval(start, end - 1), chrom), and each hit prints "chrom\tstart\tend\n" of the TARGET
+// record, hits in leaf-chain order, queries in file order.  The difference is the shape of the work: the reference
+// calls grove.intersect once per query line; this reads the whole query file into structure-of-arrays buffers and
+// makes ONE grove.intersect_batch call (count -> scan -> emit on the device), then prints from the CSR result.
+//
+//   gg_isec -q query.bed -t target.bed [-o out.bed] [-k order] [-s]     (-s: target is sorted -> sorted inserts)
+//
+// BED parsing follows io/bed_reader.cpp:395-431 for the three mandatory columns: tab/space separated, digits only,
+// start < end, else the run fails with the reader's message.  Lines that are empty or start with '#', "track" or
+// "browser" are skipped.
+#include <charconv>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <stdexcept>
+#include <string>
+#include <string_view>
+#include <vector>
+
+#include "genogrove_b200/grove.hpp"
+
+namespace gdt = genogrove_b200::data_type;
+namespace gst = genogrove_b200::structure;
+
+struct bed3 {
+    std::string chrom;
+    std::size_t start = 0, end = 0;
+};
+
+static bool skip_line(std::string_view l) {
+    return l.empty() || l[0] == '#' || l.substr(0, 5) == "track" || l.substr(0, 7) == "browser";
+}
+
+static std::string_view next_field(std::string_view l, std::size_t& pos) {
+    while (pos < l.size() && (l[pos] == '\t' || l[pos] == ' ')) ++pos;
+    const std::size_t b = pos;
+    while (pos < l.size() && l[pos] != '\t' && l[pos] != ' ') ++pos;
+    return l.substr(b, pos - b);
+}
+
+static std::size_t parse_coord(std::string_view f, std::size_t line_num) {
+    std::size_t v = 0;
+    if (f.empty() || f.find_first_not_of("0123456789") != std::string_view::npos)
+        throw std::runtime_error("Invalid coordinate format at line " + std::to_string(line_num));
+    auto [p, ec] = std::from_chars(f.data(), f.data() + f.size(), v);
+    if (ec != std::errc{}) throw std::runtime_error("Coordinate out of range at line " + std::to_string(line_num));
+    return v;
+}
+
+template <typename F>
+static void for_each_bed(const std::string& path, F&& cb) {
+    std::ifstream in(path);
+    if (!in) throw std::runtime_error("Failed to open file: " + path);
+    std::string line;
+    std::size_t line_num = 0;
+    while (std::getline(in, line)) {
+        ++line_num;
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        if (skip_line(line)) continue;
+        std::size_t pos = 0;
+        const std::string_view l(line);
+        const std::string_view c = next_field(l, pos), s = next_field(l, pos), e = next_field(l, pos);
+        if (c.empty() || s.empty() || e.empty()) throw std::runtime_error("Invalid line format at line " + std::to_string(line_num));
+        bed3 r{std::string(c), parse_coord(s, line_num), parse_coord(e, line_num)};
+        if (r.start >= r.end)
+            throw std::runtime_error("Start coordinate is greater than or equal to the end coordinate at line " + std::to_string(line_num));
+        cb(std::move(r));
+    }
+}
+
+int main(int argc, char** argv) {
+    std::string query, target, out_path = "stdout";
+    int order = 3;
+    bool sorted = false;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto need = [&](const char* what) -> std::string {
+            if (i + 1 >= argc) throw std::runtime_error(std::string("Error: missing value for ") + what);
+            return argv[++i];
+        };
+        try {
+            if (a == "-q" || a == "--queryfile") query = need("-q");
+            else if (a == "-t" || a == "--targetfile") target = need("-t");
+            else if (a == "-o" || a == "--outputfile") out_path = need("-o");
+            else if (a == "-k" || a == "--order") order = std::stoi(need("-k"));
+            else if (a == "-s" || a == "--sorted") sorted = true;
+            else if (a == "-h" || a == "--help") {
+                std::puts("gg_isec -q query.bed -t target.bed [-o out] [-k order] [-s]");
+                return 0;
+            } else if (query.empty()) query = a;
+            else if (target.empty()) target = a;
+        } catch (const std::exception& ex) {
+            std::fprintf(stderr, "%s\n", ex.what());
+            return 2;
+        }
+    }
+    try {
+        if (query.empty()) throw std::runtime_error("Error: queryfile is required");
+        if (target.empty()) throw std::runtime_error("Error: a target file (-t) is required");
+        if (order < 3) throw std::runtime_error("Error: order must be at least 3");
+
+        gst::grove<gdt::interval, bed3> grove(order);
+        for_each_bed(target, [&](bed3 r) {
+            const gdt::interval iv(r.start, r.end - 1);
+            std::string chrom = r.chrom;
+            if (sorted) grove.insert_data(chrom, iv, std::move(r), gst::sorted);
+            else grove.insert_data(chrom, iv, std::move(r));
+        });
+
+        // the whole query file -> SoA buffers -> one batch call
+        std::vector<std::uint32_t> qc;
+        std::vector<std::uint64_t> qs, qe;
+        for_each_bed(query, [&](bed3 r) {
+            qc.push_back(grove.index_id(r.chrom));  // npos_index for a chromosome the target lacks: no hits
+            qs.push_back(r.start);
+            qe.push_back(r.end - 1);
+        });
+        auto res = grove.intersect_batch(qc.data(), qs.data(), qe.data(), qc.size());
+
+        std::ofstream file;
+        if (out_path != "stdout") {
+            file.open(out_path);
+            if (!file.is_open()) throw std::runtime_error("Error: could not open output file: " + out_path);
+        }
+        std::ostream& out = out_path == "stdout" ? std::cout : file;
+        std::string buf;
+        buf.reserve(1 << 20);
+        for (std::size_t q = 0; q < res.size(); ++q) {
+            for (std::size_t j = 0; j < res.count(q); ++j) {
+                const bed3& t = res.key(q, j)->get_data();
+                buf += t.chrom;
+                buf += '\t';
+                buf += std::to_string(t.start);
+                buf += '\t';
+                buf += std::to_string(t.end);
+                buf += '\n';
+                if (buf.size() > (1 << 20) - 256) {
+                    out << buf;
+                    buf.clear();
+                }
+            }
+        }
+        out << buf;
+        out.flush();
+    } catch (const std::exception& ex) {
+        std::fprintf(stderr, "%s\n", ex.what());
+        return 1;
+    }
+    return 0;
+}
