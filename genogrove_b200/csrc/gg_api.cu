@@ -25,7 +25,10 @@ using namespace gg;
 
 namespace {
 
-constexpr int kBatchQpt = 4;  // consecutive queries per thread of the grouped count kernel
+#ifndef GG_BATCH_QPT
+#define GG_BATCH_QPT 4
+#endif
+constexpr int kBatchQpt = GG_BATCH_QPT;  // consecutive queries per thread of the grouped count kernel
 constexpr size_t kBatchBlockQ = 32 * kBatchQpt;  // = one warp's share: the granularity of the batch path's block totals
 constexpr int kSlots = 3;        // pipeline depth of the host-buffer path
 constexpr int kCountThreadsDefault = 256;
