@@ -1414,7 +1414,7 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
         const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
         if (nq)
             strand_count_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(),
-                                                                     idx->cbegin.as<uint32_t>(), d_chrom, d_start, d_end, d_strand,
+                                                                     idx->er_base, d_chrom, d_start, d_end, d_strand,
                                                                      nq, idx->s_cnt.as<uint32_t>(), idx->s_hi.as<uint32_t>(), d_err);
         GG_CUDA(cudaGetLastError());
         GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(idx->s_cnt.as<uint32_t>(), d_off, nq, idx->s_scan.p, d_base, d_total, st)));
@@ -1425,7 +1425,7 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
     GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, strand_emit_kernel<C, Q>, kQueryThreads, 0));
     const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
     if (nq)
-        strand_emit_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(), idx->cbegin.as<uint32_t>(),
+        strand_emit_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(), idx->er_base,
                                                                 d_chrom, d_start, d_strand, nq, idx->s_hi.as<uint32_t>(), d_off, d_hits,
                                                                 hits_base, capacity);
     GG_CUDA(cudaGetLastError());
@@ -1477,9 +1477,21 @@ gg_status gg_index_set_strands(gg_index* idx, const uint8_t* strand, size_t n) {
             return fail(idx, GG_ERR_INVALID_ARG, "genomic_coordinate: strand must be one of '+', '-', '.', '*'");
     }
     GG_CUDA(cudaSetDevice(idx->device));
-    GG_CUDA(idx->strand.ensure(n ? n : 1));
-    if (n) GG_CUDA(cudaMemcpyAsync(idx->strand.p, strand, n, cudaMemcpyHostToDevice, idx->stream));
-    GG_CUDA(cudaStreamSynchronize(idx->stream));
+    const size_t C = idx->n_chrom;
+    const uint32_t level0_elems = idx->h_tab[C] - idx->h_tab[0];
+    DeviceBuf tmp;
+    GG_CUDA(tmp.ensure(n ? n : 1));
+    cudaError_t e = idx->strand.ensure(level0_elems ? level0_elems : 1);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(tmp.p, strand, n, cudaMemcpyHostToDevice, idx->stream);
+    if (e == cudaSuccess) {
+        pad_strand_kernel<<<blocks_for(level0_elems, 256), 256, 0, idx->stream>>>(tmp.as<uint8_t>(), idx->cbegin.as<uint32_t>(),
+                                                                                 idx->cnt.as<uint32_t>(), idx->tab.as<uint32_t>(),
+                                                                                 idx->n_chrom, idx->strand.as<uint8_t>());
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
+    tmp.release();
+    if (e != cudaSuccess) return fail(idx, GG_ERR_CUDA, "gg_index_set_strands", e);
     idx->has_strand = true;
     return GG_OK;
 }
