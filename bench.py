@@ -364,7 +364,7 @@ def main():
                                "algorithmic_bytes": fl_bytes, "achieved_gbs": fl_bytes / (fl_ms / 1e3) / 1e9,
                                "frac": fl_bytes / (fl_ms / 1e3) / 1e9 / peak},
                   "stranded": {"queries_per_sec": nq * world / (st_ms / 1e3), "ms_per_step": st_ms,
-                               "kernels": "strand_count_kernel + exclusive_scan_kernel + strand_emit_kernel",
+                               "kernels": "strand_count_group_kernel + exclusive_scan_kernel (block totals) + intersect_emit_scan_kernel<kStrand>",
                                "hits_per_query": st_total[0] / nq, "algorithmic_bytes": st_bytes,
                                "achieved_gbs": st_bytes / (st_ms / 1e3) / 1e9, "frac": st_bytes / (st_ms / 1e3) / 1e9 / peak,
                                "strands": "index: uniform over + - . ; queries: uniform over + -"},

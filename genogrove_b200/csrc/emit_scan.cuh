@@ -12,18 +12,28 @@
 // of err_flag reports the overflow (offsets are complete either way).
 #pragma once
 #include "intersect.cuh"
+#include "strand.cuh"
 
 namespace gg {
 
 constexpr uint32_t kEmitScanSlack = 8;  // spare slots in front of each warp's stage (see emit_walk_staged)
 
-template <typename C, typename Q, int kWalk>
+// kStrand (genomic_coordinate keys, strand.cuh): cnt_in holds the strand-compatible counts and the walk also tests
+// the strand byte of every rank against qstrand[q]; strands = padded level-0 strand bytes, slot_base = tab[0][0].
+struct StrandArgs {
+    const uint8_t* strands;
+    const uint8_t* qstrand;
+    uint32_t slot_base;
+};
+
+template <typename C, typename Q, int kWalk, bool kStrand = false>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
                            const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
                            const uint64_t* __restrict__ block_prefix, uint32_t blk_q, uint64_t* __restrict__ offsets,
                            uint32_t* __restrict__ hits, uint64_t capacity, uint64_t* __restrict__ next_base_out,
-                           uint64_t* __restrict__ total_out, uint32_t* __restrict__ err_flag, int tab_in_smem) {
+                           uint64_t* __restrict__ total_out, uint32_t* __restrict__ err_flag, int tab_in_smem,
+                           StrandArgs sa = StrandArgs{nullptr, nullptr, 0}) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStageWords = kEmitStage + kEmitScanSlack;
     constexpr uint32_t kWarps = kQueryThreads / 32;
@@ -90,17 +100,21 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
             const uint64_t wbase = run - base;  // chunk-local index of the warp's first hit
             run += wtotal;
             if (wtotal == 0) continue;
-            uint32_t chrom = 0, hi = 0;
+            uint32_t chrom = 0, hi = 0, qst = 0;
             C qs = 0;
             if (c != 0) {
                 chrom = qchrom[q];
                 qs = static_cast<C>(qstart[q]);  // c > 0 implies q.start fits the index domain
                 hi = hi_in[q];
+                if (kStrand) qst = sa.qstrand[q];
             }
             if (wtotal <= kEmitStage) {
                 if (c != 0) {
                     const uint32_t s_begin = stage_addr + static_cast<uint32_t>(excl) * 4u;
-                    if (kWalk == 16)
+                    if (kStrand)
+                        emit_walk_staged8_strand<C>(ix, tabp, stride, n_levels, chrom, qs, hi,
+                                                    sa.strands + (tabp[chrom] - sa.slot_base), qst, s_begin, s_begin + c * 4u);
+                    else if (kWalk == 16)
                         emit_walk_staged16<C>(ix, tabp, stride, n_levels, chrom, qs, hi, s_begin, s_begin + c * 4u);
                     else
                         emit_walk_staged8<C>(ix, tabp, stride, n_levels, chrom, qs, hi, s_begin, s_begin + c * 4u);
@@ -117,7 +131,11 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                 }
                 __syncwarp();
             } else if (c != 0 && wbase + excl + c <= capacity) {
-                emit_walk_global<C>(ix, tabp, stride, n_levels, chrom, qs, hi, hits + wbase + excl, c);
+                if (kStrand)
+                    strand_walk<C, true>(ix, stride, n_levels, chrom, qs, hi, c, sa.strands + (tabp[chrom] - sa.slot_base), qst,
+                                         hits + wbase + excl);
+                else
+                    emit_walk_global<C>(ix, tabp, stride, n_levels, chrom, qs, hi, hits + wbase + excl, c);
             }
         }
     }

@@ -105,7 +105,8 @@ struct gg_index {
     // ---- two-phase host API state
     DeviceBuf h2_qc, h2_qs, h2_qe, h2_off, h2_hits;
     DeviceBuf fl_qc, fl_qs, fl_qe, fl_pred, fl_succ;  // gg_flanking_batch staging
-    DeviceBuf strand;        // u8 per concatenated chain rank ('+', '-', '.', '*'), gg_index_set_strands
+    DeviceBuf strand;        // u8 per level-0 slot ('+', '-', '.', '*'; pads 0), gg_index_set_strands
+    DeviceBuf SN, EN;        // StrandNode per level-0 node (+1 sentinel) in chain order / sorted-end order (strand.cuh)
     bool has_strand = false;
     DeviceBuf sq_qc, sq_qs, sq_qe, sq_str, sq_off, sq_hits;  // gg_intersect_batch_stranded staging
     DeviceBuf s_cnt, s_hi, s_scan, s_total;                   // stranded path scratch (device calls too)
@@ -379,7 +380,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
         const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
         void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
-                     uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int) =
+                     uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs) =
             idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16> : intersect_emit_scan_kernel<C, Q, 8>;
         if (smem > 48 * 1024)
             GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -392,7 +393,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
         kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix,
                                                 static_cast<uint32_t>(kBatchBlockQ), d_off, d_hits, capacity, d_next_base, d_total,
-                                                d_err, tab_in_smem ? 1 : 0);
+                                                d_err, tab_in_smem ? 1 : 0, StrandArgs{nullptr, nullptr, 0});
         GG_CUDA(cudaGetLastError());
         idx->bstats.kernel_launches++;
     }
@@ -1039,7 +1040,7 @@ void gg_index_destroy(gg_index* idx) {
     cudaDeviceSynchronize();
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
-                         &idx->ER, &idx->cbegin, &idx->strand, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
+                         &idx->ER, &idx->cbegin, &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
                          &idx->s_cnt, &idx->s_hi, &idx->s_scan, &idx->s_total, &idx->fl_qc, &idx->fl_qs, &idx->fl_qe, &idx->fl_pred, &idx->fl_succ})
         b->release();
     for (auto& s : idx->slots) {
@@ -1403,55 +1404,75 @@ gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64
 // ------------------------------------------------------------------------------------------ stranded intersect
 
 namespace {
+// Count phase (emit_only = false): strand_count_group_kernel -> scan of the per-128-query block totals (+ *d_base),
+// *d_total = hits of the batch.  Emit phase (emit_only = true): intersect_emit_scan_kernel<.., kStrand> writes
+// d_off[0..nq] (global offsets) and the chunk-local hit ranks.  Both use idx->s_cnt / s_hi / s_scan.
 template <typename C, typename Q>
 gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, const uint8_t* d_strand,
-                          size_t nq, uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, uint64_t hits_base,
-                          const uint64_t* d_base, uint64_t* d_total, uint32_t* d_err, bool emit_only, cudaStream_t st) {
-    const size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads));
+                          size_t nq, uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, const uint64_t* d_base,
+                          uint64_t* d_total, uint32_t* d_err, bool emit_only, cudaStream_t st) {
+    char* p = static_cast<char*>(idx->s_scan.p);
+    const size_t nb = batch_blocks(nq), nb1 = nb + 1;
+    unsigned long long* block_total = reinterpret_cast<unsigned long long*>(p);
+    uint64_t* block_prefix = reinterpret_cast<uint64_t*>(p + round_up(nb1 * 8, 256));
+    void* scan_state = p + round_up(nb1 * 8, 256) + round_up((nb1 + 1) * 8, 256);
+    uint32_t* d_cnt = idx->s_cnt.as<uint32_t>();
+    uint32_t* d_hi = idx->s_hi.as<uint32_t>();
     if (!emit_only) {
-        int per_sm = 0;
-        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, strand_count_kernel<C, Q>, kQueryThreads, 0));
-        const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
-        if (nq)
-            strand_count_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(),
-                                                                     idx->er_base, d_chrom, d_start, d_end, d_strand,
-                                                                     nq, idx->s_cnt.as<uint32_t>(), idx->s_hi.as<uint32_t>(), d_err);
-        GG_CUDA(cudaGetLastError());
-        GG_CUDA((exclusive_scan_async<uint32_t, uint64_t>(idx->s_cnt.as<uint32_t>(), d_off, nq, idx->s_scan.p, d_base, d_total, st)));
-        idx->bstats.kernel_launches += 2;
+        if (nq) {
+            auto kern = strand_count_group_kernel<C, Q, kBatchQpt>;
+            int per_sm = 0;
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
+            const size_t tiles = div_up(nq, static_cast<size_t>(kQueryThreads) * kBatchQpt);
+            const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
+            const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end);
+            kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->SN.as<StrandNode>(), idx->EN.as<StrandNode>(), idx->er_base,
+                                                 d_chrom, d_start, d_end, d_strand, nq, d_cnt, d_hi, block_total, d_err, vec_ok);
+            GG_CUDA(cudaGetLastError());
+            idx->bstats.kernel_launches++;
+        }
+        GG_CUDA((exclusive_scan_async<uint64_t, uint64_t>(reinterpret_cast<const uint64_t*>(block_total), block_prefix, nb, scan_state,
+                                                           d_base, d_total, st)));
+        idx->bstats.kernel_launches++;
         return GG_OK;
     }
+    const bool tab_in_smem = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024;
+    const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
+    const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
+    auto kern = intersect_emit_scan_kernel<C, Q, 8, true>;
+    if (smem > 48 * 1024) GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     int per_sm = 0;
-    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, strand_emit_kernel<C, Q>, kQueryThreads, 0));
-    const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
-    if (nq)
-        strand_emit_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->strand.as<uint8_t>(), idx->er_base,
-                                                                d_chrom, d_start, d_strand, nq, idx->s_hi.as<uint32_t>(), d_off, d_hits,
-                                                                hits_base, capacity);
+    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+    if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "emit kernel does not fit on an SM");
+    const size_t ctas = div_up(std::max<size_t>(nb, 1), kQueryThreads / 32);
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
+    kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix,
+                                            static_cast<uint32_t>(kBatchBlockQ), d_off, d_hits, capacity, nullptr, nullptr, d_err,
+                                            tab_in_smem ? 1 : 0, StrandArgs{idx->strand.as<uint8_t>(), d_strand, idx->er_base});
     GG_CUDA(cudaGetLastError());
-    idx->bstats.kernel_launches += 1;
+    idx->bstats.kernel_launches++;
     return GG_OK;
 }
 
 gg_status dispatch_stranded(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
                             const uint8_t* d_strand, int q_bytes, size_t nq, uint64_t* d_off, uint32_t* d_hits,
-                            uint64_t capacity, uint64_t hits_base, const uint64_t* d_base, uint64_t* d_total, uint32_t* d_err,
-                            bool emit_only, cudaStream_t st) {
+                            uint64_t capacity, const uint64_t* d_base, uint64_t* d_total, uint32_t* d_err, bool emit_only,
+                            cudaStream_t st) {
     if (idx->coord_bytes == 8)
         return launch_stranded<uint64_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start), static_cast<const uint64_t*>(d_end),
-                                                   d_strand, nq, d_off, d_hits, capacity, hits_base, d_base, d_total, d_err, emit_only, st);
+                                                   d_strand, nq, d_off, d_hits, capacity, d_base, d_total, d_err, emit_only, st);
     if (q_bytes == 8)
         return launch_stranded<uint32_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start), static_cast<const uint64_t*>(d_end),
-                                                   d_strand, nq, d_off, d_hits, capacity, hits_base, d_base, d_total, d_err, emit_only, st);
+                                                   d_strand, nq, d_off, d_hits, capacity, d_base, d_total, d_err, emit_only, st);
     return launch_stranded<uint32_t, uint32_t>(idx, d_chrom, static_cast<const uint32_t*>(d_start), static_cast<const uint32_t*>(d_end),
-                                               d_strand, nq, d_off, d_hits, capacity, hits_base, d_base, d_total, d_err, emit_only, st);
+                                               d_strand, nq, d_off, d_hits, capacity, d_base, d_total, d_err, emit_only, st);
 }
 
 gg_status ensure_strand_scratch(gg_index* idx, size_t nq) {
     const size_t m = nq ? nq : 1;
-    GG_CUDA(idx->s_cnt.ensure(m * 4));
-    GG_CUDA(idx->s_hi.ensure(m * 4));
-    GG_CUDA(idx->s_scan.ensure(scan_state_bytes(m)));
+    GG_CUDA(idx->s_cnt.ensure(round_up(m * 4, 256)));
+    GG_CUDA(idx->s_hi.ensure(round_up(m * 4, 256)));
+    GG_CUDA(idx->s_scan.ensure(batch_ctl_bytes(m)));
     GG_CUDA(idx->s_total.ensure(16));
     GG_CUDA(idx->err_flag.ensure(16));
     return GG_OK;
@@ -1489,9 +1510,42 @@ gg_status gg_index_set_strands(gg_index* idx, const uint8_t* strand, size_t n) {
                                                                                  idx->n_chrom, idx->strand.as<uint8_t>());
         e = cudaGetLastError();
     }
+    // per-node strand records (class prefix counts + masks) in chain order and sorted-end order
+    const uint32_t n_nodes = level0_elems >> kFanoutLog2, nn1 = n_nodes + 1;
+    DeviceBuf cntS, cntE, preS, preE, scan_state;
+    if (e == cudaSuccess) e = idx->SN.ensure(static_cast<size_t>(nn1) * sizeof(StrandNode));
+    if (e == cudaSuccess) e = idx->EN.ensure(static_cast<size_t>(nn1) * sizeof(StrandNode));
+    if (e == cudaSuccess) e = cntS.ensure(static_cast<size_t>(nn1) * 16);
+    if (e == cudaSuccess) e = cntE.ensure(static_cast<size_t>(nn1) * 16);
+    if (e == cudaSuccess) e = preS.ensure(static_cast<size_t>(nn1) * 16 + 16);
+    if (e == cudaSuccess) e = preE.ensure(static_cast<size_t>(nn1) * 16 + 16);
+    if (e == cudaSuccess) e = scan_state.ensure(scan_state_bytes(static_cast<size_t>(nn1) * 4));
+    if (e == cudaSuccess) {
+        const unsigned wpb = 8;
+        strand_node_kernel<<<blocks_for(nn1, wpb), wpb * 32, 0, idx->stream>>>(
+            idx->strand.as<uint8_t>(), idx->ER.as<uint32_t>(), idx->tab.as<uint32_t>(), idx->n_chrom, n_nodes,
+            idx->SN.as<StrandNode>(), idx->EN.as<StrandNode>(), cntS.as<uint32_t>(), cntE.as<uint32_t>());
+        e = cudaGetLastError();
+    }
+    // one scan per family over [class][node]: the running count carries across classes, so subtract each class's
+    // start (= pre[k][0]) when packing — done by scanning each class row separately instead
+    for (uint32_t k = 0; k < 4 && e == cudaSuccess; ++k) {
+        e = exclusive_scan_async<uint32_t, uint32_t>(cntS.as<uint32_t>() + static_cast<size_t>(k) * nn1,
+                                                     preS.as<uint32_t>() + static_cast<size_t>(k) * nn1, nn1 - 1, scan_state.p, nullptr,
+                                                     nullptr, idx->stream);
+        if (e == cudaSuccess)
+            e = exclusive_scan_async<uint32_t, uint32_t>(cntE.as<uint32_t>() + static_cast<size_t>(k) * nn1,
+                                                         preE.as<uint32_t>() + static_cast<size_t>(k) * nn1, nn1 - 1, scan_state.p, nullptr,
+                                                         nullptr, idx->stream);
+    }
+    if (e == cudaSuccess) {
+        strand_pack_kernel<<<blocks_for(nn1, 256), 256, 0, idx->stream>>>(preS.as<uint32_t>(), preE.as<uint32_t>(), n_nodes,
+                                                                         idx->SN.as<StrandNode>(), idx->EN.as<StrandNode>());
+        e = cudaGetLastError();
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
     tmp.release();
-    if (e != cudaSuccess) return fail(idx, GG_ERR_CUDA, "gg_index_set_strands", e);
+    for (DeviceBuf* b : {&cntS, &cntE, &preS, &preE, &scan_state}) b->release();
     idx->has_strand = true;
     return GG_OK;
 }
@@ -1516,11 +1570,11 @@ gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, c
     idx->bstats.n_chunks = 1;
     idx->counted_nq = 0;
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
-    s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, 0, nullptr,
+    s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, nullptr,
                           idx->s_total.as<uint64_t>(), idx->err_flag.as<uint32_t>(), false, st);
     if (s != GG_OK) return s;
-    s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, 0, nullptr,
-                          nullptr, nullptr, true, st);
+    s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, nullptr,
+                          nullptr, idx->err_flag.as<uint32_t>(), true, st);
     if (s != GG_OK) return s;
     if (total_hits) {
         uint32_t flag = 0;
@@ -1570,14 +1624,13 @@ gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, co
         GG_CUDA(cudaMemcpyAsync(idx->sq_qe.p, q_end + q0, m * 8, cudaMemcpyHostToDevice, st));
         GG_CUDA(cudaMemcpyAsync(idx->sq_str.p, q_strand + q0, m, cudaMemcpyHostToDevice, st));
         s = dispatch_stranded(idx, idx->sq_qc.as<uint32_t>(), idx->sq_qs.p, idx->sq_qe.p, idx->sq_str.as<uint8_t>(), 8, m,
-                              idx->sq_off.as<uint64_t>(), nullptr, 0, base, idx->d_base.as<uint64_t>(), idx->s_total.as<uint64_t>(),
+                              idx->sq_off.as<uint64_t>(), nullptr, 0, idx->d_base.as<uint64_t>(), idx->s_total.as<uint64_t>(),
                               idx->err_flag.as<uint32_t>(), false, st);
         if (s != GG_OK) return s;
         uint64_t total = 0;
         uint32_t flag = 0;
         GG_CUDA(cudaMemcpyAsync(&total, idx->s_total.p, 8, cudaMemcpyDeviceToHost, st));
         GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
-        GG_CUDA(cudaMemcpyAsync(offsets + q0, idx->sq_off.p, (m + 1) * 8, cudaMemcpyDeviceToHost, st));
         GG_CUDA(cudaStreamSynchronize(st));
         s = strand_query_error(idx, flag);
         if (s != GG_OK) return s;
@@ -1585,8 +1638,9 @@ gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, co
         s = ensure_pinned_hits(idx, base + total, base);
         if (s != GG_OK) return s;
         s = dispatch_stranded(idx, idx->sq_qc.as<uint32_t>(), idx->sq_qs.p, idx->sq_qe.p, idx->sq_str.as<uint8_t>(), 8, m,
-                              idx->sq_off.as<uint64_t>(), idx->sq_hits.as<uint32_t>(), total, base, nullptr, nullptr, nullptr, true, st);
+                              idx->sq_off.as<uint64_t>(), idx->sq_hits.as<uint32_t>(), total, nullptr, nullptr, idx->err_flag.as<uint32_t>(), true, st);
         if (s != GG_OK) return s;
+        GG_CUDA(cudaMemcpyAsync(offsets + q0, idx->sq_off.p, (m + 1) * 8, cudaMemcpyDeviceToHost, st));
         if (total) GG_CUDA(cudaMemcpyAsync(idx->pinned_hits + base, idx->sq_hits.p, total * 4, cudaMemcpyDeviceToHost, st));
         base += total;
         GG_CUDA(cudaMemcpyAsync(idx->d_base.p, &base, 8, cudaMemcpyHostToDevice, st));

@@ -9,12 +9,17 @@
 //     { r : start[r] <= q.end  &&  end[r] >= q.start  &&  compatible(strand[r], q.strand) }   ascending in chain rank,
 // the chain being ordered by (start, end, strand with '*' < '.' < '+' < '-') (genomic_coordinate.hpp:97-110).
 //
-// Same flattened index as the interval path plus one byte per level-0 slot (the strand, padded like the leaf level).  Two passes, no atomics:
-//   pass 1  hi = ub(S, q.end), n_sp = hi - ub(E, q.start - 1) spatial hits (directory + bracketed search, as the
-//           interval count pass); walk back from hi - 1 until n_sp spatial hits were seen (max-end levels skip
-//           subtrees), count the strand-compatible ones -> cnt[q]; hi[q] saved
-//   scan    offsets = exclusive scan of cnt
-//   pass 2  the same walk, writing compatible ranks back to front at offsets[q]
+// Same flattened index as the interval path plus, per level-0 node (32 slots), a 32-byte strand record in chain
+// order (SN) and one in sorted-end order (EN): the number of keys of each strand class ('*', '.', '+', '-') before
+// the node and a 32-bit membership mask per class.  With them the strand-specific count is a closed form, like the
+// interval count — no walk in pass 1:
+//   #{r : start[r] <= q.end, end[r] >= q.start, class(r) in K} = rank_S(K, hi) - rank_E(K, lo),   K = {q.strand, '*'}
+//   (hi = ub(S, q.end), lo = ub(E, q.start - 1): every key with end < q.start also has start <= q.end)
+//   rank_X(K, i) = sum over k in K of pre_X[k][i >> 5] + popc(bits_X[k][i >> 5] & ((1 << (i & 31)) - 1))
+// Three kernels per batch, no atomics, reference order — the shape of the interval batch path:
+//   strand_count_group_kernel (4 consecutive queries per thread, finger search) -> scan of the per-128-query block
+//   totals -> intersect_emit_scan_kernel<.., kStrand = true> (offsets + hits; the walk tests end >= q.start AND the
+//   strand byte of each rank, 8 ranks per step: 32 bytes of ends + 8 strand bytes, SIMD byte compare)
 #pragma once
 #include "intersect.cuh"
 
@@ -88,71 +93,188 @@ __device__ __forceinline__ uint32_t strand_walk(const IndexView<C>& ix, uint32_t
     return compat;
 }
 
-// Pass 1: one query per thread.  err_flag bit 0: start > end; bit 2: strand byte not one of + - . *
-template <typename C, typename Q>
-__global__ void __launch_bounds__(kQueryThreads)
-strand_count_kernel(IndexView<C> ix, const uint8_t* __restrict__ strands, uint32_t slot_base,
-                    const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, const Q* __restrict__ qend,
-                    const uint8_t* __restrict__ qstrand, size_t nq, uint32_t* __restrict__ cnt_out,
-                    uint32_t* __restrict__ hi_out, uint32_t* __restrict__ err_flag) {
-    const uint32_t stride = ix.n_chrom + 1;
-    const size_t n_tiles = (nq + kQueryThreads - 1) / kQueryThreads;
-    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const size_t q = tile * kQueryThreads + threadIdx.x;
-        if (q >= nq) continue;
-        const uint32_t chrom = qchrom[q];
-        const Q qs_raw = qstart[q], qe_raw = qend[q];
-        const uint32_t qst = qstrand[q];
-        const bool bad = qs_raw > qe_raw, bad_strand = !strand_valid(qst);
-        if (bad) atomicOr(err_flag, 1u);
-        if (bad_strand) atomicOr(err_flag, 4u);
-        const bool ok = !bad && !bad_strand && chrom < ix.n_chrom &&
-                        !(sizeof(Q) > sizeof(C) && qs_raw > static_cast<Q>(coord_max<C>::value));
-        uint32_t cnt = 0, hi = 0;
-        if (ok) {
-            const C qe = clamp_coord<C, Q>(qe_raw);
-            const C qs = static_cast<C>(qs_raw);
-            const uint32_t d0 = ix.dir_off[chrom], last_bin = ix.dir_off[chrom + 1] - d0 - 2;
-            const uint32_t leaf = ix.tab[chrom];
-            const C be = qe >> ix.dir_shift;
-            const uint32_t b1 = be > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(be);
-            hi = bracket_upper_bound<C>(ix.S + leaf, ix.dirS[d0 + b1], ix.dirS[d0 + b1 + 1], qe);
-            uint32_t lo = 0;
-            if (qs > 0) {
-                const C xe = static_cast<C>(qs - 1);
-                const C bs = xe >> ix.dir_shift;
-                const uint32_t b2 = bs > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(bs);
-                lo = bracket_upper_bound<C>(ix.E + leaf, ix.dirE[d0 + b2], ix.dirE[d0 + b2 + 1], xe);
+// ---- per-node strand records ---------------------------------------------------------------------------------
+struct StrandNode {
+    uint32_t pre[4];   // keys of class k ('*', '.', '+', '-') in all level-0 slots before this node (global, all chromosomes)
+    uint32_t bits[4];  // bit j: slot 32 * node + j holds a key of class k
+};
+static_assert(sizeof(StrandNode) == 32, "one 32-byte sector per node");
+
+__device__ __forceinline__ uint32_t strand_class(uint32_t s) { return s == '*' ? 0u : s == '.' ? 1u : s == '+' ? 2u : 3u; }
+
+// One warp per level-0 node: class masks of the node in chain order (from the padded strand bytes) and in
+// sorted-end order (strand of the interval whose end sits in each slot, through ER); per-class key counts go to
+// cnt_S / cnt_E [class][node] for the prefix scans.  Node n_nodes is the sentinel behind the last chromosome.
+__global__ void strand_node_kernel(const uint8_t* __restrict__ strandP, const uint32_t* __restrict__ ER,
+                                   const uint32_t* __restrict__ row0, uint32_t n_chrom, uint32_t n_nodes,
+                                   StrandNode* __restrict__ SN, StrandNode* __restrict__ EN, uint32_t* __restrict__ cnt_S,
+                                   uint32_t* __restrict__ cnt_E) {
+    const uint32_t node = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (node > n_nodes) return;
+    const uint32_t lane = lane_id();
+    uint32_t bs = 0, be = 0;  // strand byte of this lane's slot in either order (0 = pad)
+    if (node < n_nodes) {
+        const uint32_t slot = (node << kFanoutLog2) + lane;
+        bs = strandP[slot];
+        const uint32_t rank = ER[slot];
+        if (rank != 0xFFFFFFFFu) {
+            uint32_t lo = 0, hi = n_chrom;  // chromosome owning this node
+            const uint32_t p = row0[0] + slot;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (row0[mid] <= p) lo = mid; else hi = mid;
             }
-            const uint32_t n_sp = hi - lo;
-            if (n_sp != 0)
-                cnt = qst == '*' ? n_sp  // the wildcard query matches every strand (genomic_coordinate.hpp:158)
-                                 : strand_walk<C, false>(ix, stride, ix.n_levels, chrom, qs, hi, n_sp, strands + (leaf - slot_base), qst, nullptr);
+            be = strandP[row0[lo] - row0[0] + rank];
         }
-        cnt_out[q] = cnt;
-        hi_out[q] = hi;
+    }
+#pragma unroll
+    for (uint32_t k = 0; k < 4; ++k) {
+        const uint32_t sym = k == 0 ? '*' : k == 1 ? '.' : k == 2 ? '+' : '-';
+        const uint32_t ms = __ballot_sync(0xffffffffu, bs == sym), me = __ballot_sync(0xffffffffu, be == sym);
+        if (lane == 0) {
+            SN[node].bits[k] = ms;
+            EN[node].bits[k] = me;
+            cnt_S[k * (n_nodes + 1) + node] = __popc(ms);
+            cnt_E[k * (n_nodes + 1) + node] = __popc(me);
+        }
     }
 }
 
-// Pass 2: hits[offsets[q] - hits_base ...) = compatible chain ranks, ascending.  Ranks at or beyond `capacity` are
-// not written (the caller sized the buffer from offsets[nq]).
-template <typename C, typename Q>
+// scanned per-class counts [class][node] -> the records' pre[] fields
+__global__ void strand_pack_kernel(const uint32_t* __restrict__ pre_S, const uint32_t* __restrict__ pre_E, uint32_t n_nodes,
+                                   StrandNode* __restrict__ SN, StrandNode* __restrict__ EN) {
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node > n_nodes) return;
+#pragma unroll
+    for (uint32_t k = 0; k < 4; ++k) {
+        SN[node].pre[k] = pre_S[k * (n_nodes + 1) + node];
+        EN[node].pre[k] = pre_E[k * (n_nodes + 1) + node];
+    }
+}
+
+// keys of class `cls` or '*' among the first i slots of the chromosome whose first node is node0 (global count)
+__device__ __forceinline__ uint32_t strand_rank(const StrandNode* __restrict__ N, uint32_t node0, uint32_t i, uint32_t cls) {
+    const uint4* rec = reinterpret_cast<const uint4*>(N + node0 + (i >> kFanoutLog2));
+    const uint4 pre = rec[0], bits = rec[1];
+    const uint32_t below = (1u << (i & 31u)) - 1u;
+    const uint32_t pc = cls == 1 ? pre.y : cls == 2 ? pre.z : pre.w, bc = cls == 1 ? bits.y : cls == 2 ? bits.z : bits.w;
+    return pre.x + pc + __popc((bits.x | bc) & below);
+}
+
+// Pass 1: QPT consecutive queries per thread — the interval count pass (count_group: directory + finger search)
+// followed by the closed-form strand count.  Outputs as intersect_count_group_kernel: cnt / hi per query and
+// block_total[b] = hits of the b-th block of 32 * QPT queries.  err_flag bit 0: start > end; bit 2: a strand byte
+// outside "+-.*" (genomic_coordinate's constructor check, genomic_coordinate.hpp:78-81).
+template <typename C, typename Q, int QPT>
 __global__ void __launch_bounds__(kQueryThreads)
-strand_emit_kernel(IndexView<C> ix, const uint8_t* __restrict__ strands, uint32_t slot_base,
-                   const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, const uint8_t* __restrict__ qstrand,
-                   size_t nq, const uint32_t* __restrict__ hi_in, const uint64_t* __restrict__ offsets,
-                   uint32_t* __restrict__ hits, uint64_t hits_base, uint64_t capacity) {
-    const uint32_t stride = ix.n_chrom + 1;
-    const size_t n_tiles = (nq + kQueryThreads - 1) / kQueryThreads;
+strand_count_group_kernel(IndexView<C> ix, const StrandNode* __restrict__ SN, const StrandNode* __restrict__ EN,
+                          uint32_t slot_base, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
+                          const Q* __restrict__ qend, const uint8_t* __restrict__ qstrand, size_t nq,
+                          uint32_t* __restrict__ cnt_out, uint32_t* __restrict__ hi_out,
+                          unsigned long long* __restrict__ block_total, uint32_t* __restrict__ err_flag, int vec_ok) {
+    constexpr size_t kTileQ = static_cast<size_t>(kQueryThreads) * QPT;
+    const size_t n_tiles = (nq + kTileQ - 1) / kTileQ;
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const size_t q = tile * kQueryThreads + threadIdx.x;
-        if (q >= nq) continue;
-        const uint64_t o0 = offsets[q], o1 = offsets[q + 1];
-        const uint32_t n = static_cast<uint32_t>(o1 - o0);
-        if (n == 0 || o1 - hits_base > capacity) continue;
-        const uint32_t chrom = qchrom[q];
-        strand_walk<C, true>(ix, stride, ix.n_levels, chrom, static_cast<C>(qstart[q]), hi_in[q], n,
-                             strands + (ix.tab[chrom] - slot_base), qstrand[q], hits + (o0 - hits_base));
+        const size_t q0 = tile * kTileQ + static_cast<size_t>(threadIdx.x) * QPT;
+        const bool vec = vec_ok && q0 + QPT <= nq;
+        uint32_t chrom[QPT], qst[QPT];
+        Q qs_raw[QPT], qe_raw[QPT];
+        if (vec) {
+            load_vec_stream<uint32_t, QPT>(qchrom + q0, chrom);
+            load_vec_stream<Q, QPT>(qstart + q0, qs_raw);
+            load_vec_stream<Q, QPT>(qend + q0, qe_raw);
+        } else {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j) {
+                const bool in = q0 + j < nq;
+                chrom[j] = in ? qchrom[q0 + j] : GG_NO_CHROM_DEV;
+                qs_raw[j] = in ? qstart[q0 + j] : Q(0);
+                qe_raw[j] = in ? qend[q0 + j] : Q(0);
+            }
+        }
+        bool bad_strand = false;
+#pragma unroll
+        for (int j = 0; j < QPT; ++j) {
+            qst[j] = q0 + j < nq ? qstrand[q0 + j] : uint32_t('*');
+            if (!strand_valid(qst[j])) {
+                bad_strand = true;
+                chrom[j] = GG_NO_CHROM_DEV;  // no hits for this query; the call fails with the flag below
+            }
+        }
+        uint32_t cnt[QPT], hi[QPT];
+        C qs[QPT];
+        uint32_t flags = count_group<C, Q, QPT>(ix, ix.tab, chrom, qs_raw, qe_raw, cnt, hi, qs) ? 1u : 0u;
+        if (bad_strand) flags |= 4u;
+        if (flags) atomicOr(err_flag, flags);
+#pragma unroll
+        for (int j = 0; j < QPT; ++j) {
+            if (cnt[j] != 0 && qst[j] != '*') {  // the wildcard query matches every strand: cnt = spatial count
+                const uint32_t node0 = (ix.tab[chrom[j]] - slot_base) >> kFanoutLog2, cls = strand_class(qst[j]);
+                cnt[j] = strand_rank(SN, node0, hi[j], cls) - strand_rank(EN, node0, hi[j] - cnt[j], cls);
+            }
+        }
+        if (vec) {
+            store_vec_u32<QPT>(cnt_out + q0, cnt);
+            store_vec_u32<QPT>(hi_out + q0, hi);
+        } else {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j) {
+                if (q0 + j < nq) {
+                    cnt_out[q0 + j] = cnt[j];
+                    hi_out[q0 + j] = hi[j];
+                }
+            }
+        }
+        unsigned long long wsum = 0;
+#pragma unroll
+        for (int j = 0; j < QPT; ++j) wsum += cnt[j];
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        if (lane_id() == 0) {
+            const size_t wq0 = tile * kTileQ + static_cast<size_t>(threadIdx.x & ~31u) * QPT;  // the warp's first query
+            if (wq0 < nq) block_total[wq0 / (32 * QPT)] = wsum;
+        }
+    }
+}
+
+}  // namespace gg
+
+namespace gg {
+
+// The staged backward walk of emit_scan (emit_walk_staged8 in intersect.cuh) with the strand test: ranks hi-1,
+// hi-2, ... in aligned groups of 8; a hit must have end >= q.start AND a compatible strand byte.  Hits go to the
+// shared-memory stage back to front until the query's list [s_begin, s_end) is full (its length is the exact
+// number of compatible hits, so nothing below the last one written can still match).
+template <typename C>
+__device__ __forceinline__ void emit_walk_staged8_strand(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
+                                                         int n_levels, uint32_t chrom, C qs, uint32_t hi,
+                                                         const uint8_t* __restrict__ strands, uint32_t q_strand,
+                                                         uint32_t s_begin, uint32_t s_end) {
+    const C* __restrict__ leaf_end = ix.M + tabp[chrom];
+    const uint32_t q4 = q_strand * 0x01010101u;
+    const bool wild = q_strand == '*';
+    const bool has_levels = n_levels > 1;
+    uint32_t r_hi = hi, sp = s_end;
+    C ea[8];
+    while (sp > s_begin && r_hi != 0) {
+        if ((r_hi & (kFanout - 1)) == 0 && has_levels) {
+            const uint32_t span = emit_skip_span<C>(ix, tabp, stride, n_levels, chrom, qs, r_hi);
+            if (span) {
+                r_hi -= span;
+                continue;
+            }
+        }
+        const uint32_t g8 = (r_hi - 1) & ~7u, top = r_hi - g8;
+        load8(leaf_end + g8, ea);
+        const uint2 sw = *reinterpret_cast<const uint2*>(strands + g8);
+        const uint32_t m_lo = wild ? 0xFFFFFFFFu : strand_compat4(sw.x, q4), m_hi = wild ? 0xFFFFFFFFu : strand_compat4(sw.y, q4);
+#pragma unroll
+        for (int k = 7; k >= 0; --k) {
+            const bool ok = static_cast<uint32_t>(k) < top && ea[k] >= qs && (((k < 4 ? m_lo : m_hi) >> (8 * (k & 3))) & 1u) &&
+                            sp > s_begin;
+            if (ok) { sp -= 4; sts32(sp, g8 + k); }
+        }
+        r_hi = g8;
     }
 }
 
