@@ -92,3 +92,29 @@ def test_isec_matches_oracle(tmp_path, sorted_target):
             i = perm[base + int(r)]
             lines.append(f"{names[chrom[i]]}\t{s[i]}\t{e[i]}\n")
     assert got == "".join(lines)
+
+
+GFF_TARGET = ("##gff-version 3\nchr1\ttest\tgene\t101\t500\t.\t+\t.\tID=gene1\nchr1\ttest\tgene\t601\t900\t.\t-\t.\tID=gene2\n"
+              "chr2\ttest\tgene\t201\t400\t.\t+\t.\tID=gene3\n")
+GFF_QUERY = ("##gff-version 3\nchr1\ttest\texon\t151\t250\t.\t+\t.\tID=q1;Parent=gene1\n"
+             "chr1\ttest\texon\t851\t950\t.\t-\t.\tID=q2;Parent=gene2\nchr2\ttest\texon\t501\t600\t.\t+\t.\tID=q3\n")
+
+
+@pytest.mark.gpu
+def test_isec_gff_and_cross_type_known_answers(tmp_path):
+    """tests/cli/intersect-e2e-test.cpp:371-385 (GFF vs GFF), :431-443 (BED query vs GFF target), :445-461 (GFF query vs
+    BED target), with the content of tests/cli/data/{target,query}.{gff,bed}."""
+    tg, qg = tmp_path / "target.gff", tmp_path / "query.gff"
+    tb, qb = tmp_path / "target.bed", tmp_path / "query.bed"
+    tg.write_text(GFF_TARGET)
+    qg.write_text(GFF_QUERY)
+    tb.write_text("chr1\t100\t500\nchr1\t600\t900\nchr2\t200\t400\n")
+    qb.write_text("chr1\t150\t250\nchr1\t850\t950\nchr2\t500\t600\n")
+    assert _run(["-q", str(qg), "-t", str(tg)]).stdout == "chr1\t101\t500\nchr1\t601\t900\n"
+    assert _run(["-q", str(qb), "-t", str(tg)]).stdout == "chr1\t101\t500\nchr1\t601\t900\n"
+    assert _run(["-q", str(qg), "-t", str(tb)]).stdout == "chr1\t100\t500\nchr1\t600\t900\n"
+    # 1-based inclusive vs 0-based half-open: GFF [501,600] == BED [500,600): touches BED target [100,500)? no.
+    qg.write_text("chr1\t.\tx\t500\t500\t.\t+\t.\tID=a\nchr1\t.\tx\t501\t501\t.\t+\t.\tID=b\n")
+    assert _run(["-q", str(qg), "-t", str(tb)]).stdout == "chr1\t100\t500\n"  # base 500 (1-based) = 0-based 499: inside [100,500)
+    qg.write_text("chr1\t.\tx\t0\t5\t.\t+\t.\tID=a\n")
+    assert "Invalid GFF coordinates" in _run(["-q", str(qg), "-t", str(tb)], 1).stderr

@@ -8,8 +8,12 @@
 // calls grove.intersect once per query line; this reads the whole query file into structure-of-arrays buffers and
 // makes ONE grove.intersect_batch call (count -> scan -> emit on the device), then prints from the CSR result.
 //
-//   gg_isec -q query.bed -t target.bed [-o out.bed] [-k order] [-s]     (-s: target is sorted -> sorted inserts)
+//   gg_isec -q query.{bed,gff,gtf} -t target.{bed,gff,gtf} [-o out] [-k order] [-s]   (-s: target is sorted -> sorted inserts)
 //
+// GFF/GTF files (by extension .gff / .gff3 / .gtf) are accepted on either side, as in the reference CLI: 1-based
+// inclusive [start, end] becomes interval(start - 1, end - 1) (cli/src/handlers/gff.cpp:22-30,
+// cli/include/handlers/gff.hpp:52-57), so BED and GFF records meet in one 0-based closed space and cross-type queries
+// work; a hit prints the target record's own seqid / start / end (gff.hpp:61-63, bed.hpp:60-62).
 // BED parsing follows io/bed_reader.cpp:395-431 for the three mandatory columns: tab/space separated, digits only,
 // start < end, else the run fails with the reader's message.  Lines that are empty or start with '#', "track" or
 // "browser" are skipped.
@@ -28,10 +32,19 @@
 namespace gdt = genogrove_b200::data_type;
 namespace gst = genogrove_b200::structure;
 
-struct bed3 {
+struct bed3 {  // one target / query record: the printed fields + its 0-based closed interval
     std::string chrom;
-    std::size_t start = 0, end = 0;
+    std::size_t start = 0, end = 0;  // as written in the file (what a hit prints)
+    std::size_t lo = 0, hi = 0;      // canonical closed interval: BED [start, end - 1], GFF [start - 1, end - 1]
 };
+
+static bool is_gff(const std::string& path) {
+    auto ends = [&](const char* suf) {
+        const std::size_t n = std::strlen(suf);
+        return path.size() >= n && path.compare(path.size() - n, n, suf) == 0;
+    };
+    return ends(".gff") || ends(".gff3") || ends(".gtf");
+}
 
 static bool skip_line(std::string_view l) {
     return l.empty() || l[0] == '#' || l.substr(0, 5) == "track" || l.substr(0, 7) == "browser";
@@ -67,11 +80,49 @@ static void for_each_bed(const std::string& path, F&& cb) {
         const std::string_view l(line);
         const std::string_view c = next_field(l, pos), s = next_field(l, pos), e = next_field(l, pos);
         if (c.empty() || s.empty() || e.empty()) throw std::runtime_error("Invalid line format at line " + std::to_string(line_num));
-        bed3 r{std::string(c), parse_coord(s, line_num), parse_coord(e, line_num)};
+        bed3 r{std::string(c), parse_coord(s, line_num), parse_coord(e, line_num), 0, 0};
         if (r.start >= r.end)
             throw std::runtime_error("Start coordinate is greater than or equal to the end coordinate at line " + std::to_string(line_num));
+        r.lo = r.start;
+        r.hi = r.end - 1;
         cb(std::move(r));
     }
+}
+
+// GFF3 / GTF: 9 tab-separated columns, seqid = 1, start = 4, end = 5 (1-based inclusive, start <= end, start >= 1)
+template <typename F>
+static void for_each_gff(const std::string& path, F&& cb) {
+    std::ifstream in(path);
+    if (!in) throw std::runtime_error("Failed to open file: " + path);
+    std::string line;
+    std::size_t line_num = 0;
+    while (std::getline(in, line)) {
+        ++line_num;
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        if (line.empty() || line[0] == '#') continue;
+        std::string_view l(line), col[5];
+        std::size_t pos = 0;
+        int k = 0;
+        for (; k < 5 && pos <= l.size(); ++k) {
+            const std::size_t t = l.find('\t', pos);
+            col[k] = l.substr(pos, t == std::string_view::npos ? std::string_view::npos : t - pos);
+            if (t == std::string_view::npos) { ++k; break; }
+            pos = t + 1;
+        }
+        if (k < 5 || col[0].empty()) throw std::runtime_error("Invalid line format at line " + std::to_string(line_num));
+        bed3 r{std::string(col[0]), parse_coord(col[3], line_num), parse_coord(col[4], line_num), 0, 0};
+        if (r.start < 1 || r.start > r.end)
+            throw std::runtime_error("Invalid GFF coordinates at line " + std::to_string(line_num));
+        r.lo = r.start - 1;
+        r.hi = r.end - 1;
+        cb(std::move(r));
+    }
+}
+
+template <typename F>
+static void for_each_record(const std::string& path, F&& cb) {
+    if (is_gff(path)) for_each_gff(path, cb);
+    else for_each_bed(path, cb);
 }
 
 int main(int argc, char** argv) {
@@ -106,8 +157,8 @@ int main(int argc, char** argv) {
         if (order < 3) throw std::runtime_error("Error: order must be at least 3");
 
         gst::grove<gdt::interval, bed3> grove(order);
-        for_each_bed(target, [&](bed3 r) {
-            const gdt::interval iv(r.start, r.end - 1);
+        for_each_record(target, [&](bed3 r) {
+            const gdt::interval iv(r.lo, r.hi);
             std::string chrom = r.chrom;
             if (sorted) grove.insert_data(chrom, iv, std::move(r), gst::sorted);
             else grove.insert_data(chrom, iv, std::move(r));
@@ -116,10 +167,10 @@ int main(int argc, char** argv) {
         // the whole query file -> SoA buffers -> one batch call
         std::vector<std::uint32_t> qc;
         std::vector<std::uint64_t> qs, qe;
-        for_each_bed(query, [&](bed3 r) {
+        for_each_record(query, [&](bed3 r) {
             qc.push_back(grove.index_id(r.chrom));  // npos_index for a chromosome the target lacks: no hits
-            qs.push_back(r.start);
-            qe.push_back(r.end - 1);
+            qs.push_back(r.lo);
+            qe.push_back(r.hi);
         });
         auto res = grove.intersect_batch(qc.data(), qs.data(), qe.data(), qc.size());
 
