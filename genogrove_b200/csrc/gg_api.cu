@@ -104,7 +104,6 @@ struct gg_index {
 
     // ---- two-phase host API state
     DeviceBuf h2_qc, h2_qs, h2_qe, h2_off, h2_hits;
-    DeviceBuf fl_qc, fl_qs, fl_qe, fl_pred, fl_succ;  // gg_flanking_batch staging
     DeviceBuf strand;        // u8 per level-0 slot ('+', '-', '.', '*'; pads 0), gg_index_set_strands
     DeviceBuf SN, EN;        // StrandNode per level-0 node (+1 sentinel) in chain order / sorted-end order (strand.cuh)
     bool has_strand = false;
@@ -1041,7 +1040,7 @@ void gg_index_destroy(gg_index* idx) {
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
                          &idx->ER, &idx->cbegin, &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
-                         &idx->s_cnt, &idx->s_hi, &idx->s_scan, &idx->s_total, &idx->fl_qc, &idx->fl_qs, &idx->fl_qe, &idx->fl_pred, &idx->fl_succ})
+                         &idx->s_cnt, &idx->s_hi, &idx->s_scan, &idx->s_total})
         b->release();
     for (auto& s : idx->slots) {
         for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan, &s.fscratch, &s.err}) b->release();
@@ -1378,24 +1377,32 @@ gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64
     cudaStream_t st = idx->stream;
     GG_CUDA(idx->err_flag.ensure(16));
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    GG_CUDA(cudaStreamSynchronize(st));  // the flag is clear before any slot stream touches it
+    gg_status s = ensure_slots(idx);
+    if (s != GG_OK) return s;
+    // chunks round-robin over the pipeline slots' streams: H2D of chunk k+1 and D2H of chunk k-1 overlap kernel k
     const size_t chunk = static_cast<size_t>(std::max<int64_t>(idx->chunk_queries, 1024));
     const size_t cap = std::min(chunk, nq ? nq : 1);
-    GG_CUDA(idx->fl_qc.ensure(cap * 4));
-    GG_CUDA(idx->fl_qs.ensure(cap * 8));
-    GG_CUDA(idx->fl_qe.ensure(cap * 8));
-    GG_CUDA(idx->fl_pred.ensure(cap * 4));
-    GG_CUDA(idx->fl_succ.ensure(cap * 4));
-    for (size_t q0 = 0; q0 < nq; q0 += chunk) {
+    size_t k = 0;
+    for (size_t q0 = 0; q0 < nq; q0 += chunk, ++k) {
+        Slot& sl = idx->slots[k % kSlots];
         const size_t m = std::min(chunk, nq - q0);
-        GG_CUDA(cudaMemcpyAsync(idx->fl_qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, st));
-        GG_CUDA(cudaMemcpyAsync(idx->fl_qs.p, q_start + q0, m * 8, cudaMemcpyHostToDevice, st));
-        GG_CUDA(cudaMemcpyAsync(idx->fl_qe.p, q_end + q0, m * 8, cudaMemcpyHostToDevice, st));
-        gg_status s = dispatch_flanking(idx, idx->fl_qc.as<uint32_t>(), idx->fl_qs.p, idx->fl_qe.p, 8, m,
-                                        idx->fl_pred.as<uint32_t>(), idx->fl_succ.as<uint32_t>(), idx->err_flag.as<uint32_t>(), st);
+        if (k >= kSlots) GG_CUDA(cudaStreamSynchronize(sl.st));  // (buffers below may be regrown only when idle)
+        GG_CUDA(sl.qc.ensure(cap * 4));
+        GG_CUDA(sl.qs.ensure(cap * 8));
+        GG_CUDA(sl.qe.ensure(cap * 8));
+        GG_CUDA(sl.cnt.ensure(cap * 4));
+        GG_CUDA(sl.hi.ensure(cap * 4));
+        GG_CUDA(cudaMemcpyAsync(sl.qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qs.p, q_start + q0, m * 8, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qe.p, q_end + q0, m * 8, cudaMemcpyHostToDevice, sl.st));
+        s = dispatch_flanking(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, 8, m, sl.cnt.as<uint32_t>(), sl.hi.as<uint32_t>(),
+                              idx->err_flag.as<uint32_t>(), sl.st);
         if (s != GG_OK) return s;
-        GG_CUDA(cudaMemcpyAsync(pred + q0, idx->fl_pred.p, m * 4, cudaMemcpyDeviceToHost, st));
-        GG_CUDA(cudaMemcpyAsync(succ + q0, idx->fl_succ.p, m * 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(pred + q0, sl.cnt.p, m * 4, cudaMemcpyDeviceToHost, sl.st));
+        GG_CUDA(cudaMemcpyAsync(succ + q0, sl.hi.p, m * 4, cudaMemcpyDeviceToHost, sl.st));
     }
+    for (int i = 0; i < kSlots; ++i) GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
     return check_query_error(idx, st);  // synchronises the stream
 }
 
