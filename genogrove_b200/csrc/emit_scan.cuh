@@ -18,6 +18,7 @@ namespace gg {
 
 constexpr uint32_t kEmitScanSlack = 8;  // spare slots in front of each warp's stage (see emit_walk_staged)
 
+// kDense: intersect_emit_dense_kernel follows and writes the tiles with >= kDenseMin hits (skipped here).
 // kStrand (genomic_coordinate keys, strand.cuh): cnt_in holds the strand-compatible counts and the walk also tests
 // the strand byte of every rank against qstrand[q]; strands = padded level-0 strand bytes, slot_base = tab[0][0].
 struct StrandArgs {
@@ -26,7 +27,83 @@ struct StrandArgs {
     uint32_t slot_base;
 };
 
-template <typename C, typename Q, int kWalk, bool kStrand = false>
+// Warp tiles whose hit lists do not fit the stage (dense indexes, long nested intervals: cfg5 has ~150 hits per query,
+// GENCODE-shaped cfg3 ~20).  All 32 lanes keep walking their own queries concurrently; each lane owns a private
+// 16-entry segment of the warp's stage, fills it back to front, and when no lane can take another 8-rank group the
+// warp flushes all segments: a lane's segment is a contiguous run of its output list, so it goes out as 64-byte
+// pieces written by 16 threads each (whole 32-byte sectors instead of one 4-byte store per hit and lane — the direct
+// walk costs 8x the L2 write transactions).  Runs in its own kernel (intersect_emit_dense_kernel) so the common
+// path keeps its register budget.
+constexpr uint32_t kDenseSeg = kEmitStage / 32;  // stage entries per lane (16)
+// Tiles between the stage size and this many hits are walked straight to global memory by intersect_emit_scan_kernel
+// (skewed lists: a few long ones among short ones — GENCODE-shaped data — gain nothing from the segment flush);
+// from 64 hits per query on average the 8x saving in L2 write transactions wins (cfg5: 201 -> 89 ms).
+constexpr uint32_t kDenseMin = 2048;
+
+template <typename C, bool kStrand>
+__device__ __forceinline__ void emit_dense_tile(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
+                                                int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t c, uint64_t o_lo,
+                                                uint32_t stage_addr, uint32_t* __restrict__ out, uint64_t room,
+                                                const uint8_t* __restrict__ strands, uint32_t q_strand) {
+    static_assert(kDenseSeg == 16, "flush assumes two 16-entry segments per warp-wide store");
+    const uint32_t lane = lane_id();
+    const C* __restrict__ leaf_end = ix.M + (c != 0 ? tabp[chrom] : 0u);
+    const uint32_t q4 = q_strand * 0x01010101u;
+    const bool wild = !kStrand || q_strand == '*';
+    const uint32_t seg_addr = stage_addr + lane * (kDenseSeg * 4u);
+    uint32_t left = c, r_hi = hi;  // hits still to write (the next one goes to out[o_lo + left - 1])
+    C ea[8];
+    while (__any_sync(0xffffffffu, left != 0)) {
+        uint32_t n = 0;  // entries in this lane's segment: slots [kDenseSeg - n, kDenseSeg)
+        while (left != 0 && n + 8 <= kDenseSeg && r_hi != 0) {
+            if ((r_hi & (kFanout - 1)) == 0 && n_levels > 1) {
+                const uint32_t span = emit_skip_span<C>(ix, tabp, stride, n_levels, chrom, qs, r_hi);
+                if (span) {
+                    r_hi -= span;
+                    continue;
+                }
+            }
+            const uint32_t g8 = (r_hi - 1) & ~7u, top = r_hi - g8;
+            load8(leaf_end + g8, ea);
+            uint32_t m_lo = 0xFFFFFFFFu, m_hi = 0xFFFFFFFFu;
+            if (kStrand && !wild) {
+                const uint2 sw = *reinterpret_cast<const uint2*>(strands + g8);
+                m_lo = strand_compat4(sw.x, q4);
+                m_hi = strand_compat4(sw.y, q4);
+            }
+#pragma unroll
+            for (int k = 7; k >= 0; --k) {
+                const bool ok = static_cast<uint32_t>(k) < top && ea[k] >= qs && (((k < 4 ? m_lo : m_hi) >> (8 * (k & 3))) & 1u) &&
+                                left != 0;
+                if (ok) {
+                    --left;
+                    ++n;
+                    sts32(seg_addr + (kDenseSeg - n) * 4u, g8 + k);
+                }
+            }
+            r_hi = g8;
+        }
+        if (r_hi == 0) left = 0;  // (cannot happen with counts that match the index; keeps the loop finite)
+        __syncwarp();
+        // flush: segment s (lane s) holds n_s entries for out[o_lo_s + left_s ...]; 16 threads per segment, two segments
+        // per step (positions are tile-local and fit 32 bits: the tile has fewer than 2^31 hits)
+        const uint32_t dst0 = static_cast<uint32_t>(o_lo) + left;
+        const uint32_t e = lane & 15u, half = lane >> 4;
+        const uint32_t room32 = room > 0xFFFFFFFFull ? 0xFFFFFFFFu : static_cast<uint32_t>(room);
+        if (__any_sync(0xffffffffu, n != 0)) {
+#pragma unroll 4
+            for (uint32_t j = 0; j < 16; ++j) {
+                const uint32_t sgm = 2 * j + half;
+                const uint32_t n_s = __shfl_sync(0xffffffffu, n, sgm);
+                const uint32_t pos = __shfl_sync(0xffffffffu, dst0, sgm) + e;
+                if (e < n_s && pos < room32) __stcs(out + pos, lds32(stage_addr + (sgm * kDenseSeg + (kDenseSeg - n_s) + e) * 4u));
+            }
+        }
+        __syncwarp();
+    }
+}
+
+template <typename C, typename Q, int kWalk, bool kStrand = false, bool kDense = false>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
                            const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
@@ -130,13 +207,87 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                         if (wbase + i < capacity) hits[wbase + i] = lds32(sa);
                 }
                 __syncwarp();
-            } else if (c != 0 && wbase + excl + c <= capacity) {
+            } else if (kDense && wtotal >= kDenseMin && wtotal < (1ull << 31)) {
+                // a dense tile: intersect_emit_dense_kernel finds it from the per-tile totals of the count pass and writes it
+            } else if (c != 0 && wbase + excl + c <= capacity) {  // too large for the stage but not dense: straight to global memory
                 if (kStrand)
                     strand_walk<C, true>(ix, stride, n_levels, chrom, qs, hi, c, sa.strands + (tabp[chrom] - sa.slot_base), qst,
                                          hits + wbase + excl);
                 else
                     emit_walk_global<C>(ix, tabp, stride, n_levels, chrom, qs, hi, hits + wbase + excl, c);
             }
+        }
+    }
+}
+
+// Second half of pass 2, enqueued right after intersect_emit_scan_kernel: writes the hit lists of the warp tiles that
+// kernel skipped (at least kDenseMin hits in 32 consecutive queries).  tile_total[t] (u32, saturating; written by the
+// count pass) says which tiles those are, so a batch without any costs one coalesced read of 4 bytes per 32 queries.
+// A warp takes a dense tile, rebuilds its CSR base from block_prefix and the tile totals before it in the block,
+// scans the 32 counts and writes the lists through emit_dense_tile.  Offsets were stored by the first kernel.
+template <typename C, typename Q, bool kStrand>
+__global__ void __launch_bounds__(kQueryThreads)
+intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
+                            const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
+                            const uint64_t* __restrict__ block_prefix, const uint32_t* __restrict__ tile_total,
+                            uint32_t blk_q, uint32_t* __restrict__ hits, uint64_t capacity, StrandArgs sa) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr uint32_t kStageWords = kEmitStage + kEmitScanSlack;
+    constexpr uint32_t kWarps = kQueryThreads / 32;
+    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
+    const uint32_t stage_addr = smem_u32(smem_raw) + (warp * kStageWords + kEmitScanSlack) * 4u;
+    const uint32_t stride = ix.n_chrom + 1;
+    const int n_levels = ix.n_levels;
+    const uint32_t* __restrict__ tabp = ix.tab;
+    const size_t n_tiles = (nq + 31) / 32;
+    const uint32_t tiles_per_blk = blk_q / 32;
+    const size_t warps_total = static_cast<size_t>(gridDim.x) * kWarps;
+    // 32 tiles per warp step: one coalesced read of their totals, then the dense ones (rare) one after the other
+    for (size_t t0 = (static_cast<size_t>(blockIdx.x) * kWarps + warp) * 32; t0 < n_tiles; t0 += warps_total * 32) {
+        const uint32_t my_total = t0 + lane < n_tiles ? tile_total[t0 + lane] : 0u;
+        uint32_t dense = __ballot_sync(0xffffffffu, my_total >= kDenseMin);
+        while (dense != 0) {
+            const uint32_t j = __ffs(dense) - 1;
+            dense &= dense - 1;
+            const size_t t = t0 + j;
+            const size_t blk = t / tiles_per_blk;
+            uint64_t tile_base = block_prefix[blk];
+            bool exact = true;  // a saturated total in front of this tile: fall back to summing the counts
+            for (size_t u = blk * tiles_per_blk; u < t; ++u) {
+                const uint32_t v = tile_total[u];
+                exact &= v != 0xFFFFFFFFu;
+                tile_base += v;
+            }
+            if (!exact) {
+                tile_base = block_prefix[blk];
+                for (size_t qq = blk * blk_q + lane; qq < t * 32; qq += 32) tile_base += cnt_in[qq];  // per-lane partial sums
+                uint64_t part = tile_base - block_prefix[blk];
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+                tile_base = block_prefix[blk] + part;
+            }
+            const size_t q = t * 32 + lane;
+            const uint32_t c = q < nq ? cnt_in[q] : 0u;
+            uint64_t inc = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint64_t o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= static_cast<uint32_t>(d)) inc += o;
+            }
+            const uint64_t excl = inc - c, wtotal = __shfl_sync(0xffffffffu, inc, 31);
+            if (wtotal >= (1ull << 31)) continue;  // written by intersect_emit_scan_kernel itself
+            const uint64_t wbase = tile_base - block_prefix[0];
+            uint32_t chrom = 0, hi = 0, qst = 0;
+            C qs = 0;
+            if (c != 0) {
+                chrom = qchrom[q];
+                qs = static_cast<C>(qstart[q]);
+                hi = hi_in[q];
+                if (kStrand) qst = sa.qstrand[q];
+            }
+            const uint8_t* strands = kStrand && c != 0 ? sa.strands + (tabp[chrom] - sa.slot_base) : nullptr;
+            const uint64_t room = capacity > wbase ? capacity - wbase : 0ull;  // positions of this tile that fit the buffer
+            emit_dense_tile<C, kStrand>(ix, tabp, stride, n_levels, chrom, qs, hi, c, excl, stage_addr, hits + wbase, room, strands, qst);
         }
     }
 }

@@ -108,7 +108,7 @@ struct gg_index {
     DeviceBuf SN, EN;        // StrandNode per level-0 node (+1 sentinel) in chain order / sorted-end order (strand.cuh)
     bool has_strand = false;
     DeviceBuf sq_qc, sq_qs, sq_qe, sq_str, sq_off, sq_hits;  // gg_intersect_batch_stranded staging
-    DeviceBuf s_cnt, s_hi, s_scan, s_total;                   // stranded path scratch (device calls too)
+    DeviceBuf s_cnt, s_hi, s_tile, s_scan, s_total;                   // stranded path scratch (device calls too)
     size_t h2_nq = 0;
     uint64_t h2_total = 0;
     bool h2_valid = false;
@@ -129,6 +129,9 @@ struct gg_index {
     int64_t emit_ctas_per_sm = 0;
     int64_t fused_ctas_per_sm = 0;
     int64_t fused_kernel = 0;  // single-call path: 0 = count -> block scan -> emit_scan kernels, 1 = the one-kernel look-back form
+    int64_t dense_emit = -1;   // segment-staged emit of dense warp tiles (emit_scan.cuh): -1 = by the density seen so far, 0 off, 1 on
+    bool s_dense = false;      // stranded path: the count phase's choice, kept for the emit phase of the same batch
+    double seen_hits_per_query = 0.0;  // of the most recent batch whose hit total the host has read
     int64_t emit_walk = 8;     // ranks per walk step of emit_scan: 8 (sorted batches) or 16 (scattered batches)
     int64_t fused_regs40 = 0;  // 1: the 40-register build of the fused kernel (6 CTAs/SM) instead of 32 registers (8 CTAs/SM)
     int64_t host_mode = 0;   // host-buffer pipeline: 0 = one fused kernel per chunk, 1 = count -> scan -> emit kernels
@@ -160,6 +163,15 @@ gg_status fail(gg_index* idx, gg_status st, const char* what, cudaError_t e = cu
         cudaError_t e_ = (call);                                         \
         if (e_ != cudaSuccess) return fail(idx, GG_ERR_CUDA, #call, e_); \
     } while (0)
+
+// dense warp tiles (>= kDenseMin hits in 32 queries) only exist when queries average tens of hits; the dense pass (and the
+// per-tile totals it needs from the count pass) is switched on from what earlier batches / chunks on this handle showed
+inline bool dense_pass_on(const gg_index* idx) {
+    return idx->dense_emit < 0 ? idx->seen_hits_per_query >= 32.0 : idx->dense_emit != 0;
+}
+inline void note_density(gg_index* idx, uint64_t hits, size_t nq) {
+    if (nq >= 1024) idx->seen_hits_per_query = static_cast<double>(hits) / static_cast<double>(nq);
+}
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline unsigned blocks_for(size_t n, unsigned threads) { return static_cast<unsigned>(div_up(n ? n : 1, threads)); }
@@ -211,7 +223,7 @@ gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads) * kBatchQpt);
         unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
         kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi,
-                                             scan2_tile_total(scratch), nullptr, d_err, vec_ok);
+                                             scan2_tile_total(scratch), nullptr, d_err, vec_ok, nullptr);
     } else if (idx->count_mode == 0) {
         auto kern = intersect_count_dir_kernel<C, Q>;
         int per_sm = static_cast<int>(idx->count_ctas_per_sm);
@@ -327,7 +339,7 @@ gg_status launch_fused(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
 // The single-call batch path (default): count (4 consecutive queries per thread, finger search) -> exclusive scan
 // of the per-block hit totals (one block = 128 queries, ~0.8 % of the batch) -> emit_scan (offsets + hits).
 // scratch layout: [block_total u64 x nb][block_prefix u64 x (nb + 1)][look-back state of the small scan]
-//                 [cnt u32 x nq][hi u32 x nq]
+//                 [cnt u32 x nq][hi u32 x nq][tile_total u32 x nq/32]
 inline size_t batch_blocks(size_t nq) { return div_up(nq, kBatchBlockQ); }
 inline size_t batch_ctl_bytes(size_t nq) {
     const size_t nb = batch_blocks(nq) + 1;
@@ -335,7 +347,28 @@ inline size_t batch_ctl_bytes(size_t nq) {
 }
 // one scratch buffer serves either flavour of the single-call path
 inline size_t single_scratch_bytes(size_t nq) {
-    return std::max(round_up(fused_scratch_bytes(nq), 256), batch_ctl_bytes(nq)) + 2 * round_up((nq ? nq : 1) * 4, 256);
+    return std::max(round_up(fused_scratch_bytes(nq), 256), batch_ctl_bytes(nq)) + 2 * round_up((nq ? nq : 1) * 4, 256) +
+           round_up(div_up(nq ? nq : 1, 32) * 4, 256);  // + per-tile totals (u32 per 32 queries) for the dense emit
+}
+
+// Second half of pass 2: the warp tiles with more hits than the stage holds (found from the count pass's per-tile totals).
+template <typename C, typename Q, bool kStrand>
+gg_status launch_emit_dense(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, size_t nq, const uint32_t* d_cnt,
+                            const uint32_t* d_hi, const uint64_t* block_prefix, const uint32_t* d_tile,
+                            uint32_t* d_hits, uint64_t capacity, StrandArgs sa, cudaStream_t st) {
+    if (nq == 0) return GG_OK;
+    auto kern = intersect_emit_dense_kernel<C, Q, kStrand>;
+    const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + 16;
+    int per_sm = 0;
+    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+    if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "dense emit kernel does not fit on an SM");
+    const size_t ctas = div_up(div_up(nq, 32 * 32), kQueryThreads / 32);  // a warp step covers 32 tiles
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(std::max<size_t>(ctas, 1), static_cast<size_t>(idx->sm_count) * per_sm));
+    kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix, d_tile,
+                                            static_cast<uint32_t>(kBatchBlockQ), d_hits, capacity, sa);
+    GG_CUDA(cudaGetLastError());
+    idx->bstats.kernel_launches++;
+    return GG_OK;
 }
 
 template <typename C, typename Q>
@@ -350,9 +383,11 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     char* tail = p + std::max(round_up(fused_scratch_bytes(nq), 256), batch_ctl_bytes(nq));
     uint32_t* d_cnt = reinterpret_cast<uint32_t*>(tail);
     uint32_t* d_hi = reinterpret_cast<uint32_t*>(tail + round_up((nq ? nq : 1) * 4, 256));
+    uint32_t* d_tile = reinterpret_cast<uint32_t*>(tail + 2 * round_up((nq ? nq : 1) * 4, 256));
     const bool tab_in_smem = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024;
+    const bool dense = dense_pass_on(idx);
     if (nq) {
-        auto kern = intersect_count_group_kernel<C, Q, kBatchQpt>;
+        auto kern = dense ? intersect_count_group_kernel<C, Q, kBatchQpt, true> : intersect_count_group_kernel<C, Q, kBatchQpt, false>;
         int per_sm = static_cast<int>(idx->count_ctas_per_sm);
         if (per_sm <= 0) {
             GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
@@ -362,7 +397,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
         const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end);
         kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_cnt, d_hi, nullptr, block_total,
-                                             d_err, vec_ok);
+                                             d_err, vec_ok, dense ? d_tile : nullptr);
         GG_CUDA(cudaGetLastError());
         idx->bstats.kernel_launches++;
     }
@@ -380,7 +415,8 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
         void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
                      uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs) =
-            idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16> : intersect_emit_scan_kernel<C, Q, 8>;
+            dense ? intersect_emit_scan_kernel<C, Q, 8, false, true>
+                  : (idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16> : intersect_emit_scan_kernel<C, Q, 8>);
         if (smem > 48 * 1024)
             GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         int per_sm = static_cast<int>(idx->emit_ctas_per_sm);
@@ -396,7 +432,9 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         GG_CUDA(cudaGetLastError());
         idx->bstats.kernel_launches++;
     }
-    return GG_OK;
+    if (!dense) return GG_OK;
+    return launch_emit_dense<C, Q, false>(idx, d_chrom, d_start, nq, d_cnt, d_hi, block_prefix, d_tile, d_hits, capacity,
+                                          StrandArgs{nullptr, nullptr, 0}, st);
 }
 
 gg_status dispatch_fused(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, int q_bytes,
@@ -938,6 +976,7 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
         if (static_cast<uint32_t>(sl.h_next_base[1]) & 1u) any_invalid = true;
         const uint64_t total = base[k + 1] - base[k];
         est_per_q = std::max(1.0, static_cast<double>(base[k + 1]) / static_cast<double>(q0 + m));
+        note_density(idx, base[k + 1], q0 + m);
         if (total) {
             if (total > sl.launch_cap) {  // estimate too small: exact re-run of this chunk (same base, same offsets)
                 GG_CUDA(cudaStreamSynchronize(sl.st));
@@ -1040,7 +1079,7 @@ void gg_index_destroy(gg_index* idx) {
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
                          &idx->ER, &idx->cbegin, &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
-                         &idx->s_cnt, &idx->s_hi, &idx->s_scan, &idx->s_total})
+                         &idx->s_cnt, &idx->s_hi, &idx->s_tile, &idx->s_scan, &idx->s_total})
         b->release();
     for (auto& s : idx->slots) {
         for (DeviceBuf* b : {&s.qc, &s.qs, &s.qe, &s.cnt, &s.hi, &s.off, &s.hits, &s.scan, &s.fscratch, &s.err}) b->release();
@@ -1196,6 +1235,7 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
         GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
         GG_CUDA(cudaStreamSynchronize(st));
         idx->bstats.n_hits = *total_hits;
+        note_density(idx, *total_hits, nq);
         if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
         if (flag & 2u) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
     }
@@ -1305,6 +1345,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "emit_ctas_per_sm" && value >= 0 && value <= 32) idx->emit_ctas_per_sm = value;
     else if (k == "fused_ctas_per_sm" && value >= 0 && value <= 32) idx->fused_ctas_per_sm = value;
     else if (k == "fused_kernel" && (value == 0 || value == 1)) idx->fused_kernel = value;
+    else if (k == "dense_emit" && value >= -1 && value <= 1) idx->dense_emit = value;
     else if (k == "emit_walk" && (value == 8 || value == 16)) idx->emit_walk = value;
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
@@ -1427,14 +1468,16 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
     uint32_t* d_hi = idx->s_hi.as<uint32_t>();
     if (!emit_only) {
         if (nq) {
-            auto kern = strand_count_group_kernel<C, Q, kBatchQpt>;
+            idx->s_dense = dense_pass_on(idx);  // the emit phase of this batch follows the same choice
+            auto kern = idx->s_dense ? strand_count_group_kernel<C, Q, kBatchQpt, true> : strand_count_group_kernel<C, Q, kBatchQpt, false>;
             int per_sm = 0;
             GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
             const size_t tiles = div_up(nq, static_cast<size_t>(kQueryThreads) * kBatchQpt);
             const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
             const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end);
             kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->SN.as<StrandNode>(), idx->EN.as<StrandNode>(), idx->er_base,
-                                                 d_chrom, d_start, d_end, d_strand, nq, d_cnt, d_hi, block_total, d_err, vec_ok);
+                                                 d_chrom, d_start, d_end, d_strand, nq, d_cnt, d_hi, block_total, d_err, vec_ok,
+                                                 idx->s_dense ? idx->s_tile.as<uint32_t>() : nullptr);
             GG_CUDA(cudaGetLastError());
             idx->bstats.kernel_launches++;
         }
@@ -1446,7 +1489,7 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
     const bool tab_in_smem = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024;
     const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
     const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
-    auto kern = intersect_emit_scan_kernel<C, Q, 8, true>;
+    auto kern = idx->s_dense ? intersect_emit_scan_kernel<C, Q, 8, true, true> : intersect_emit_scan_kernel<C, Q, 8, true, false>;
     if (smem > 48 * 1024) GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     int per_sm = 0;
     GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
@@ -1458,7 +1501,9 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
                                             tab_in_smem ? 1 : 0, StrandArgs{idx->strand.as<uint8_t>(), d_strand, idx->er_base});
     GG_CUDA(cudaGetLastError());
     idx->bstats.kernel_launches++;
-    return GG_OK;
+    if (!idx->s_dense) return GG_OK;
+    return launch_emit_dense<C, Q, true>(idx, d_chrom, d_start, nq, d_cnt, d_hi, block_prefix, idx->s_tile.as<uint32_t>(), d_hits,
+                                         capacity, StrandArgs{idx->strand.as<uint8_t>(), d_strand, idx->er_base}, st);
 }
 
 gg_status dispatch_stranded(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
@@ -1479,6 +1524,7 @@ gg_status ensure_strand_scratch(gg_index* idx, size_t nq) {
     const size_t m = nq ? nq : 1;
     GG_CUDA(idx->s_cnt.ensure(round_up(m * 4, 256)));
     GG_CUDA(idx->s_hi.ensure(round_up(m * 4, 256)));
+    GG_CUDA(idx->s_tile.ensure(round_up(div_up(m, 32) * 4, 256)));
     GG_CUDA(idx->s_scan.ensure(batch_ctl_bytes(m)));
     GG_CUDA(idx->s_total.ensure(16));
     GG_CUDA(idx->err_flag.ensure(16));
@@ -1589,6 +1635,7 @@ gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, c
         GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
         GG_CUDA(cudaStreamSynchronize(st));
         idx->bstats.n_hits = *total_hits;
+        note_density(idx, *total_hits, nq);
         s = strand_query_error(idx, flag);
         if (s != GG_OK) return s;
         if (*total_hits > capacity) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
@@ -1641,6 +1688,7 @@ gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, co
         GG_CUDA(cudaStreamSynchronize(st));
         s = strand_query_error(idx, flag);
         if (s != GG_OK) return s;
+        note_density(idx, total, m);
         GG_CUDA(idx->sq_hits.ensure((total ? total : 1) * 4));
         s = ensure_pinned_hits(idx, base + total, base);
         if (s != GG_OK) return s;

@@ -449,12 +449,13 @@ __device__ __forceinline__ void store_vec_u32(uint32_t* __restrict__ p, const ui
 // intersect_count_dir_kernel (tile_total, for the two-phase API's scan), and / or block_total[b] = hits of the
 // b-th block of 32 * QPT consecutive queries (one warp's share; plain stores, no atomics) for the batch path,
 // whose emit kernel turns scanned block totals into offsets itself.  A warp's queries never straddle a scan tile.
-template <typename C, typename Q, int QPT>
+template <typename C, typename Q, int QPT, bool kTiles = false>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_count_group_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                              const Q* __restrict__ qend, size_t nq, uint32_t* __restrict__ cnt_out,
                              uint32_t* __restrict__ hi_out, unsigned long long* __restrict__ tile_total,
-                             unsigned long long* __restrict__ block_total, uint32_t* __restrict__ err_flag, int vec_ok) {
+                             unsigned long long* __restrict__ block_total, uint32_t* __restrict__ err_flag, int vec_ok,
+                             uint32_t* __restrict__ tile_total32 = nullptr) {
     static_assert(kScanTile % (32 * QPT) == 0, "a warp's queries must stay inside one scan tile");
     constexpr size_t kTileQ = static_cast<size_t>(kQueryThreads) * QPT;
     const size_t n_tiles = (nq + kTileQ - 1) / kTileQ;
@@ -494,8 +495,18 @@ intersect_count_group_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchro
         unsigned long long wsum = 0;
 #pragma unroll
         for (int j = 0; j < QPT; ++j) wsum += cnt[j];
+        if constexpr (kTiles) {
+            // sums over the 32 / QPT lanes of one 32-query tile first (per-tile totals for the dense emit), then the warp
 #pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+            for (int d = 1; d < 32 / QPT; d <<= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+            if ((lane_id() & (32 / QPT - 1)) == 0 && q0 < nq)
+                tile_total32[q0 / 32] = wsum > 0xFFFFFFFFull ? 0xFFFFFFFFu : static_cast<uint32_t>(wsum);
+#pragma unroll
+            for (int d = 32 / QPT; d < 32; d <<= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        } else {
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        }
         if (lane_id() == 0) {
             const size_t wq0 = tile * kTileQ + static_cast<size_t>(threadIdx.x & ~31u) * QPT;  // the warp's first query
             if (tile_total && wsum != 0) atomicAdd(&tile_total[wq0 / kScanTile], wsum);

@@ -165,13 +165,14 @@ __device__ __forceinline__ uint32_t strand_rank(const StrandNode* __restrict__ N
 // followed by the closed-form strand count.  Outputs as intersect_count_group_kernel: cnt / hi per query and
 // block_total[b] = hits of the b-th block of 32 * QPT queries.  err_flag bit 0: start > end; bit 2: a strand byte
 // outside "+-.*" (genomic_coordinate's constructor check, genomic_coordinate.hpp:78-81).
-template <typename C, typename Q, int QPT>
+template <typename C, typename Q, int QPT, bool kTiles = false>
 __global__ void __launch_bounds__(kQueryThreads)
 strand_count_group_kernel(IndexView<C> ix, const StrandNode* __restrict__ SN, const StrandNode* __restrict__ EN,
                           uint32_t slot_base, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                           const Q* __restrict__ qend, const uint8_t* __restrict__ qstrand, size_t nq,
                           uint32_t* __restrict__ cnt_out, uint32_t* __restrict__ hi_out,
-                          unsigned long long* __restrict__ block_total, uint32_t* __restrict__ err_flag, int vec_ok) {
+                          unsigned long long* __restrict__ block_total, uint32_t* __restrict__ err_flag, int vec_ok,
+                             uint32_t* __restrict__ tile_total32 = nullptr) {
     constexpr size_t kTileQ = static_cast<size_t>(kQueryThreads) * QPT;
     const size_t n_tiles = (nq + kTileQ - 1) / kTileQ;
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -228,8 +229,18 @@ strand_count_group_kernel(IndexView<C> ix, const StrandNode* __restrict__ SN, co
         unsigned long long wsum = 0;
 #pragma unroll
         for (int j = 0; j < QPT; ++j) wsum += cnt[j];
+        if constexpr (kTiles) {
+            // sums over the 32 / QPT lanes of one 32-query tile first (per-tile totals for the dense emit), then the warp
 #pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+            for (int d = 1; d < 32 / QPT; d <<= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+            if ((lane_id() & (32 / QPT - 1)) == 0 && q0 < nq)
+                tile_total32[q0 / 32] = wsum > 0xFFFFFFFFull ? 0xFFFFFFFFu : static_cast<uint32_t>(wsum);
+#pragma unroll
+            for (int d = 32 / QPT; d < 32; d <<= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        } else {
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        }
         if (lane_id() == 0) {
             const size_t wq0 = tile * kTileQ + static_cast<size_t>(threadIdx.x & ~31u) * QPT;  // the warp's first query
             if (wq0 < nq) block_total[wq0 / (32 * QPT)] = wsum;

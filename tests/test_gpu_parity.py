@@ -3,7 +3,8 @@ ordered rank list per query).  Marked gpu: run on the B200 box."""
 import numpy as np
 import pytest
 
-from helpers import expected_chain, oracle_csr, random_index, random_queries
+import oracle as O
+from helpers import chrom_offsets, expected_chain, oracle_csr, random_index, random_queries
 
 pytestmark = pytest.mark.gpu
 
@@ -233,7 +234,7 @@ def test_fused_device_api_and_capacity(gg, oracle):
             got = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
                                    d_hits.data_ptr(), cap, stream, sync_total=True)
             assert got == total
-            assert idx.batch_stats().kernel_launches == 3  # count, block scan, emit_scan
+            assert idx.batch_stats().kernel_launches in (3, 4)  # count, block scan, emit_scan (+ emit_dense for dense batches)
             assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
             h_hits = d_hits.cpu().numpy()
             assert np.array_equal(h_hits.view(np.uint32)[:total], exp_hits)
@@ -365,3 +366,55 @@ def test_long_nested_intervals_use_max_end_pruning(gg, oracle):
 def test_smoke_entry(gg, oracle):
     import __graft_entry__ as ge
     ge.smoke()
+
+
+@pytest.mark.parametrize("n,span,max_len,q", [(3000, 4000, 3000, 5000), (40000, 200000, 30000, 20001), (600, 2000, 1500, 2000)])
+def test_dense_tiles_windowed_emit(n, span, max_len, q):
+    """Warp tiles with far more hits than the 512-entry stage (hundreds to thousands of hits per query): written by
+    intersect_emit_dense_kernel in windows.  Interval and stranded paths, sorted and random batch order, and the
+    capacity contract (offsets complete, ranks beyond the buffer dropped)."""
+    import torch
+    from genogrove_b200 import DeviceIndex, GGError, TIE_EXPLICIT
+    rng = np.random.default_rng(n + q)
+    chrom, s, e = random_index(rng, n, 2, span=span, max_len=max_len, dup=n == 600)
+    st = np.frombuffer(b"+-.*", dtype=np.uint8)[rng.integers(0, 4, n)]
+    qc, qs, qe = random_queries(rng, q, 2, span=span, max_len=max(2, max_len // 3), extra_chrom=1)
+    qst = np.frombuffer(b"+-.*", dtype=np.uint8)[rng.integers(0, 4, q)]
+    idx = DeviceIndex(0)
+    idx.set_option("dense_emit", 1 if n != 600 else -1)  # forced on; the last case relies on the density seen so far
+    so = np.array([O.STRAND_ORDER[chr(c)] for c in st], dtype=np.uint64)
+    perm = idx.build(chrom, s, e, 2, tie_mode=TIE_EXPLICIT, tie_key=(so << np.uint64(32)) | np.arange(n, dtype=np.uint64))
+    idx.set_strands(st[perm])
+    coff = chrom_offsets(chrom, 2)
+    for order in ("random", "sorted"):
+        if order == "sorted":
+            o = np.lexsort((qs, qc))
+            qc, qs, qe, qst = qc[o], qs[o], qe[o], qst[o]
+        eo, eh = O.flat_intersect_batch(s[perm], e[perm], coff, qc, qs, qe)
+        assert len(eh) / q > 40  # dense: most 32-query tiles exceed the stage
+        off, hits = idx.intersect_batch(qc, qs, qe)
+        assert np.array_equal(off, eo) and np.array_equal(hits, eh)
+        so_, sh_ = O.flat_intersect_batch_stranded(s[perm], e[perm], st[perm], coff, qc, qs, qe, qst)
+        off, hits = idx.intersect_batch_stranded(qc, qs, qe, qst)
+        assert np.array_equal(off, so_) and np.array_equal(hits, sh_)
+    # device call with a buffer that is too small: offsets complete, the prefix that fits is exact
+    dev = torch.device("cuda:0")
+    d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
+    d_s = torch.from_numpy(qs.astype(np.uint32).view(np.int32)).to(dev)
+    d_e = torch.from_numpy(qe.astype(np.uint32).view(np.int32)).to(dev)
+    d_off = torch.empty(q + 1, dtype=torch.int64, device=dev)
+    cap = len(eh) // 3
+    d_hits = torch.full((cap + 64,), -1, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    with pytest.raises(GGError) as ei:
+        idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, q, d_off.data_ptr(), d_hits.data_ptr(), cap, stream,
+                         sync_total=True)
+    assert ei.value.status == 7 and idx.last_total == len(eh)
+    assert np.array_equal(d_off.cpu().numpy().view(np.uint64), eo)
+    got = d_hits.cpu().numpy()
+    assert (got[cap:] == -1).all()  # nothing written beyond the capacity
+    # every complete 32-query tile below the capacity is exact
+    last_full = int(np.searchsorted(eo, cap, side="right")) - 1
+    last_full = (last_full // 128) * 128
+    upto = int(eo[last_full]) if last_full > 0 else 0
+    assert np.array_equal(got[:upto].view(np.uint32), eh[:upto])
