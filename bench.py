@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--queries", type=int, default=100_000_000, help="queries per GPU")
     ap.add_argument("--shuffled", action="store_true", help="shuffled instead of coordinate-sorted queries")
     ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--cpu-sample", type=int, default=4_000_000, help="queries in the CPU baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=32_000_000, help="queries in the CPU baseline sample")
     ap.add_argument("--cpu-order", type=int, default=32, help="B+ tree order of the reference grove (3 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
