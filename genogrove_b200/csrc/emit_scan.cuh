@@ -71,15 +71,13 @@ __device__ __forceinline__ void emit_dense_tile(const IndexView<C>& ix, const ui
                 m_lo = strand_compat4(sw.x, q4);
                 m_hi = strand_compat4(sw.y, q4);
             }
-#pragma unroll
-            for (int k = 7; k >= 0; --k) {
-                const bool ok = static_cast<uint32_t>(k) < top && ea[k] >= qs && (((k < 4 ? m_lo : m_hi) >> (8 * (k & 3))) & 1u) &&
-                                left != 0;
-                if (ok) {
-                    --left;
-                    ++n;
-                    sts32(seg_addr + (kDenseSeg - n) * 4u, g8 + k);
-                }
+            uint32_t m = group_hit_mask<C>(ea, qs, top, m_lo, m_hi);
+            while (m != 0 && left != 0) {  // hits of the group, highest rank first
+                const uint32_t k = 31u - __clz(m);
+                m ^= 1u << k;
+                --left;
+                ++n;
+                sts32(seg_addr + (kDenseSeg - n) * 4u, g8 + k);
             }
             r_hi = g8;
         }

@@ -252,6 +252,18 @@ strand_count_group_kernel(IndexView<C> ix, const StrandNode* __restrict__ SN, co
 
 namespace gg {
 
+// bit k set: rank g8 + k of a walk group overlaps the query (end >= q.start) and, with strand masks (0xFF per
+// compatible byte, strand_compat4), has a compatible strand; ranks at or above `top` are masked off
+template <typename C>
+__device__ __forceinline__ uint32_t group_hit_mask(const C (&ea)[8], C qs, uint32_t top, uint32_t m_lo, uint32_t m_hi) {
+    uint32_t m = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m |= (ea[k] >= qs ? 1u : 0u) << k;
+    // one bit per byte of the compat masks -> 4 + 4 bits (multiply gathers bits 0, 8, 16, 24 into the top nibble)
+    const uint32_t c_lo = ((m_lo & 0x01010101u) * 0x10204080u) >> 28, c_hi = ((m_hi & 0x01010101u) * 0x10204080u) >> 28;
+    return m & (c_lo | (c_hi << 4)) & ((1u << top) - 1u);
+}
+
 // The staged backward walk of emit_scan (emit_walk_staged8 in intersect.cuh) with the strand test: ranks hi-1,
 // hi-2, ... in aligned groups of 8; a hit must have end >= q.start AND a compatible strand byte.  Hits go to the
 // shared-memory stage back to front until the query's list [s_begin, s_end) is full (its length is the exact
@@ -279,11 +291,12 @@ __device__ __forceinline__ void emit_walk_staged8_strand(const IndexView<C>& ix,
         load8(leaf_end + g8, ea);
         const uint2 sw = *reinterpret_cast<const uint2*>(strands + g8);
         const uint32_t m_lo = wild ? 0xFFFFFFFFu : strand_compat4(sw.x, q4), m_hi = wild ? 0xFFFFFFFFu : strand_compat4(sw.y, q4);
-#pragma unroll
-        for (int k = 7; k >= 0; --k) {
-            const bool ok = static_cast<uint32_t>(k) < top && ea[k] >= qs && (((k < 4 ? m_lo : m_hi) >> (8 * (k & 3))) & 1u) &&
-                            sp > s_begin;
-            if (ok) { sp -= 4; sts32(sp, g8 + k); }
+        uint32_t m = group_hit_mask<C>(ea, qs, top, m_lo, m_hi);
+        while (m != 0 && sp > s_begin) {  // hits of the group, highest rank first
+            const uint32_t k = 31u - __clz(m);
+            m ^= 1u << k;
+            sp -= 4;
+            sts32(sp, g8 + k);
         }
         r_hi = g8;
     }
