@@ -301,7 +301,7 @@ def main():
             dom, dom_ms, dom_bytes = "intersect_emit_scan_kernel", kernel_ms["emit"], bytes_emit
         else:
             dom, dom_ms, dom_bytes = "intersect_count_group_kernel", kernel_ms["count"], bytes_count
-        launches_per_step = 3  # count_group, block scan, emit_scan (the dense-tile kernel only runs for batches averaging >= 32 hits/query)
+        launches_per_step = 3  # count_group, block scan, emit_scan (the dense-tile kernel only runs for batches averaging >= 12 hits/query)
     else:
         bytes_count = 12 * nq + 8 * nq                   # read (chrom,start,end) u32, write count u32 + hi u32
         bytes_emit = 4 * total + 8 * (nq + 1) + 12 * nq  # write ranks, read offsets, chrom/start/hi

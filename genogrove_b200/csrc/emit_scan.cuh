@@ -17,6 +17,10 @@
 namespace gg {
 
 constexpr uint32_t kEmitScanSlack = 8;  // spare slots in front of each warp's stage (see emit_walk_staged)
+// stage entries per warp of intersect_emit_scan_kernel: the dense-batch variant doubles the stage (4 KB per warp, 6 CTAs per
+// SM instead of 8) so that tiles of 16-32 hits per query still leave through coalesced stores (GENCODE-shaped cfg3: 88 % of
+// the tiles exceed 512 hits, 0.5 % exceed 1024)
+__host__ __device__ constexpr uint32_t emit_stage_entries(bool strand, bool dense) { return dense && !strand ? 2u * kEmitStage : kEmitStage; }
 
 // kDense: intersect_emit_dense_kernel follows and writes the tiles with >= kDenseMin hits (skipped here).
 // kStrand (genomic_coordinate keys, strand.cuh): cnt_in holds the strand-compatible counts and the walk also tests
@@ -110,7 +114,8 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                            uint64_t* __restrict__ total_out, uint32_t* __restrict__ err_flag, int tab_in_smem,
                            StrandArgs sa = StrandArgs{nullptr, nullptr, 0}) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr uint32_t kStageWords = kEmitStage + kEmitScanSlack;
+    constexpr uint32_t kStage = emit_stage_entries(kStrand, kDense);
+    constexpr uint32_t kStageWords = kStage + kEmitScanSlack;
     constexpr uint32_t kWarps = kQueryThreads / 32;
     uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + kWarps * kStageWords;
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
@@ -183,7 +188,7 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                 hi = hi_in[q];
                 if (kStrand) qst = sa.qstrand[q];
             }
-            if (wtotal <= kEmitStage) {
+            if (wtotal <= kStage) {
                 if (c != 0) {
                     const uint32_t s_begin = stage_addr + static_cast<uint32_t>(excl) * 4u;
                     if (kStrand)

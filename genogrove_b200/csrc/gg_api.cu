@@ -166,8 +166,8 @@ gg_status fail(gg_index* idx, gg_status st, const char* what, cudaError_t e = cu
 
 // dense warp tiles (>= kDenseMin hits in 32 queries) only exist when queries average tens of hits; the dense pass (and the
 // per-tile totals it needs from the count pass) is switched on from what earlier batches / chunks on this handle showed
-inline bool dense_pass_on(const gg_index* idx) {
-    return idx->dense_emit < 0 ? idx->seen_hits_per_query >= 32.0 : idx->dense_emit != 0;
+inline bool dense_pass_on(const gg_index* idx, double min_density = 32.0) {
+    return idx->dense_emit < 0 ? idx->seen_hits_per_query >= min_density : idx->dense_emit != 0;
 }
 inline void note_density(gg_index* idx, uint64_t hits, size_t nq) {
     if (nq >= 1024) idx->seen_hits_per_query = static_cast<double>(hits) / static_cast<double>(nq);
@@ -385,7 +385,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     uint32_t* d_hi = reinterpret_cast<uint32_t*>(tail + round_up((nq ? nq : 1) * 4, 256));
     uint32_t* d_tile = reinterpret_cast<uint32_t*>(tail + 2 * round_up((nq ? nq : 1) * 4, 256));
     const bool tab_in_smem = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024;
-    const bool dense = dense_pass_on(idx);
+    const bool dense = dense_pass_on(idx, 12.0);  // the dense variants also carry the hybrid walk for tiles above the stage
     if (nq) {
         auto kern = dense ? intersect_count_group_kernel<C, Q, kBatchQpt, true> : intersect_count_group_kernel<C, Q, kBatchQpt, false>;
         int per_sm = static_cast<int>(idx->count_ctas_per_sm);
@@ -412,7 +412,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     }
     {
         const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
-        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
+        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (emit_stage_entries(false, dense) + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
         void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
                      uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs) =
             dense ? intersect_emit_scan_kernel<C, Q, 8, false, true>

@@ -213,8 +213,9 @@ void gg_host_free(void* p);
  * path per chunk with an estimated hit capacity [default], 1 = count, read the total, emit); "fused_kernel" (single-call
  * path: 0 = count -> block scan -> emit_scan kernels [default], 1 = one kernel with a look-back scan; its knobs:
  * "fused_ctas_per_sm", "fused_regs40"); "emit_walk" (ranks per walk step of emit_scan: 8 [default] or 16);
- * "dense_emit" (second emit kernel for warp tiles with >= 2048 hits in 32 queries, per-lane stage segments and sector-sized
- * stores: -1 = on once a batch / chunk on this handle averaged >= 32 hits per query [default], 0 = off, 1 = on);
+ * "dense_emit" (dense-batch variants of pass 2: a 1024-hit stage per 32-query tile instead of 512, and a second emit kernel
+ * for tiles with >= 2048 hits, per-lane stage segments and sector-sized stores: -1 = on once a batch / chunk on this
+ * handle averaged >= 12 hits per query (stranded path: >= 32) [default], 0 = off, 1 = on);
  * "count_mode" (two-phase API: 2 = directory + finger search, 4 consecutive queries per thread [default], 0 = directory,
  * one query per thread, 1 = tiered tree kernel: TMA-staged windows / warp bracket / per-lane descent; for mode 1:
  * "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and "count_threads" (128..1024));
