@@ -10,7 +10,7 @@ rng = np.random.default_rng(5)
 L = synth.HG38_LENGTHS[:3]
 chrom, start, end, qc, qs, qe = [], [], [], [], [], []
 for c in range(3):
-    n = 8_500_000
+    n = int(os.environ.get("N_PER", 8_500_000))  # 2_000_000: a uniform ~20 hits/query batch
     ln = np.exp(rng.uniform(np.log(100), np.log(10000), n)).astype(np.int64)
     st = (rng.random(n) * (int(L[c]) - ln - 1)).astype(np.int64)
     chrom.append(np.full(n, c, np.uint32)); start.append(st.astype(np.uint64)); end.append((st + ln - 1).astype(np.uint64))
