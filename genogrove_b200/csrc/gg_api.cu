@@ -128,7 +128,9 @@ struct gg_index {
     int64_t count_ctas_per_sm = 0;  // 0 = occupancy API
     int64_t emit_ctas_per_sm = 0;
     int64_t fused_ctas_per_sm = 0;
-    int64_t fused_kernel = 0;  // single-call path: 0 = count -> block scan -> emit_scan kernels, 1 = the one-kernel look-back form
+    int64_t fused_kernel = -1;  // single-call path: 0 = count -> block scan -> emit_scan kernels, 1 = the one-kernel look-back form,
+                                // -1 = by batch size (one kernel up to kOneKernelMaxQ queries: launch latency dominates there)
+    bool last_one_kernel = false;  // what the last single-call dispatch ran (which kernel times are valid)
     int64_t dense_emit = -1;   // segment-staged emit of dense warp tiles (emit_scan.cuh): -1 = by the density seen so far, 0 off, 1 on
     bool s_dense = false;      // stranded path: the count phase's choice, kept for the emit phase of the same batch
     double seen_hits_per_query = 0.0;  // of the most recent batch whose hit total the host has read
@@ -437,11 +439,20 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
                                           StrandArgs{nullptr, nullptr, 0}, st);
 }
 
+// measured on B200 (tools/small_batch_probe.py, cfg2 index): 1 k .. 100 k queries 40-46 us in one kernel against 50-66 us for
+// the three launches; equal near 1 M queries; from 4 M on the three-kernel form wins (131 vs 146 us, 246 vs 307 us at 10 M)
+constexpr size_t kOneKernelMaxQ = 512 * 1024;
+inline bool use_one_kernel(const gg_index* idx, size_t nq) {
+    return idx->fused_kernel < 0 ? nq <= kOneKernelMaxQ : idx->fused_kernel != 0;
+}
+
 gg_status dispatch_fused(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, int q_bytes,
                          size_t nq, uint64_t* d_off, uint32_t* d_hits, uint64_t capacity, const uint64_t* d_base,
                          uint64_t* d_next_base, uint64_t* d_total, void* scratch, uint32_t* d_err, cudaStream_t st) {
+    const bool one = use_one_kernel(idx, nq);
+    idx->last_one_kernel = one;
 #define GG_SINGLE(C, Q)                                                                                                      \
-    (idx->fused_kernel ? launch_fused<C, Q>(idx, d_chrom, (const Q*)d_start, (const Q*)d_end, nq, d_off, d_hits, capacity,    \
+    (one ? launch_fused<C, Q>(idx, d_chrom, (const Q*)d_start, (const Q*)d_end, nq, d_off, d_hits, capacity,    \
                                             d_base, d_next_base, d_total, scratch, d_err, st)                                \
                        : launch_batch<C, Q>(idx, d_chrom, (const Q*)d_start, (const Q*)d_end, nq, d_off, d_hits, capacity,    \
                                             d_base, d_next_base, d_total, scratch, d_err, st))
@@ -1227,7 +1238,7 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
     if (idx->timing) {
         GG_CUDA(cudaEventRecord(idx->ev[4], st));
         idx->ev_emit_valid = true;
-        idx->ev_count_valid = !idx->fused_kernel;  // count / block-scan / emit_scan times of the three-kernel form
+        idx->ev_count_valid = !idx->last_one_kernel;  // count / block-scan / emit_scan times of the three-kernel form
     }
     if (total_hits) {
         uint32_t flag = 0;
@@ -1344,7 +1355,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "count_ctas_per_sm" && value >= 0 && value <= 32) idx->count_ctas_per_sm = value;
     else if (k == "emit_ctas_per_sm" && value >= 0 && value <= 32) idx->emit_ctas_per_sm = value;
     else if (k == "fused_ctas_per_sm" && value >= 0 && value <= 32) idx->fused_ctas_per_sm = value;
-    else if (k == "fused_kernel" && (value == 0 || value == 1)) idx->fused_kernel = value;
+    else if (k == "fused_kernel" && value >= -1 && value <= 1) idx->fused_kernel = value;
     else if (k == "dense_emit" && value >= -1 && value <= 1) idx->dense_emit = value;
     else if (k == "emit_walk" && (value == 8 || value == 16)) idx->emit_walk = value;
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;

@@ -234,7 +234,7 @@ def test_fused_device_api_and_capacity(gg, oracle):
             got = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nb, len(qc), d_off.data_ptr(),
                                    d_hits.data_ptr(), cap, stream, sync_total=True)
             assert got == total
-            assert idx.batch_stats().kernel_launches in (3, 4)  # count, block scan, emit_scan (+ emit_dense for dense batches)
+            assert idx.batch_stats().kernel_launches in (1, 3, 4)  # one look-back kernel (small batches), or count, block scan, emit_scan (+ emit_dense)
             assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
             h_hits = d_hits.cpu().numpy()
             assert np.array_equal(h_hits.view(np.uint32)[:total], exp_hits)

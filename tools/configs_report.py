@@ -53,6 +53,9 @@ for name in want:
     w = MAKE[name]()
     nq, n = len(w.q_chrom), len(w.chrom)
     idx = DeviceIndex(0)
+    for kv in os.environ.get("GG_OPTS", "").split(","):  # e.g. GG_OPTS=fused_kernel=1,dense_emit=0
+        if kv:
+            idx.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     idx.build(w.chrom, w.start, w.end, w.n_chrom, want_perm=False)
     idx.build(w.chrom, w.start, w.end, w.n_chrom, want_perm=False)
     ist = idx.stats()
