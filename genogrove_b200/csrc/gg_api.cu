@@ -439,8 +439,8 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
                                           StrandArgs{nullptr, nullptr, 0}, st);
 }
 
-// measured on B200 (tools/small_batch_probe.py, cfg2 index): 1 k .. 100 k queries 40-46 us in one kernel against 50-66 us for
-// the three launches; equal near 1 M queries; from 4 M on the three-kernel form wins (131 vs 146 us, 246 vs 307 us at 10 M)
+// measured on B200 (tools/small_batch_probe.py, cfg2 index): 1 k .. 100 k queries 30-33 us in one kernel against 39-44 us for
+// the three launches; 56 vs 63 us at 1 M queries; from 4 M on the three-kernel form wins (121 vs 135 us, 234 vs 295 us at 10 M)
 constexpr size_t kOneKernelMaxQ = 512 * 1024;
 inline bool use_one_kernel(const gg_index* idx, size_t nq) {
     return idx->fused_kernel < 0 ? nq <= kOneKernelMaxQ : idx->fused_kernel != 0;
@@ -816,7 +816,7 @@ gg_status ensure_slots(gg_index* idx) {
         GG_CUDA(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
         GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&s.h_next_base), 16, cudaHostAllocDefault));
     }
-    GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&idx->h_err), 16, cudaHostAllocDefault));
+    if (!idx->h_err) GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&idx->h_err), 16, cudaHostAllocDefault));
     idx->slots_ready = true;
     return GG_OK;
 }
@@ -1218,21 +1218,22 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
     GG_CUDA(cudaSetDevice(idx->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     GG_CUDA(idx->fused_scratch.ensure(single_scratch_bytes(nq)));
-    GG_CUDA(idx->fused_out.ensure(16));
-    GG_CUDA(idx->err_flag.ensure(16));
+    GG_CUDA(idx->err_flag.ensure(16));  // one 16-byte mailbox: [0, 4) error flag, [8, 16) hit total — one memset, one read
+    if (!idx->h_err) GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&idx->h_err), 16, cudaHostAllocDefault));
+    uint64_t* d_total = reinterpret_cast<uint64_t*>(idx->err_flag.as<char>() + 8);
     idx->bstats = gg_batch_stats{};
     idx->bstats.n_queries = nq;
     idx->bstats.n_chunks = 1;
     idx->ev_count_valid = idx->ev_emit_valid = false;
     idx->counted_nq = 0;  // the two-phase emit needs its own count pass
-    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
+    GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 16, st));
     if (idx->timing) {
         GG_CUDA(cudaEventRecord(idx->ev[0], st));
         GG_CUDA(cudaEventRecord(idx->ev[3], st));
     }
     idx->in_device_call = true;
     gg_status s = dispatch_fused(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_offsets, d_hits, capacity, nullptr, nullptr,
-                                 idx->fused_out.as<uint64_t>(), idx->fused_scratch.p, idx->err_flag.as<uint32_t>(), st);
+                                 d_total, idx->fused_scratch.p, idx->err_flag.as<uint32_t>(), st);
     idx->in_device_call = false;
     if (s != GG_OK) return s;
     if (idx->timing) {
@@ -1241,10 +1242,10 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
         idx->ev_count_valid = !idx->last_one_kernel;  // count / block-scan / emit_scan times of the three-kernel form
     }
     if (total_hits) {
-        uint32_t flag = 0;
-        GG_CUDA(cudaMemcpyAsync(total_hits, idx->fused_out.p, 8, cudaMemcpyDeviceToHost, st));
-        GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(idx->h_err, idx->err_flag.p, 16, cudaMemcpyDeviceToHost, st));  // pinned: no staging copy
         GG_CUDA(cudaStreamSynchronize(st));
+        const uint32_t flag = idx->h_err[0];
+        std::memcpy(total_hits, idx->h_err + 2, 8);
         idx->bstats.n_hits = *total_hits;
         note_density(idx, *total_hits, nq);
         if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
