@@ -1173,10 +1173,13 @@ gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, cons
         idx->ev_count_valid = true;
     }
     idx->counted_nq = nq;
-    if (total_hits) {
-        GG_CUDA(cudaMemcpyAsync(total_hits, d_offsets + nq, 8, cudaMemcpyDeviceToHost, st));
-        s = check_query_error(idx, st);  // synchronises the stream
-        if (s != GG_OK) return s;
+    if (total_hits) {  // both words land in pinned memory (no staging copies), one synchronisation
+        if (!idx->h_err) GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&idx->h_err), 16, cudaHostAllocDefault));
+        GG_CUDA(cudaMemcpyAsync(idx->h_err + 2, d_offsets + nq, 8, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaMemcpyAsync(idx->h_err, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        std::memcpy(total_hits, idx->h_err + 2, 8);
+        if (idx->h_err[0] & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
         idx->bstats.n_hits = *total_hits;
     }
     return GG_OK;
@@ -1643,9 +1646,12 @@ gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, c
     if (s != GG_OK) return s;
     if (total_hits) {
         uint32_t flag = 0;
-        GG_CUDA(cudaMemcpyAsync(total_hits, idx->s_total.p, 8, cudaMemcpyDeviceToHost, st));
-        GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        if (!idx->h_err) GG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&idx->h_err), 16, cudaHostAllocDefault));
+        GG_CUDA(cudaMemcpyAsync(idx->h_err + 2, idx->s_total.p, 8, cudaMemcpyDeviceToHost, st));  // pinned: no staging copies
+        GG_CUDA(cudaMemcpyAsync(idx->h_err, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
         GG_CUDA(cudaStreamSynchronize(st));
+        std::memcpy(total_hits, idx->h_err + 2, 8);
+        flag = idx->h_err[0];
         idx->bstats.n_hits = *total_hits;
         note_density(idx, *total_hits, nq);
         s = strand_query_error(idx, flag);
