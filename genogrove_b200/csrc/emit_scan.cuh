@@ -280,7 +280,7 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
 // A warp takes a dense tile, rebuilds its CSR base from block_prefix and the tile totals before it in the block,
 // scans the 32 counts and writes the lists through emit_dense_tile.  Offsets were stored by the first kernel.
 template <typename C, typename Q, bool kStrand>
-__global__ void __launch_bounds__(kQueryThreads)
+__global__ void __launch_bounds__(kQueryThreads, 5)
 intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
                             const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
                             const uint64_t* __restrict__ block_prefix, const uint32_t* __restrict__ tile_total,
