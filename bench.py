@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--one-kernel", action="store_true", help="single-call path as ONE kernel (decoupled look-back scan)")
     ap.add_argument("--regs40", action="store_true", help="40-register build of the one-kernel form")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--emit-tma", type=int, default=-1, help="pass 2 kernel: 1 TMA ring + bulk store [default], 2 TMA ring + vector stores, 0 emit_scan")
+    ap.add_argument("--emit-ctas-per-sm", type=int, default=0)
     return ap.parse_args()
 
 
@@ -222,6 +224,10 @@ def main():
         idx.set_option("fused_regs40", 1)
     if args.ctas_per_sm:
         idx.set_option("fused_ctas_per_sm", args.ctas_per_sm)
+    if args.emit_tma >= 0:
+        idx.set_option("emit_tma", args.emit_tma)
+    if args.emit_ctas_per_sm:
+        idx.set_option("emit_ctas_per_sm", args.emit_ctas_per_sm)
     idx.set_option("timing", 1)  # library CUDA events around its kernels, on the launching stream
     kms = {"count": [], "scan": [], "emit": [], "fused": []}
 

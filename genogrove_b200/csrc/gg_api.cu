@@ -5,15 +5,19 @@
 #include "../../include/gg_b200.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "build.cuh"
 #include "common.cuh"
+#include "device_buf.h"
 #include "emit_scan.cuh"
+#include "emit_tma.cuh"
 #include "flanking.cuh"
 #include "fused.cuh"
 #include "intersect.cuh"
@@ -22,6 +26,10 @@
 #include "strand.cuh"
 
 using namespace gg;
+
+namespace gg {
+std::atomic<long long> g_alloc_fail_countdown{0};
+}
 
 namespace {
 
@@ -32,30 +40,6 @@ constexpr int kBatchQpt = GG_BATCH_QPT;  // consecutive queries per thread of th
 constexpr size_t kBatchBlockQ = 32 * kBatchQpt;  // = one warp's share: the granularity of the batch path's block totals
 constexpr int kSlots = 3;        // pipeline depth of the host-buffer path
 constexpr int kCountThreadsDefault = 256;
-
-struct DeviceBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
-        if (bytes <= cap && p) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes ? bytes : 16;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-    }
-    template <typename T>
-    T* as() const {
-        return static_cast<T*>(p);
-    }
-};
 
 struct Slot {
     cudaStream_t st = nullptr;
@@ -87,6 +71,9 @@ struct gg_index {
     DeviceBuf ER;           // chain rank of each sorted end (flanking.cuh), indexed by level-0 slot - er_base
     uint32_t er_base = 0;   // = tab[0][0]
     DeviceBuf cbegin;       // [n_chrom + 1] first concatenated chain rank of each chromosome
+    DeviceBuf flat[kFlatLevels];  // flat max-end hierarchy over the level-0 slots (emit_tma.cuh)
+    DeviceBuf cslot;        // [n_chrom + 1] first level-0 slot of each chromosome (= tab[0][c] - tab[0][0])
+    int n_flat = 0;
     int dir_shift = 0;
     uint64_t dir_entries = 0;
     std::vector<uint64_t> h_cnt;
@@ -134,7 +121,25 @@ struct gg_index {
     int64_t dense_emit = -1;   // segment-staged emit of dense warp tiles (emit_scan.cuh): -1 = by the density seen so far, 0 off, 1 on
     bool s_dense = false;      // stranded path: the count phase's choice, kept for the emit phase of the same batch
     double seen_hits_per_query = 0.0;  // of the most recent batch whose hit total the host has read
+    double seen_hits_per_query_strand = 0.0;  // same for the stranded path (its dense threshold differs: 32 vs 12)
+    // fully asynchronous device calls (total_hits == NULL) still feed the density heuristic: the call's hit total is copied
+    // to this pinned mailbox behind the kernels and picked up — if it has landed — at the start of the next call
+    uint32_t* h_lazy = nullptr;
+    cudaEvent_t ev_lazy = nullptr;
+    bool lazy_pending = false, lazy_stranded = false;
+    size_t lazy_nq = 0;
     int64_t emit_walk = 8;     // ranks per walk step of emit_scan: 8 (sorted batches) or 16 (scattered batches)
+    int64_t emit_tma = 0;      // pass 2 of the single-call path: 0 = intersect_emit_scan_kernel [default: measured faster, the
+                               // kernel is issue-bound and the TMA plumbing costs instructions], 1 = intersect_emit_tma_kernel
+                               // (TMA ring in, TMA bulk store out), 2 = same with 16-byte vector stores instead of the bulk store
+    // ---- compact host path (gg_intersect_batch_compact)
+    CompactQuery* pinned_cq = nullptr;   // pinned, nq entries
+    size_t pinned_cq_cap = 0;
+    uint8_t* pinned_delta = nullptr;     // pinned byte stream of back-deltas
+    size_t pinned_delta_cap = 0;
+    std::vector<gg_compact_chunk> cchunks;
+    std::vector<uint32_t> h_cslot;       // host copy of the first level-0 slot of each chromosome
+    int compact_delta_bytes = 1;         // width the next chunk starts with (sticky: widened after an overflow)
     int64_t fused_regs40 = 0;  // 1: the 40-register build of the fused kernel (6 CTAs/SM) instead of 32 registers (8 CTAs/SM)
     int64_t host_mode = 0;   // host-buffer pipeline: 0 = one fused kernel per chunk, 1 = count -> scan -> emit kernels
     int64_t count_mode = 2;  // 2: directory + finger search, 4 consecutive queries per thread; 0: directory, one query
@@ -168,11 +173,42 @@ gg_status fail(gg_index* idx, gg_status st, const char* what, cudaError_t e = cu
 
 // dense warp tiles (>= kDenseMin hits in 32 queries) only exist when queries average tens of hits; the dense pass (and the
 // per-tile totals it needs from the count pass) is switched on from what earlier batches / chunks on this handle showed
-inline bool dense_pass_on(const gg_index* idx, double min_density = 32.0) {
-    return idx->dense_emit < 0 ? idx->seen_hits_per_query >= min_density : idx->dense_emit != 0;
+inline bool dense_pass_on(const gg_index* idx, bool stranded = false) {
+    if (idx->dense_emit >= 0) return idx->dense_emit != 0;
+    return stranded ? idx->seen_hits_per_query_strand >= 32.0 : idx->seen_hits_per_query >= 12.0;
 }
-inline void note_density(gg_index* idx, uint64_t hits, size_t nq) {
-    if (nq >= 1024) idx->seen_hits_per_query = static_cast<double>(hits) / static_cast<double>(nq);
+// (batches of fewer than 64 k queries say little about the next large one and do not move the estimate)
+inline void note_density(gg_index* idx, uint64_t hits, size_t nq, bool stranded = false) {
+    if (nq < 65536) return;
+    (stranded ? idx->seen_hits_per_query_strand : idx->seen_hits_per_query) = static_cast<double>(hits) / static_cast<double>(nq);
+}
+// pick up the hit total an asynchronous device call left in the pinned mailbox (no wait: skipped if not landed yet)
+inline void poll_lazy_density(gg_index* idx) {
+    if (!idx->lazy_pending || cudaEventQuery(idx->ev_lazy) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    uint64_t total = 0;
+    std::memcpy(&total, idx->h_lazy + 2, 8);
+    note_density(idx, total, idx->lazy_nq, idx->lazy_stranded);
+    idx->lazy_pending = false;
+}
+inline cudaError_t post_lazy_density(gg_index* idx, const void* d_total8, size_t nq, bool stranded, cudaStream_t st) {
+    if (!idx->h_lazy) {
+        cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&idx->h_lazy), 16, cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&idx->ev_lazy, cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+    }
+    if (idx->lazy_pending && cudaEventQuery(idx->ev_lazy) != cudaSuccess) {  // previous total still in flight: keep that one
+        cudaGetLastError();
+        return cudaSuccess;
+    }
+    cudaError_t e = cudaMemcpyAsync(idx->h_lazy + 2, d_total8, 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaEventRecord(idx->ev_lazy, st);
+    idx->lazy_pending = e == cudaSuccess;
+    idx->lazy_nq = nq;
+    idx->lazy_stranded = stranded;
+    return e;
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -194,15 +230,33 @@ IndexView<C> make_view(const gg_index* idx) {
     v.dirE = idx->dirE.as<uint32_t>();
     v.dir_off = idx->dir_off.as<uint32_t>();
     v.dir_shift = idx->dir_shift;
+    v.base0 = idx->h_tab.empty() ? 0u : idx->h_tab[0];
     return v;
+}
+
+template <typename C>
+FlatMax<C> make_flat(const gg_index* idx) {
+    FlatMax<C> f;
+    f.leaf = idx->M.as<C>() + (idx->h_tab.empty() ? 0u : idx->h_tab[0]);
+    f.lv0 = idx->flat[0].as<C>();
+    f.lv1 = idx->flat[1].as<C>();
+    f.lv2 = idx->flat[2].as<C>();
+    f.lv3 = idx->flat[3].as<C>();
+    f.cbase = idx->cslot.as<uint32_t>();
+    f.n_chrom = idx->n_chrom;
+    f.n_lv = idx->n_flat;
+    return f;
 }
 
 size_t count_smem_bytes(const gg_index* idx) {
     size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
     return 2 * (static_cast<size_t>(idx->staged_elems) + kWin) * idx->coord_bytes + ((tab_elems + 3) & ~size_t(3)) * 4 + 32;
 }
+// the [n_levels][n_chrom + 1] offset table is copied into shared memory only while it is small; scaffold-level
+// assemblies (tens of thousands of contigs) read it through L1 instead
+inline bool tab_fits_smem(const gg_index* idx) { return static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024; }
 size_t emit_smem_bytes(const gg_index* idx) {
-    size_t tab_elems = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1);
+    size_t tab_elems = tab_fits_smem(idx) ? static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) : 0;
     return static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitSlack) * 4 + tab_elems * 4 + 16;
 }
 
@@ -213,7 +267,9 @@ gg_status launch_count(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
                        uint64_t* d_off, uint32_t* d_cnt, uint32_t* d_hi, uint32_t* d_err, void* scratch,
                        const uint64_t* d_base, cudaStream_t st, cudaEvent_t ev_after_count) {
     GG_CUDA(scan2_prepare_async(scratch, nq, st));
-    if (idx->count_mode == 2) {
+    // (the TMA-window kernel of count_mode 1 keeps the whole offset table in shared memory: many-contig groves take the
+    // directory kernel instead — same results)
+    if (idx->count_mode == 2 || (idx->count_mode == 1 && !tab_fits_smem(idx))) {
         // 4 consecutive queries per thread (finger search): the default
         const int vec_ok = aligned16(d_chrom) && aligned16(d_start) && aligned16(d_end) && aligned16(d_cnt) && aligned16(d_hi);
         auto kern = intersect_count_group_kernel<C, Q, kBatchQpt>;
@@ -275,7 +331,8 @@ gg_status launch_emit(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, 
     }
     size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads));
     unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
-    kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_hi, d_off, d_hits, hits_base);
+    kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_hi, d_off, d_hits, hits_base,
+                                            tab_fits_smem(idx) ? 1 : 0);
     GG_CUDA(cudaGetLastError());
     idx->bstats.kernel_launches++;
     return GG_OK;
@@ -387,9 +444,13 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     uint32_t* d_hi = reinterpret_cast<uint32_t*>(tail + round_up((nq ? nq : 1) * 4, 256));
     uint32_t* d_tile = reinterpret_cast<uint32_t*>(tail + 2 * round_up((nq ? nq : 1) * 4, 256));
     const bool tab_in_smem = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4 <= 8 * 1024;
-    const bool dense = dense_pass_on(idx, 12.0);  // the dense variants also carry the hybrid walk for tiles above the stage
+    const bool dense = dense_pass_on(idx);  // the dense variants also carry the hybrid walk for tiles above the stage
+    // pass 2 through the async proxy (emit_tma.cuh): TMA needs 16-byte aligned query arrays and 32-bit tile indices
+    const bool tma = !dense && idx->emit_tma != 0 && idx->emit_walk == 8 && aligned16(d_chrom) && aligned16(d_start) &&
+                     nq < 0xFFFFFFFFull;
     if (nq) {
-        auto kern = dense ? intersect_count_group_kernel<C, Q, kBatchQpt, true> : intersect_count_group_kernel<C, Q, kBatchQpt, false>;
+        auto kern = dense ? intersect_count_group_kernel<C, Q, kBatchQpt, true>
+                          : (tma ? intersect_count_group_kernel<C, Q, kBatchQpt, false, true> : intersect_count_group_kernel<C, Q, kBatchQpt, false>);
         int per_sm = static_cast<int>(idx->count_ctas_per_sm);
         if (per_sm <= 0) {
             GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
@@ -411,6 +472,25 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     if (timed) {
         GG_CUDA(cudaEventRecord(idx->ev[2], st));
         GG_CUDA(cudaEventRecord(idx->ev[3], st));
+    }
+    if (tma) {
+        const bool cb_smem = (static_cast<size_t>(idx->n_chrom) + 1) * 4 <= 8 * 1024;
+        const size_t smem = emit_tma_smem_bytes<Q>(cb_smem ? idx->n_chrom + 1 : 0);
+        auto kern = idx->emit_tma == 2 ? intersect_emit_tma_kernel<C, Q, uint32_t, false, false> : intersect_emit_tma_kernel<C, Q, uint32_t, false, true>;
+        GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        int per_sm = static_cast<int>(idx->emit_ctas_per_sm);
+        if (per_sm <= 0) {
+            GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+            if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "emit kernel does not fit on an SM");
+        }
+        const size_t ctas = div_up(std::max<size_t>(nb, 1), kQueryThreads / 32);
+        const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
+        kern<<<grid, kQueryThreads, smem, st>>>(make_flat<C>(idx), reinterpret_cast<const uint2*>(d_cnt), d_chrom, d_start, nq, block_prefix,
+                                                static_cast<uint32_t>(kBatchBlockQ), d_off, nullptr, d_hits, capacity, d_next_base, d_total,
+                                                d_err, cb_smem ? 1 : 0);
+        GG_CUDA(cudaGetLastError());
+        idx->bstats.kernel_launches++;
+        return GG_OK;
     }
     {
         const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
@@ -532,9 +612,10 @@ gg_status sort_by_field(gg_index* idx, const Field* d_field, int nbits, Key* key
 }
 
 // Shared by gg_index_build (do_sort = true) and gg_index_upload_sorted (do_sort = false).
+// dev_input: chrom / start / end / tie_key / rank_to_input are DEVICE pointers (gg_index_build_device).
 gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
                      const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom, uint32_t* rank_to_input,
-                     bool do_sort) {
+                     bool do_sort, bool dev_input = false) {
     if (!idx) return GG_ERR_INVALID_ARG;
     idx->err.clear();
     idx->built = false;
@@ -571,20 +652,29 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
 
     const size_t nn = n ? n : 1;
     GG_CUDA(cudaEventRecord(e0, st));
-    GG_CUDA(d_chrom.ensure(nn * 4));
-    GG_CUDA(d_start.ensure(nn * 8));
-    GG_CUDA(d_end.ensure(nn * 8));
+    if (dev_input && n) {
+        d_chrom.borrow(chrom, n * 4);
+        d_start.borrow(start, n * 8);
+        d_end.borrow(end, n * 8);
+        if (tie_mode == GG_TIE_EXPLICIT) d_tie.borrow(tie_key, n * 8);
+    } else {
+        GG_CUDA(d_chrom.ensure(nn * 4));
+        GG_CUDA(d_start.ensure(nn * 8));
+        GG_CUDA(d_end.ensure(nn * 8));
+    }
     GG_CUDA(d_stats.ensure(sizeof(BuildStats)));
     GG_CUDA(idx->cnt.ensure(static_cast<size_t>(n_chrom) * 4));
     GG_CUDA(cudaMemsetAsync(d_stats.p, 0, sizeof(BuildStats), st));
     GG_CUDA(cudaMemsetAsync(idx->cnt.p, 0, static_cast<size_t>(n_chrom) * 4, st));
     if (n) {
-        GG_CUDA(cudaMemcpyAsync(d_chrom.p, chrom, n * 4, cudaMemcpyHostToDevice, st));
-        GG_CUDA(cudaMemcpyAsync(d_start.p, start, n * 8, cudaMemcpyHostToDevice, st));
-        GG_CUDA(cudaMemcpyAsync(d_end.p, end, n * 8, cudaMemcpyHostToDevice, st));
-        if (tie_mode == GG_TIE_EXPLICIT) {
-            GG_CUDA(d_tie.ensure(n * 8));
-            GG_CUDA(cudaMemcpyAsync(d_tie.p, tie_key, n * 8, cudaMemcpyHostToDevice, st));
+        if (!dev_input) {
+            GG_CUDA(cudaMemcpyAsync(d_chrom.p, chrom, n * 4, cudaMemcpyHostToDevice, st));
+            GG_CUDA(cudaMemcpyAsync(d_start.p, start, n * 8, cudaMemcpyHostToDevice, st));
+            GG_CUDA(cudaMemcpyAsync(d_end.p, end, n * 8, cudaMemcpyHostToDevice, st));
+            if (tie_mode == GG_TIE_EXPLICIT) {
+                GG_CUDA(d_tie.ensure(n * 8));
+                GG_CUDA(cudaMemcpyAsync(d_tie.p, tie_key, n * 8, cudaMemcpyHostToDevice, st));
+            }
         }
         index_stats_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(),
                                                               d_end.as<uint64_t>(), d_tie.as<uint64_t>(), n, n_chrom,
@@ -719,7 +809,35 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
                 idx->S.as<uint32_t>(), idx->E.as<uint32_t>(), idx->M.as<uint32_t>(), row, row_below, C);
     }
     GG_CUDA(cudaGetLastError());
-    if (rank_to_input && n) GG_CUDA(cudaMemcpyAsync(rank_to_input, perm, n * 4, cudaMemcpyDeviceToHost, st));
+    {
+        // flat max-end hierarchy over the level-0 slots of all chromosomes (emit_tma.cuh) + first slot per chromosome
+        std::vector<uint32_t>& h_cslot = idx->h_cslot;
+        h_cslot.resize(C + 1);
+        for (uint32_t c = 0; c <= C; ++c) h_cslot[c] = idx->h_tab[c] - idx->h_tab[0];
+        GG_CUDA(idx->cslot.ensure((C + 1) * 4));
+        GG_CUDA(cudaMemcpyAsync(idx->cslot.p, h_cslot.data(), (C + 1) * 4, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaStreamSynchronize(st));  // (h_cslot is pageable host data)
+        uint32_t n_src = level0_elems;
+        const char* src = idx->M.as<char>() + static_cast<size_t>(idx->h_tab[0]) * idx->coord_bytes;
+        idx->n_flat = 0;
+        for (int k = 0; k < kFlatLevels; ++k) {
+            const uint32_t n_dst = static_cast<uint32_t>(div_up(n_src, kFanout));
+            GG_CUDA(idx->flat[k].ensure(static_cast<size_t>(n_dst ? n_dst : 1) * idx->coord_bytes));
+            if (n_dst) {
+                if (wide)
+                    flat_max_kernel<uint64_t><<<blocks_for(n_dst, 8), 256, 0, st>>>(reinterpret_cast<const uint64_t*>(src), idx->flat[k].as<uint64_t>(), n_src, n_dst);
+                else
+                    flat_max_kernel<uint32_t><<<blocks_for(n_dst, 8), 256, 0, st>>>(reinterpret_cast<const uint32_t*>(src), idx->flat[k].as<uint32_t>(), n_src, n_dst);
+            }
+            idx->n_flat = k + 1;
+            src = idx->flat[k].as<char>();
+            n_src = n_dst;
+            if (n_dst <= 1) break;
+        }
+        GG_CUDA(cudaGetLastError());
+    }
+    if (rank_to_input && n)
+        GG_CUDA(cudaMemcpyAsync(rank_to_input, perm, n * 4, dev_input ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
     {
         // ---- root directory: per-chromosome max coordinate = max over the (single) top node of M
         const size_t top_elems = static_cast<size_t>(C) * kFanout;
@@ -836,6 +954,21 @@ gg_status ensure_pinned_hits(gg_index* idx, size_t need_elems, size_t keep_elems
     return GG_OK;
 }
 
+// Error exits of the pipelined host-buffer calls must not leave chunks in flight: their async D2H copies would keep
+// writing into the caller's buffers after the call has failed.  Drains every slot stream unless dismissed.
+struct SlotDrain {
+    gg_index* idx;
+    bool armed = true;
+    ~SlotDrain() {
+        if (!armed || !idx->slots_ready) return;
+        for (int i = 0; i < kSlots; ++i) {
+            if (idx->slots[i].st) cudaStreamSynchronize(idx->slots[i].st);
+            idx->slots[i].busy = false;
+        }
+        cudaGetLastError();
+    }
+};
+
 // The reference-facing host-buffer call: chunked count -> scan -> emit pipeline over kSlots streams.
 template <typename Q>
 gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* q_start, const Q* q_end, size_t nq,
@@ -870,7 +1003,8 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
     GG_CUDA(cudaMemsetAsync(idx->d_base.p, 0, 8, st0));
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st0));
     GG_CUDA(cudaStreamSynchronize(st0));
-    for (int i = 0; i < kSlots; ++i) idx->slots[i].busy = false;
+    for (int i = 0; i < kSlots; ++i) idx->slots[i].busy = false;  // (every exit of the previous call drained the slots)
+    SlotDrain drain{idx};
 
     std::vector<uint64_t> base(n_chunks + 1, 0);
     cudaEvent_t prev_scan = nullptr;
@@ -1032,6 +1166,7 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
         GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
         idx->slots[i].busy = false;
     }
+    drain.armed = false;
     s = check_query_error(idx, st0);
     if (s != GG_OK) return s;
     if (any_invalid) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
@@ -1042,6 +1177,240 @@ gg_status intersect_batch_host(gg_index* idx, const uint32_t* q_chrom, const Q* 
     *hits = idx->pinned_hits;
     *n_hits = base[n_chunks];
     idx->bstats.n_hits = base[n_chunks];
+    return GG_OK;
+}
+
+// ------------------------------------------------------------------------------------------ compact host path
+// count (records) -> block-total scan -> intersect_emit_tma_kernel writing {chunk-local offset, hi slot} per query and a
+// back-delta of OutT per hit (emit_tma.cuh).  u32 index layout, u32 queries.
+template <typename OutT>
+gg_status launch_batch_compact(gg_index* idx, const uint32_t* d_chrom, const uint32_t* d_start, const uint32_t* d_end,
+                               size_t nq, CompactQuery* d_qres, OutT* d_delta, uint64_t capacity, uint64_t* d_total,
+                               void* scratch, uint32_t* d_err, cudaStream_t st) {
+    using C = uint32_t;
+    using Q = uint32_t;
+    char* p = static_cast<char*>(scratch);
+    const size_t nb = batch_blocks(nq), nb1 = nb + 1;
+    unsigned long long* block_total = reinterpret_cast<unsigned long long*>(p);
+    uint64_t* block_prefix = reinterpret_cast<uint64_t*>(p + round_up(nb1 * 8, 256));
+    void* scan_state = p + round_up(nb1 * 8, 256) + round_up((nb1 + 1) * 8, 256);
+    char* tail = p + std::max(round_up(fused_scratch_bytes(nq), 256), batch_ctl_bytes(nq));
+    uint32_t* d_rec = reinterpret_cast<uint32_t*>(tail);  // uint2[nq] over the cnt + hi regions of the scratch
+    if (nq) {
+        auto kern = intersect_count_group_kernel<C, Q, kBatchQpt, false, true>;
+        int per_sm = 0;
+        GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
+        if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "count kernel does not fit on an SM");
+        const size_t tiles = div_up(nq, static_cast<size_t>(kQueryThreads) * kBatchQpt);
+        const unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
+        kern<<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), d_chrom, d_start, d_end, nq, d_rec, nullptr, nullptr, block_total,
+                                             d_err, 1, nullptr);
+        GG_CUDA(cudaGetLastError());
+        idx->bstats.kernel_launches++;
+    }
+    GG_CUDA((exclusive_scan_async<uint64_t, uint64_t>(reinterpret_cast<const uint64_t*>(block_total), block_prefix, nb, scan_state,
+                                                       nullptr, nullptr, st)));
+    idx->bstats.kernel_launches++;
+    const size_t smem = emit_tma_smem_bytes<Q>(0);
+    auto kern = intersect_emit_tma_kernel<C, Q, OutT, true, false>;
+    GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int per_sm = 0;
+    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
+    if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "emit kernel does not fit on an SM");
+    const size_t ctas = div_up(std::max<size_t>(nb, 1), kQueryThreads / 32);
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
+    kern<<<grid, kQueryThreads, smem, st>>>(make_flat<C>(idx), reinterpret_cast<const uint2*>(d_rec), nullptr, d_start, nq, block_prefix,
+                                            static_cast<uint32_t>(kBatchBlockQ), nullptr, d_qres, d_delta, capacity, nullptr, d_total,
+                                            d_err, 0);
+    GG_CUDA(cudaGetLastError());
+    idx->bstats.kernel_launches++;
+    return GG_OK;
+}
+
+gg_status dispatch_batch_compact(gg_index* idx, int width, const uint32_t* d_chrom, const uint32_t* d_start,
+                                 const uint32_t* d_end, size_t nq, CompactQuery* d_qres, void* d_delta, uint64_t capacity,
+                                 uint64_t* d_total, void* scratch, uint32_t* d_err, cudaStream_t st) {
+    if (width == 1) return launch_batch_compact<uint8_t>(idx, d_chrom, d_start, d_end, nq, d_qres, static_cast<uint8_t*>(d_delta), capacity, d_total, scratch, d_err, st);
+    if (width == 2) return launch_batch_compact<uint16_t>(idx, d_chrom, d_start, d_end, nq, d_qres, static_cast<uint16_t*>(d_delta), capacity, d_total, scratch, d_err, st);
+    return launch_batch_compact<uint32_t>(idx, d_chrom, d_start, d_end, nq, d_qres, static_cast<uint32_t*>(d_delta), capacity, d_total, scratch, d_err, st);
+}
+
+template <typename T>
+gg_status ensure_pinned(gg_index* idx, T*& ptr, size_t& cap, size_t need, size_t keep, const char* what) {
+    if (need <= cap && ptr) return GG_OK;
+    const size_t want = std::max<size_t>(need, 4096);
+    T* np = nullptr;
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&np), want * sizeof(T), cudaHostAllocDefault);
+    if (e != cudaSuccess) return fail(idx, GG_ERR_OOM, what, e);
+    if (ptr) {
+        if (keep) std::memcpy(np, ptr, keep * sizeof(T));
+        cudaFreeHost(ptr);
+    }
+    ptr = np;
+    cap = want;
+    return GG_OK;
+}
+
+// Chunked pipeline over the kSlots streams, like intersect_batch_host, for the compact result form: per chunk H2D of 12 B
+// per query, the three kernels, D2H of 8 B per query + delta_bytes per hit.  A chunk is launched with an estimated delta
+// capacity and the handle's current delta width; overflow of either re-runs the chunk (exact size / next width).
+gg_status intersect_batch_compact_host(gg_index* idx, const uint32_t* q_chrom, const uint32_t* q_start, const uint32_t* q_end,
+                                       size_t nq, gg_compact_result* out) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!out || (nq && (!q_chrom || !q_start || !q_end))) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "the compact call needs a u32-layout index");
+    GG_CUDA(cudaSetDevice(idx->device));
+    gg_status s = ensure_slots(idx);
+    if (s != GG_OK) return s;
+    idx->h2_valid = false;
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+    // chunks stay below 2^32 hits (chunk-local u32 offsets) for any realistic density; a chunk that does not is reported
+    const size_t chunk = static_cast<size_t>(std::max<int64_t>(idx->chunk_queries, kScanTile) / kScanTile * kScanTile);
+    const size_t n_chunks = nq ? div_up(nq, chunk) : 0;
+    idx->bstats.n_chunks = static_cast<uint32_t>(n_chunks);
+    idx->cchunks.assign(n_chunks, gg_compact_chunk{});
+    *out = gg_compact_result{};
+    out->chunk_queries = chunk;
+    out->n_chrom = idx->n_chrom;
+    out->chrom_slot_base = idx->h_cslot.data();
+    s = ensure_pinned(idx, idx->pinned_cq, idx->pinned_cq_cap, std::max<size_t>(nq, 1), 0, "pinned query records");
+    if (s != GG_OK) return s;
+    if (!idx->pinned_delta) {
+        s = ensure_pinned(idx, idx->pinned_delta, idx->pinned_delta_cap, 4096, 0, "pinned delta stream");
+        if (s != GG_OK) return s;
+    }
+    out->queries = reinterpret_cast<const gg_compact_query*>(idx->pinned_cq);
+    out->deltas = idx->pinned_delta;
+    if (nq == 0) return GG_OK;
+    for (int i = 0; i < kSlots; ++i) idx->slots[i].busy = false;
+    SlotDrain drain{idx};
+
+    bool any_invalid = false;
+    double est_per_q = std::max(8.0, idx->seen_hits_per_query * 1.1);
+    uint64_t hit_base = 0, byte_off = 0;
+    std::vector<int> width_of(n_chunks, 0);
+    auto stage_a = [&](size_t k) -> gg_status {
+        Slot& sl = idx->slots[k % kSlots];
+        if (sl.busy) {
+            GG_CUDA(cudaEventSynchronize(sl.ev_done));
+            sl.busy = false;
+        }
+        const size_t q0 = k * chunk, m = std::min(chunk, nq - q0);
+        GG_CUDA(sl.qc.ensure(m * 4));
+        GG_CUDA(sl.qs.ensure(m * 4));
+        GG_CUDA(sl.qe.ensure(m * 4));
+        GG_CUDA(sl.off.ensure(m * 8));  // CompactQuery records
+        GG_CUDA(sl.fscratch.ensure(single_scratch_bytes(m)));
+        GG_CUDA(sl.err.ensure(16));
+        const int width = idx->compact_delta_bytes;
+        width_of[k] = width;
+        const size_t want = (static_cast<size_t>(est_per_q * 1.25 * static_cast<double>(m)) + 4096) * width;
+        if (sl.hits.cap < want) GG_CUDA(sl.hits.ensure(want));
+        sl.launch_cap = sl.hits.cap / width;
+        GG_CUDA(cudaMemcpyAsync(sl.qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qs.p, q_start + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemcpyAsync(sl.qe.p, q_end + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
+        GG_CUDA(cudaMemsetAsync(sl.err.p, 0, 16, sl.st));
+        uint64_t* d_total = reinterpret_cast<uint64_t*>(sl.err.as<char>() + 8);
+        gg_status r = dispatch_batch_compact(idx, width, sl.qc.as<uint32_t>(), sl.qs.as<uint32_t>(), sl.qe.as<uint32_t>(), m,
+                                             sl.off.as<CompactQuery>(), sl.hits.p, sl.launch_cap, d_total, sl.fscratch.p,
+                                             sl.err.as<uint32_t>(), sl.st);
+        if (r != GG_OK) return r;
+        GG_CUDA(cudaMemcpyAsync(sl.h_next_base, sl.err.p, 16, cudaMemcpyDeviceToHost, sl.st));  // [flag, -, total]
+        GG_CUDA(cudaEventRecord(sl.ev_total, sl.st));
+        GG_CUDA(cudaMemcpyAsync(idx->pinned_cq + q0, sl.off.p, m * 8, cudaMemcpyDeviceToHost, sl.st));
+        sl.busy = true;
+        return GG_OK;
+    };
+    auto stage_b = [&](size_t k) -> gg_status {
+        Slot& sl = idx->slots[k % kSlots];
+        const size_t q0 = k * chunk, m = std::min(chunk, nq - q0);
+        for (;;) {
+            GG_CUDA(cudaEventSynchronize(sl.ev_total));
+            const uint32_t flag = static_cast<uint32_t>(sl.h_next_base[0]);
+            const uint64_t total = sl.h_next_base[1];
+            if (flag & 1u) any_invalid = true;
+            if (flag & 8u) return fail(idx, GG_ERR_CAPACITY, "a chunk of the compact call has 2^32 hits or more: lower chunk_queries");
+            int width = width_of[k];
+            const bool too_narrow = (flag & 16u) != 0 && width < 4, too_small = total > sl.launch_cap;
+            if (!too_narrow && !too_small) {
+                est_per_q = std::max(1.0, static_cast<double>(hit_base + total) / static_cast<double>(q0 + m));
+                note_density(idx, hit_base + total, q0 + m);
+                gg_compact_chunk& ck = idx->cchunks[k];
+                ck.q_begin = q0;
+                ck.n_queries = m;
+                ck.n_hits = total;
+                ck.hit_base = hit_base;
+                ck.delta_byte_offset = byte_off;
+                ck.delta_bytes = static_cast<uint32_t>(width);
+                const uint64_t bytes = total * width;
+                if (byte_off + bytes > idx->pinned_delta_cap) {
+                    // grow with an estimate of the final size; copies of earlier chunks must have landed first
+                    for (int i = 0; i < kSlots; ++i)
+                        if (idx->slots[i].busy) GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
+                    const double per_q = static_cast<double>(byte_off + bytes) / static_cast<double>(q0 + m);
+                    const size_t est = static_cast<size_t>(per_q * 1.15 * static_cast<double>(nq)) + 65536;
+                    gg_status r = ensure_pinned(idx, idx->pinned_delta, idx->pinned_delta_cap, std::max<size_t>(est, byte_off + bytes),
+                                                byte_off, "pinned delta stream");
+                    if (r != GG_OK) return r;
+                }
+                if (bytes) GG_CUDA(cudaMemcpyAsync(idx->pinned_delta + byte_off, sl.hits.p, bytes, cudaMemcpyDeviceToHost, sl.st));
+                hit_base += total;
+                byte_off = round_up(byte_off + bytes, 16);
+                GG_CUDA(cudaEventRecord(sl.ev_done, sl.st));
+                return GG_OK;
+            }
+            // re-run this chunk: one width up and / or with the exact capacity (same queries, already on the device)
+            GG_CUDA(cudaStreamSynchronize(sl.st));
+            if (too_narrow) {
+                width *= 2;
+                idx->compact_delta_bytes = std::max(idx->compact_delta_bytes, width);
+                width_of[k] = width;
+            }
+            const size_t want = std::max<size_t>(static_cast<size_t>(total), 1) * width;
+            if (sl.hits.cap < want) GG_CUDA(sl.hits.ensure(want));
+            sl.launch_cap = sl.hits.cap / width;
+            GG_CUDA(cudaMemsetAsync(sl.err.p, 0, 16, sl.st));
+            uint64_t* d_total = reinterpret_cast<uint64_t*>(sl.err.as<char>() + 8);
+            gg_status r = dispatch_batch_compact(idx, width, sl.qc.as<uint32_t>(), sl.qs.as<uint32_t>(), sl.qe.as<uint32_t>(), m,
+                                                 sl.off.as<CompactQuery>(), sl.hits.p, sl.launch_cap, d_total, sl.fscratch.p,
+                                                 sl.err.as<uint32_t>(), sl.st);
+            if (r != GG_OK) return r;
+            GG_CUDA(cudaMemcpyAsync(sl.h_next_base, sl.err.p, 16, cudaMemcpyDeviceToHost, sl.st));
+            GG_CUDA(cudaEventRecord(sl.ev_total, sl.st));
+            GG_CUDA(cudaMemcpyAsync(idx->pinned_cq + q0, sl.off.p, m * 8, cudaMemcpyDeviceToHost, sl.st));
+        }
+    };
+    const size_t lead = std::min<size_t>(kSlots - 1, n_chunks);
+    for (size_t k = 0; k < lead; ++k) {
+        s = stage_a(k);
+        if (s != GG_OK) return s;
+    }
+    for (size_t k = 0; k < n_chunks; ++k) {
+        if (k + lead < n_chunks) {
+            s = stage_a(k + lead);
+            if (s != GG_OK) return s;
+        }
+        s = stage_b(k);
+        if (s != GG_OK) return s;
+    }
+    for (int i = 0; i < kSlots; ++i) {
+        GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
+        idx->slots[i].busy = false;
+    }
+    drain.armed = false;
+    if (any_invalid) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+    out->n_queries = nq;
+    out->n_hits = hit_base;
+    out->queries = reinterpret_cast<const gg_compact_query*>(idx->pinned_cq);
+    out->deltas = idx->pinned_delta;
+    out->delta_bytes_total = byte_off;
+    out->chunks = idx->cchunks.data();
+    out->n_chunks = static_cast<uint32_t>(n_chunks);
+    idx->bstats.n_hits = hit_base;
     return GG_OK;
 }
 
@@ -1089,7 +1458,7 @@ void gg_index_destroy(gg_index* idx) {
     cudaDeviceSynchronize();
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
-                         &idx->ER, &idx->cbegin, &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
+                         &idx->ER, &idx->cbegin, &idx->cslot, &idx->flat[0], &idx->flat[1], &idx->flat[2], &idx->flat[3], &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
                          &idx->s_cnt, &idx->s_hi, &idx->s_tile, &idx->s_scan, &idx->s_total})
         b->release();
     for (auto& s : idx->slots) {
@@ -1101,7 +1470,11 @@ void gg_index_destroy(gg_index* idx) {
         if (s.h_next_base) cudaFreeHost(s.h_next_base);
     }
     if (idx->pinned_hits) cudaFreeHost(idx->pinned_hits);
+    if (idx->pinned_cq) cudaFreeHost(idx->pinned_cq);
+    if (idx->pinned_delta) cudaFreeHost(idx->pinned_delta);
     if (idx->h_err) cudaFreeHost(idx->h_err);
+    if (idx->h_lazy) cudaFreeHost(idx->h_lazy);
+    if (idx->ev_lazy) cudaEventDestroy(idx->ev_lazy);
     for (auto& e : idx->ev)
         if (e) cudaEventDestroy(e);
     if (idx->stream) cudaStreamDestroy(idx->stream);
@@ -1113,6 +1486,12 @@ const char* gg_last_error(const gg_index* idx) { return idx ? idx->err.c_str() :
 gg_status gg_index_build(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
                          const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom, uint32_t* rank_to_input) {
     return build_impl(idx, chrom, start, end, tie_key, tie_mode, n, n_chrom, rank_to_input, true);
+}
+
+gg_status gg_index_build_device(gg_index* idx, const uint32_t* d_chrom, const uint64_t* d_start, const uint64_t* d_end,
+                                const uint64_t* d_tie_key, int tie_mode, size_t n, uint32_t n_chrom,
+                                uint32_t* d_rank_to_input) {
+    return build_impl(idx, d_chrom, d_start, d_end, d_tie_key, tie_mode, n, n_chrom, d_rank_to_input, true, true);
 }
 
 gg_status gg_index_upload_sorted(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
@@ -1143,6 +1522,69 @@ gg_status gg_intersect_batch_u32(gg_index* idx, const uint32_t* q_chrom, const u
                                  const uint32_t* q_end, size_t nq, uint64_t* offsets, const uint32_t** hits,
                                  uint64_t* n_hits) {
     return intersect_batch_host<uint32_t>(idx, q_chrom, q_start, q_end, nq, offsets, hits, n_hits);
+}
+
+gg_status gg_intersect_batch_compact(gg_index* idx, const uint32_t* q_chrom, const uint32_t* q_start, const uint32_t* q_end,
+                                     size_t nq, gg_compact_result* out) {
+    return intersect_batch_compact_host(idx, q_chrom, q_start, q_end, nq, out);
+}
+
+uint64_t gg_compact_count(const gg_compact_result* r, uint64_t q) {
+    if (!r || q >= r->n_queries) return 0;
+    const gg_compact_chunk& ck = r->chunks[q / r->chunk_queries];
+    const uint64_t end = q + 1 < ck.q_begin + ck.n_queries ? r->queries[q + 1].off : ck.n_hits;
+    return end - r->queries[q].off;
+}
+
+uint32_t gg_compact_rank(const gg_compact_result* r, const uint32_t* q_chrom, uint64_t q, uint64_t j) {
+    const gg_compact_chunk& ck = r->chunks[q / r->chunk_queries];
+    const gg_compact_query& cq = r->queries[q];
+    const uint8_t* d = r->deltas + ck.delta_byte_offset + (static_cast<uint64_t>(cq.off) + j) * ck.delta_bytes;
+    uint32_t delta;
+    if (ck.delta_bytes == 1) delta = *d;
+    else if (ck.delta_bytes == 2) { uint16_t v; std::memcpy(&v, d, 2); delta = v; }
+    else std::memcpy(&delta, d, 4);
+    return cq.hi_slot - r->chrom_slot_base[q_chrom[q]] - 1u - delta;
+}
+
+gg_status gg_compact_expand(const gg_compact_result* r, const uint32_t* q_chrom, uint64_t* offsets, uint32_t* hits,
+                            int n_threads) {
+    if (!r || !offsets || (r->n_queries && !q_chrom) || (r->n_hits && !hits)) return GG_ERR_INVALID_ARG;
+    unsigned T = n_threads > 0 ? static_cast<unsigned>(n_threads) : std::max(1u, std::thread::hardware_concurrency());
+    T = std::max(1u, std::min<unsigned>(T, std::max<uint32_t>(r->n_chunks, 1u)));
+    auto work = [&](unsigned t) {
+        for (uint32_t k = t; k < r->n_chunks; k += T) {
+            const gg_compact_chunk& ck = r->chunks[k];
+            const uint8_t* d = r->deltas + ck.delta_byte_offset;
+            for (uint64_t i = 0; i < ck.n_queries; ++i) {
+                const uint64_t q = ck.q_begin + i;
+                const gg_compact_query& cq = r->queries[q];
+                const uint64_t end = i + 1 < ck.n_queries ? r->queries[q + 1].off : ck.n_hits;
+                offsets[q] = ck.hit_base + cq.off;
+                if (end == cq.off) continue;
+                const uint32_t top = cq.hi_slot - r->chrom_slot_base[q_chrom[q]] - 1u;
+                uint32_t* o = hits + ck.hit_base;
+                if (ck.delta_bytes == 1) {
+                    for (uint64_t h = cq.off; h < end; ++h) o[h] = top - d[h];
+                } else if (ck.delta_bytes == 2) {
+                    const uint16_t* d2 = reinterpret_cast<const uint16_t*>(d);
+                    for (uint64_t h = cq.off; h < end; ++h) o[h] = top - d2[h];
+                } else {
+                    const uint32_t* d4 = reinterpret_cast<const uint32_t*>(d);
+                    for (uint64_t h = cq.off; h < end; ++h) o[h] = top - d4[h];
+                }
+            }
+        }
+    };
+    if (T == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < T; ++t) th.emplace_back(work, t);
+        for (auto& x : th) x.join();
+    }
+    offsets[r->n_queries] = r->n_hits;
+    return GG_OK;
 }
 
 gg_status gg_intersect_count_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
@@ -1229,6 +1671,7 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
     idx->bstats.n_chunks = 1;
     idx->ev_count_valid = idx->ev_emit_valid = false;
     idx->counted_nq = 0;  // the two-phase emit needs its own count pass
+    poll_lazy_density(idx);
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 16, st));
     if (idx->timing) {
         GG_CUDA(cudaEventRecord(idx->ev[0], st));
@@ -1253,6 +1696,8 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
         note_density(idx, *total_hits, nq);
         if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
         if (flag & 2u) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
+    } else {
+        GG_CUDA(post_lazy_density(idx, d_total, nq, false, st));
     }
     return GG_OK;
 }
@@ -1362,10 +1807,13 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "fused_kernel" && value >= -1 && value <= 1) idx->fused_kernel = value;
     else if (k == "dense_emit" && value >= -1 && value <= 1) idx->dense_emit = value;
     else if (k == "emit_walk" && (value == 8 || value == 16)) idx->emit_walk = value;
+    else if (k == "emit_tma" && value >= 0 && value <= 2) idx->emit_tma = value;
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;
+    else if (k == "inject_alloc_failure" && value >= 0) g_alloc_fail_countdown.store(value);
+    else if (k == "compact_delta_bytes" && (value == 1 || value == 2 || value == 4)) idx->compact_delta_bytes = static_cast<int>(value);
     else return fail(idx, GG_ERR_INVALID_ARG, "unknown option or value out of range");
     return GG_OK;
 }
@@ -1437,6 +1885,7 @@ gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64
     gg_status s = ensure_slots(idx);
     if (s != GG_OK) return s;
     // chunks round-robin over the pipeline slots' streams: H2D of chunk k+1 and D2H of chunk k-1 overlap kernel k
+    SlotDrain drain{idx};  // (error exits below leave no copy into pred / succ in flight)
     const size_t chunk = static_cast<size_t>(std::max<int64_t>(idx->chunk_queries, 1024));
     const size_t cap = std::min(chunk, nq ? nq : 1);
     size_t k = 0;
@@ -1483,7 +1932,7 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
     uint32_t* d_hi = idx->s_hi.as<uint32_t>();
     if (!emit_only) {
         if (nq) {
-            idx->s_dense = dense_pass_on(idx);  // the emit phase of this batch follows the same choice
+            idx->s_dense = dense_pass_on(idx, true);  // the emit phase of this batch follows the same choice
             auto kern = idx->s_dense ? strand_count_group_kernel<C, Q, kBatchQpt, true> : strand_count_group_kernel<C, Q, kBatchQpt, false>;
             int per_sm = 0;
             GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, 0));
@@ -1566,6 +2015,7 @@ gg_status gg_index_set_strands(gg_index* idx, const uint8_t* strand, size_t n) {
             return fail(idx, GG_ERR_INVALID_ARG, "genomic_coordinate: strand must be one of '+', '-', '.', '*'");
     }
     GG_CUDA(cudaSetDevice(idx->device));
+    idx->has_strand = false;  // until every step below has succeeded
     const size_t C = idx->n_chrom;
     const uint32_t level0_elems = idx->h_tab[C] - idx->h_tab[0];
     DeviceBuf tmp;
@@ -1614,6 +2064,10 @@ gg_status gg_index_set_strands(gg_index* idx, const uint8_t* strand, size_t n) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
     tmp.release();
     for (DeviceBuf* b : {&cntS, &cntE, &preS, &preE, &scan_state}) b->release();
+    if (e != cudaSuccess) {  // the stranded entry points must not run on missing / half-built strand records
+        idx->has_strand = false;
+        return fail(idx, GG_ERR_CUDA, "gg_index_set_strands", e);
+    }
     idx->has_strand = true;
     return GG_OK;
 }
@@ -1637,6 +2091,7 @@ gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, c
     idx->bstats.n_queries = nq;
     idx->bstats.n_chunks = 1;
     idx->counted_nq = 0;
+    poll_lazy_density(idx);
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
     s = dispatch_stranded(idx, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_offsets, d_hits, capacity, nullptr,
                           idx->s_total.as<uint64_t>(), idx->err_flag.as<uint32_t>(), false, st);
@@ -1653,10 +2108,12 @@ gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, c
         std::memcpy(total_hits, idx->h_err + 2, 8);
         flag = idx->h_err[0];
         idx->bstats.n_hits = *total_hits;
-        note_density(idx, *total_hits, nq);
+        note_density(idx, *total_hits, nq, true);
         s = strand_query_error(idx, flag);
         if (s != GG_OK) return s;
         if (*total_hits > capacity) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
+    } else {
+        GG_CUDA(post_lazy_density(idx, idx->s_total.p, nq, true, st));
     }
     return GG_OK;
 }
@@ -1706,7 +2163,7 @@ gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, co
         GG_CUDA(cudaStreamSynchronize(st));
         s = strand_query_error(idx, flag);
         if (s != GG_OK) return s;
-        note_density(idx, total, m);
+        note_density(idx, total, m, true);
         GG_CUDA(idx->sq_hits.ensure((total ? total : 1) * 4));
         s = ensure_pinned_hits(idx, base + total, base);
         if (s != GG_OK) return s;

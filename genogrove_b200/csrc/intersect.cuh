@@ -40,6 +40,7 @@ struct IndexView {
     const uint32_t* dirE;
     const uint32_t* dir_off;  // [n_chrom + 1]; chromosome c has dir_off[c+1] - dir_off[c] - 1 bins
     int dir_shift;
+    uint32_t base0;           // = tab[0][0]: first element of the leaf level (level-0 "slot" = element - base0)
 };
 
 constexpr int kQueryThreads = 256;
@@ -392,7 +393,7 @@ __device__ __forceinline__ uint32_t finger_upper_bound(const C* __restrict__ a, 
 template <typename C, typename Q, int QPT>
 __device__ __forceinline__ bool count_group(const IndexView<C>& ix, const uint32_t* __restrict__ tabp,
                                             const uint32_t (&chrom)[QPT], const Q (&qs_raw)[QPT], const Q (&qe_raw)[QPT],
-                                            uint32_t (&cnt)[QPT], uint32_t (&hi)[QPT], C (&qs)[QPT]) {
+                                            uint32_t (&cnt)[QPT], uint32_t (&hi)[QPT], C (&qs)[QPT], uint32_t (&slot)[QPT]) {
     Finger<C> fs, fe;
     uint32_t cur = GG_NO_CHROM_DEV, d0 = 0, last_bin = 0, leaf = 0;
     bool any_bad = false;
@@ -412,6 +413,7 @@ __device__ __forceinline__ bool count_group(const IndexView<C>& ix, const uint32
         cnt[j] = 0;
         hi[j] = 0;
         qs[j] = 0;
+        slot[j] = 0;
         if (ok) {
             if (chrom[j] != cur) {
                 cur = chrom[j];
@@ -427,6 +429,7 @@ __device__ __forceinline__ bool count_group(const IndexView<C>& ix, const uint32
             if (qs[j] > 0)
                 lo = finger_upper_bound<C>(ix.E + leaf, ix.dirE + d0, last_bin, shift, static_cast<C>(qs[j] - 1), fe, grouped);
             cnt[j] = hi[j] - lo;
+            slot[j] = leaf - ix.base0 + hi[j];  // level-0 slot of hi over all chromosomes (emit_tma.cuh walks on slots)
         }
     }
     return any_bad;
@@ -449,7 +452,9 @@ __device__ __forceinline__ void store_vec_u32(uint32_t* __restrict__ p, const ui
 // intersect_count_dir_kernel (tile_total, for the two-phase API's scan), and / or block_total[b] = hits of the
 // b-th block of 32 * QPT consecutive queries (one warp's share; plain stores, no atomics) for the batch path,
 // whose emit kernel turns scanned block totals into offsets itself.  A warp's queries never straddle a scan tile.
-template <typename C, typename Q, int QPT, bool kTiles = false>
+// kRec: instead of cnt_out / hi_out the kernel writes one record {count, level-0 slot of hi} per query into
+// cnt_out viewed as uint2[nq] — the input of intersect_emit_tma_kernel (emit_tma.cuh), one TMA copy per 32 queries.
+template <typename C, typename Q, int QPT, bool kTiles = false, bool kRec = false>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_count_group_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                              const Q* __restrict__ qend, size_t nq, uint32_t* __restrict__ cnt_out,
@@ -477,10 +482,21 @@ intersect_count_group_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchro
                 qe_raw[j] = in ? qend[q0 + j] : Q(0);
             }
         }
-        uint32_t cnt[QPT], hi[QPT];
+        uint32_t cnt[QPT], hi[QPT], slot[QPT];
         C qs[QPT];
-        if (count_group<C, Q, QPT>(ix, ix.tab, chrom, qs_raw, qe_raw, cnt, hi, qs)) atomicOr(err_flag, 1u);
-        if (vec) {  // (cnt_out / hi_out are 16-byte aligned whenever vec_ok: the host checks)
+        if (count_group<C, Q, QPT>(ix, ix.tab, chrom, qs_raw, qe_raw, cnt, hi, qs, slot)) atomicOr(err_flag, 1u);
+        if constexpr (kRec) {
+            uint2* rec = reinterpret_cast<uint2*>(cnt_out);
+            if (q0 + QPT <= nq) {  // (the record array is library scratch: always 16-byte aligned)
+#pragma unroll
+                for (int j = 0; j < QPT; j += 2)
+                    *reinterpret_cast<uint4*>(rec + q0 + j) = make_uint4(cnt[j], slot[j], cnt[j + 1], slot[j + 1]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < QPT; ++j)
+                    if (q0 + j < nq) rec[q0 + j] = make_uint2(cnt[j], slot[j]);
+            }
+        } else if (vec) {  // (cnt_out / hi_out are 16-byte aligned whenever vec_ok: the host checks)
             store_vec_u32<QPT>(cnt_out + q0, cnt);
             store_vec_u32<QPT>(hi_out + q0, hi);
         } else {
@@ -920,15 +936,19 @@ template <typename C, typename Q>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                       size_t nq, const uint32_t* __restrict__ hi_in, const uint64_t* __restrict__ offsets,
-                      uint32_t* __restrict__ hits, uint64_t hits_base) {
+                      uint32_t* __restrict__ hits, uint64_t hits_base, int tab_in_smem) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStageWords = kEmitStage + kEmitSlack;
-    uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + (kQueryThreads / 32) * kStageWords;
+    const uint32_t* __restrict__ stab = ix.tab;  // many-contig groves: the offset table stays in global memory (L1)
     const uint32_t stage_addr = smem_u32(smem_raw) + ((threadIdx.x >> 5) * kStageWords + kEmitSlack) * 4u;
     const uint32_t stride = ix.n_chrom + 1;
-    const uint32_t tab_elems = static_cast<uint32_t>(ix.n_levels) * stride;
-    for (uint32_t i = threadIdx.x; i < tab_elems; i += blockDim.x) stab[i] = ix.tab[i];
-    __syncthreads();
+    if (tab_in_smem) {
+        uint32_t* st = reinterpret_cast<uint32_t*>(smem_raw) + (kQueryThreads / 32) * kStageWords;
+        const uint32_t tab_elems = static_cast<uint32_t>(ix.n_levels) * stride;
+        for (uint32_t i = threadIdx.x; i < tab_elems; i += blockDim.x) st[i] = ix.tab[i];
+        stab = st;
+        __syncthreads();
+    }
 
     const int n_levels = ix.n_levels;
     const uint32_t lane = lane_id();

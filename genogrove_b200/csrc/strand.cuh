@@ -202,9 +202,9 @@ strand_count_group_kernel(IndexView<C> ix, const StrandNode* __restrict__ SN, co
                 chrom[j] = GG_NO_CHROM_DEV;  // no hits for this query; the call fails with the flag below
             }
         }
-        uint32_t cnt[QPT], hi[QPT];
+        uint32_t cnt[QPT], hi[QPT], slot[QPT];
         C qs[QPT];
-        uint32_t flags = count_group<C, Q, QPT>(ix, ix.tab, chrom, qs_raw, qe_raw, cnt, hi, qs) ? 1u : 0u;
+        uint32_t flags = count_group<C, Q, QPT>(ix, ix.tab, chrom, qs_raw, qe_raw, cnt, hi, qs, slot) ? 1u : 0u;
         if (bad_strand) flags |= 4u;
         if (flags) atomicOr(err_flag, flags);
 #pragma unroll

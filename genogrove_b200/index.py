@@ -122,6 +122,24 @@ class DeviceIndex:
         view = np.ctypeslib.as_array(hp, shape=(n_hits,))
         return offsets, (view.copy() if copy_hits else view)
 
+    def intersect_batch_compact(self, q_chrom, q_start, q_end, expand: bool = True, threads: int = 0):
+        """gg_intersect_batch_compact (u32 coordinates): the PCIe-lean result form — 8 B per query + a 1/2/4-byte
+        back-delta per hit.  expand=True decodes it on the host (gg_compact_expand) into the plain (offsets, hits) CSR;
+        expand=False returns the raw ``CompactResult`` (library-owned pinned arrays, valid until the next call)."""
+        qc, a, b = _arr(q_chrom, np.uint32), _arr(q_start, np.uint32), _arr(q_end, np.uint32)
+        nq = len(qc)
+        res = _lib.CompactResult()
+        self._check(self._L.gg_intersect_batch_compact(self._h, _ptr(qc), _ptr(a), _ptr(b), nq, C.byref(res)))
+        self.last_compact = res
+        if not expand:
+            return res
+        offsets = np.empty(nq + 1, dtype=np.uint64)
+        hits = np.empty(int(res.n_hits), dtype=np.uint32)
+        st = self._L.gg_compact_expand(C.byref(res), _ptr(qc), _ptr(offsets), _ptr(hits) if len(hits) else None, threads)
+        if st != 0:
+            raise GGError(st, "gg_compact_expand")
+        return offsets, hits
+
     def intersect_two_phase(self, q_chrom, q_start, q_end):
         """gg_intersect_count + gg_intersect_emit with a caller-owned hit buffer."""
         qc, a, b = _arr(q_chrom, np.uint32), _arr(q_start, np.uint64), _arr(q_end, np.uint64)

@@ -121,6 +121,11 @@ gg_status gg_index_build(gg_index* idx, const uint32_t* chrom, const uint64_t* s
  * a chromosome, in leaf-chain order (non-decreasing start).  No sort of (start,end) is performed. */
 gg_status gg_index_upload_sorted(gg_index* idx, const uint32_t* chrom, const uint64_t* start,
                                  const uint64_t* end, size_t n, uint32_t n_chrom);
+/* gg_index_build with DEVICE buffers in and out (intervals that already live in HBM: the chromosome-sharded group build
+ * receives its records over NVLink).  d_rank_to_input: device buffer of n u32, nullable.  The call synchronises. */
+gg_status gg_index_build_device(gg_index* idx, const uint32_t* d_chrom, const uint64_t* d_start, const uint64_t* d_end,
+                                const uint64_t* d_tie_key, int tie_mode, size_t n, uint32_t n_chrom,
+                                uint32_t* d_rank_to_input);
 gg_status gg_index_get_stats(const gg_index* idx, gg_index_stats* out);
 /* counts[c] = number of intervals of chromosome c (n_chrom entries) */
 gg_status gg_index_chrom_counts(const gg_index* idx, uint64_t* counts);
@@ -137,6 +142,50 @@ gg_status gg_intersect_batch(gg_index* idx, const uint32_t* q_chrom, const uint6
 gg_status gg_intersect_batch_u32(gg_index* idx, const uint32_t* q_chrom, const uint32_t* q_start,
                                  const uint32_t* q_end, size_t nq, uint64_t* offsets, const uint32_t** hits,
                                  uint64_t* n_hits);
+/* ---- compact result form of the host-buffer call ------------------------------------------------- */
+/* Same hits as gg_intersect_batch_u32, encoded for the PCIe link (the host path is transfer-bound: 8 B of offset + 4 B
+ * per hit down, 20 B per query up).  Per query one 8-byte record, per hit a 1-, 2- or 4-byte BACK-DELTA from the query's
+ * hi slot (hits of BED/BAM-shaped data sit within a few dozen ranks of it):
+ *     k         = q / chunk_queries                       (chunks are uniform except the last)
+ *     n_q       = (q + 1 < chunks[k].q_begin + chunks[k].n_queries ? queries[q + 1].off : chunks[k].n_hits) - queries[q].off
+ *     delta_j   = the (queries[q].off + j)-th element (chunks[k].delta_bytes wide) of deltas + chunks[k].delta_byte_offset
+ *     rank_j    = queries[q].hi_slot - chrom_slot_base[q_chrom[q]] - 1 - delta_j          ascending in j, as always
+ * gg_compact_rank / gg_compact_count below are that arithmetic.  The delta width is chosen per chunk: a chunk whose
+ * largest delta does not fit is re-run one width up (and the handle keeps the wider width).  All arrays are library-owned
+ * pinned memory, valid until the next intersect call on the handle.  Needs a coord_bytes == 4 index. */
+typedef struct gg_compact_query {
+    uint32_t off;     /* index of the query's first hit inside its chunk */
+    uint32_t hi_slot; /* level-0 slot of the first interval starting past q.end */
+} gg_compact_query;
+typedef struct gg_compact_chunk {
+    uint64_t q_begin;
+    uint64_t n_queries;
+    uint64_t n_hits;
+    uint64_t hit_base;          /* hits of all chunks before this one */
+    uint64_t delta_byte_offset; /* of this chunk's deltas inside `deltas` (16-byte aligned) */
+    uint32_t delta_bytes;       /* 1, 2 or 4 */
+    uint32_t reserved;
+} gg_compact_chunk;
+typedef struct gg_compact_result {
+    uint64_t n_queries, n_hits;
+    uint64_t chunk_queries;              /* queries per chunk (the last chunk may be shorter) */
+    const gg_compact_query* queries;     /* n_queries records */
+    const uint8_t* deltas;
+    uint64_t delta_bytes_total;
+    const gg_compact_chunk* chunks;
+    uint32_t n_chunks;
+    uint32_t n_chrom;
+    const uint32_t* chrom_slot_base;     /* [n_chrom + 1] first level-0 slot of each chromosome */
+} gg_compact_result;
+gg_status gg_intersect_batch_compact(gg_index* idx, const uint32_t* q_chrom, const uint32_t* q_start,
+                                     const uint32_t* q_end, size_t nq, gg_compact_result* out);
+/* decode helpers (host arithmetic on the arrays above; no device work) */
+uint64_t gg_compact_count(const gg_compact_result* r, uint64_t q);
+uint32_t gg_compact_rank(const gg_compact_result* r, const uint32_t* q_chrom, uint64_t q, uint64_t j);
+/* expand into the plain CSR of gg_intersect_batch (offsets: nq + 1 u64, hits: n_hits u32); n_threads <= 0: all cores */
+gg_status gg_compact_expand(const gg_compact_result* r, const uint32_t* q_chrom, uint64_t* offsets, uint32_t* hits,
+                            int n_threads);
+
 /* Two-phase variant with a caller-owned hit buffer: count fills offsets[nq+1] and keeps the batch on the
  * device; emit writes offsets[nq] ranks into hits (capacity in elements). */
 gg_status gg_intersect_count(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start,
@@ -204,6 +253,93 @@ gg_status gg_intersect_stranded_device(gg_index* idx, const uint32_t* d_chrom, c
                                        uint64_t* d_offsets, uint32_t* d_hits, uint64_t capacity,
                                        uint64_t* total_hits, void* stream);
 
+/* ---- multi-GPU: one grove over several B200s ------------------------------------------ */
+/* A gg_group owns one gg_index per GPU and the communication between them.  Two forms, same entry points:
+ *   single-process  gg_group_create(devices[], n): this process drives all listed GPUs (the C++ facade, gg_isec); data
+ *                   moves between them with peer copies over NVLink (cudaMemcpyPeerAsync), no communicator needed.
+ *   one process per GPU  gg_group_create_rank(device, rank, world, id): rank `rank` of `world` (torchrun, MPI); the
+ *                   handle owns an NCCL communicator created from the 128-byte unique id that rank 0 obtained from
+ *                   gg_group_unique_id and the launcher distributed.  libnccl.so.2 is loaded on first use (dlopen), so
+ *                   single-GPU users of this library do not need NCCL.
+ * Sharding (what the reference calls once per chromosome / once per query — grove_insert.ipp:160-172,
+ * grove_query.ipp:33-43 — spread over the GPUs):
+ *   GG_SHARD_REPLICATE  every GPU holds the whole index; a query batch is cut into contiguous slices.  No data-path
+ *                       exchange; the only collective is the all-gather of the per-rank hit totals (8 bytes per rank).
+ *   GG_SHARD_CHROM      chromosomes are bin-packed onto GPUs by interval count (LPT, gg_shard_assign); each GPU sorts /
+ *                       builds only its chromosomes; queries are partitioned by owner ON THE DEVICE (stable radix
+ *                       partition on the owner id carrying the original query index), exchanged all-to-all over
+ *                       NVLink (grouped ncclSend / ncclRecv, or peer copies), answered by the owner, and the hit lists
+ *                       travel back the same way and are put back in the original query order on the source GPU.
+ * Calls on one group are serialised by the caller; in the rank form every rank makes the same sequence of calls. */
+typedef struct gg_group gg_group;
+#define GG_SHARD_REPLICATE 0
+#define GG_SHARD_CHROM 1
+
+gg_status gg_group_create(gg_group** out, const int* devices, int n_devices);
+/* id128: 128 bytes (ncclUniqueId) */
+gg_status gg_group_unique_id(void* id128);
+gg_status gg_group_create_rank(gg_group** out, int device, int rank, int world, const void* id128);
+void gg_group_destroy(gg_group* g);
+const char* gg_group_last_error(const gg_group* g);
+int gg_group_world(const gg_group* g);
+/* the gg_index of local GPU i (single-process form: 0 .. n_devices-1; rank form: 0) — for gg_set_option / stats */
+gg_index* gg_group_index(gg_group* g, int i);
+
+/* owner[c] = rank holding chromosome c: longest-processing-time packing of the interval counts (largest chromosome first
+ * onto the least loaded rank; ties: lower chromosome id first, lower rank first).  Pure host arithmetic. */
+gg_status gg_shard_assign(const uint64_t* counts, uint32_t n_chrom, int world, uint32_t* owner);
+
+/* Build.  Single-process form: the arrays hold ALL intervals.  Rank form: GG_SHARD_REPLICATE: every rank passes all
+ * intervals; GG_SHARD_CHROM: every rank passes ITS PART of the input (any chromosomes — e.g. its slice of the BED file);
+ * records are routed to the owner of their chromosome over NVLink and each rank builds what it owns.
+ * rank_to_input (nullable): for each chain rank, the index of the interval in the global input (rank form: the
+ * concatenation of the ranks' inputs in rank order).  Single-process form: n entries, chromosome by chromosome in id
+ * order (the layout gg_index_build documents).  Rank form: the chromosomes this rank owns, in id order; *n_owned receives
+ * how many (the buffer must hold n_owned_capacity entries; GG_ERR_CAPACITY if it does not). */
+gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
+                         const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom, uint64_t* rank_to_input,
+                         size_t n_owned_capacity, size_t* n_owned);
+/* owner[c] of the last GG_SHARD_CHROM build (n_chrom entries; all zero for GG_SHARD_REPLICATE) */
+gg_status gg_group_owners(const gg_group* g, uint32_t* owner);
+
+typedef struct gg_group_stats {
+    uint64_t n_queries;       /* queries this process submitted in the last call */
+    uint64_t n_answered;      /* queries its GPUs answered (GG_SHARD_CHROM: the ones they own) */
+    uint64_t n_hits;          /* hits in this process's result */
+    uint64_t bytes_sent;      /* over NVLink, all exchanges of the call, summed over this process's GPUs */
+    uint64_t bytes_received;
+    double route_ms;          /* device time, max over this process's GPUs: owner lookup + stable partition + gather */
+    double exchange_ms;       /* queries to the owners */
+    double intersect_ms;      /* count -> scan -> emit on the owner */
+    double return_ms;         /* hit lists back to the source + re-ordering into the original query order */
+    double build_ms;          /* last gg_group_build: wall time of the slowest local GPU incl. routing of the records */
+} gg_group_stats;
+gg_status gg_group_get_stats(const gg_group* g, gg_group_stats* out);
+
+/* Batched intersect, HOST buffers.  Single-process form: the whole batch in, one CSR in original query order out
+ * (offsets[nq + 1] global, *hits = library-owned pinned buffer).  Rank form: every rank passes its slice of the batch
+ * and gets its slice's CSR (offsets local, starting at 0; *hit_base = hits of the ranks before it — the all-gather of
+ * totals).  coord_bytes 4 (u32 arrays) or 8 (u64). */
+gg_status gg_group_intersect_batch(gg_group* g, const uint32_t* q_chrom, const void* q_start, const void* q_end,
+                                   int coord_bytes, size_t nq, uint64_t* offsets, const uint32_t** hits, uint64_t* n_hits,
+                                   uint64_t* hit_base);
+/* Batched intersect, DEVICE buffers, rank form (one GPU per process; queries of this rank's slice resident on its GPU,
+ * global chromosome ids).  return_to_source != 0: the result is the slice's own CSR in original order, as above.
+ * return_to_source == 0 (GG_SHARD_CHROM): hit lists stay on the GPU that computed them — what a downstream kernel on the
+ * owner wants, and the only option when the hits of a batch exceed one GPU's memory share (cfg5: 1 B queries x 140 hits):
+ * the result describes the queries THIS rank answered, in arrival order, d_origin[i] = (source rank << 40) | index of the
+ * query in the source's slice.  Result buffers are library-owned device memory, valid until the next call. */
+typedef struct gg_group_device_result {
+    uint64_t n_queries;
+    uint64_t n_hits;
+    uint64_t hit_base;         /* return_to_source: hits of the ranks before this one; else 0 */
+    const uint64_t* d_offsets; /* n_queries + 1 */
+    const uint32_t* d_hits;
+    const uint64_t* d_origin;  /* n_queries entries when return_to_source == 0, else NULL */
+} gg_group_device_result;
+gg_status gg_group_intersect_device(gg_group* g, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                    int coord_bytes, size_t nq, int return_to_source, gg_group_device_result* out);
+
 /* ---- pinned host memory helpers ------------------------------------------------------------------ */
 gg_status gg_host_alloc(void** out, size_t bytes);
 void gg_host_free(void* p);
@@ -214,6 +350,9 @@ void gg_host_free(void* p);
  * path: 0 = count -> block scan -> emit_scan kernels, 1 = one kernel with a look-back scan, -1 = by batch size [default]:
  * one kernel up to 524288 queries, where launch latency dominates (10 k queries: 46 us against 66 us); its knobs:
  * "fused_ctas_per_sm", "fused_regs40"); "emit_walk" (ranks per walk step of emit_scan: 8 [default] or 16);
+ * "emit_tma" (pass 2 of the single-call path: 0 = intersect_emit_scan_kernel [default], 1 = intersect_emit_tma_kernel: TMA
+ * ring of the per-tile inputs + TMA bulk store of the hits, 2 = the same with 16-byte vector stores; the compact call
+ * always runs the TMA kernel);
  * "dense_emit" (dense-batch variants of pass 2: a 1024-hit stage per 32-query tile instead of 512, and a second emit kernel
  * for tiles with >= 2048 hits, per-lane stage segments and sector-sized stores: -1 = on once a batch / chunk on this
  * handle averaged >= 12 hits per query (stranded path: >= 32) [default], 0 = off, 1 = on);
@@ -221,7 +360,8 @@ void gg_host_free(void* p);
  * one query per thread, 1 = tiered tree kernel: TMA-staged windows / warp bracket / per-lane descent; for mode 1:
  * "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and "count_threads" (128..1024));
  * "count_ctas_per_sm", "emit_ctas_per_sm" (0 = occupancy API); "timing" (0/1: record CUDA events around the kernels of
- * the device-buffer calls for gg_last_batch_stats). */
+ * the device-buffer calls for gg_last_batch_stats); "compact_delta_bytes" (1, 2, 4: width the compact call starts with);
+ * "inject_alloc_failure" (debug: the k-th device allocation from now on fails, to drive the error paths). */
 gg_status gg_set_option(gg_index* idx, const char* key, int64_t value);
 
 #ifdef __cplusplus

@@ -134,7 +134,7 @@ def test_invalid_query_is_rejected(gg, oracle):
 @pytest.mark.parametrize("opt", [("chunk_queries", 4096), ("chunk_queries", 20_000), ("stage_bytes", 0),
                                  ("stage_bytes", 16384), ("stage_bytes", 196608), ("count_threads", 128),
                                  ("count_threads", 1024), ("count_mode", 1), ("count_mode", 0), ("count_mode", 2), ("fused_kernel", 1), ("fused_kernel", 0),
-                                 ("emit_walk", 16), ("host_mode", 1),
+                                 ("emit_walk", 16), ("emit_tma", 0), ("emit_tma", 1), ("emit_tma", 2), ("host_mode", 1),
                                  ("host_mode", 0), ("fused_regs40", 1), ("fused_ctas_per_sm", 1)])
 def test_options_do_not_change_results(gg, oracle, opt):
     rng = np.random.default_rng(31)
@@ -266,7 +266,7 @@ def test_fused_device_api_and_capacity(gg, oracle):
     assert np.array_equal(d_hits.cpu().numpy().view(np.uint32), exp_hits)
 
 
-@pytest.mark.parametrize("path", ["batch8", "batch16", "one_kernel"])
+@pytest.mark.parametrize("path", ["batch8", "batch16", "one_kernel", "tma_bulk", "tma_vec"])
 def test_single_call_paths_sorted_unaligned_and_ragged(gg, oracle, path):
     """The single-call device path (count, 4 consecutive queries per thread -> block scan -> emit_scan, with 8- and
     16-rank walk steps) and its one-kernel look-back form on: coordinate-sorted batches (finger search from the
@@ -279,6 +279,8 @@ def test_single_call_paths_sorted_unaligned_and_ragged(gg, oracle, path):
     idx = gg.DeviceIndex(0)
     idx.set_option("fused_kernel", 1 if path == "one_kernel" else 0)
     idx.set_option("emit_walk", 16 if path == "batch16" else 8)
+    # pass 2: the TMA kernel (ring of bulk loads in, bulk or vector stores out; emit_tma.cuh) or emit_scan (emit_scan.cuh)
+    idx.set_option("emit_tma", {"tma_bulk": 1, "tma_vec": 2}.get(path, 0))
     idx.build(chrom, start, end, 5)
     qc, qs, qe = random_queries(rng, 90_007, 5, span=2_000_000, max_len=400, extra_chrom=1)
     order = np.lexsort((qs, qc))
@@ -316,6 +318,98 @@ def test_single_call_paths_sorted_unaligned_and_ragged(gg, oracle, path):
                 assert np.array_equal(h.view(np.uint32)[:total], exp_hits[:total]) and (h[total:] == -1).all()
 
 
+@pytest.mark.parametrize("shape", ["bed", "nested", "dense"])
+def test_compact_result_form_decodes_to_the_same_csr(gg, oracle, shape):
+    """gg_intersect_batch_compact: {offset, hi slot} per query + 1/2/4-byte back-deltas per hit decode (gg_compact_expand,
+    gg_compact_rank / _count) to exactly the CSR of gg_intersect_batch.  bed: short intervals, 1-byte deltas; nested: long
+    intervals push deltas past 255 / 65535, the chunk is re-run one width up; dense: lists longer than the stage."""
+    import ctypes as C
+    rng = np.random.default_rng({"bed": 91, "nested": 92, "dense": 93}[shape])
+    if shape == "bed":
+        chrom, start, end = random_index(rng, 200_000, 24, span=2_000_000, max_len=3000)
+    elif shape == "nested":
+        chrom, start, end = random_index(rng, 300_000, 3, span=3_000_000, max_len=400, nested=True)
+        end[:3] = start[:3] + np.uint64(2_900_000)   # spans ~100 k ranks: needs 4-byte deltas
+    else:
+        n = 40_000
+        start = np.sort(rng.integers(0, 100_000, n)).astype(np.uint64)
+        end = start + rng.integers(1, 3000, n).astype(np.uint64)
+        chrom = np.zeros(n, np.uint32)
+    n_chrom = int(chrom.max()) + 1
+    idx = gg.DeviceIndex(0)
+    idx.set_option("chunk_queries", 8192)
+    idx.build(chrom, start, end, n_chrom)
+    span = int(end.max())
+    qc, qs, qe = random_queries(rng, 50_003, n_chrom, span=span, max_len=300, extra_chrom=1)
+    order = np.lexsort((qs, qc))
+    qc, qs, qe = qc[order], qs[order], qe[order]
+    exp_off, exp_hits = oracle_csr(chrom, start, end, n_chrom, qc, qs, qe)
+    for rep in range(2):  # second call: warm buffers, sticky delta width
+        off, hits = idx.intersect_batch_compact(qc, qs.astype(np.uint32), qe.astype(np.uint32), threads=1 + rep)
+        assert np.array_equal(off, exp_off) and np.array_equal(hits, exp_hits)
+    res = idx.last_compact
+    widths = {res.chunks[k].delta_bytes for k in range(res.n_chunks)}
+    assert widths <= {1, 2, 4} and res.n_chunks == -(-50_003 // 8192)
+    if shape == "bed":
+        assert widths == {1}
+    if shape == "nested":
+        assert max(widths) >= 2  # (some chunk met a delta past 255 and was re-run wider)
+    # element-wise decode helpers on a sample
+    L = idx._L
+    for q in rng.integers(0, len(qc), 300):
+        n = L.gg_compact_count(C.byref(res), int(q))
+        assert n == int(exp_off[q + 1] - exp_off[q])
+        got = [L.gg_compact_rank(C.byref(res), C.c_void_p(qc.ctypes.data), int(q), j) for j in range(n)]
+        assert got == exp_hits[int(exp_off[q]):int(exp_off[q + 1])].tolist()
+    # empty batch and invalid interval
+    off, hits = idx.intersect_batch_compact(qc[:0], qs[:0].astype(np.uint32), qe[:0].astype(np.uint32))
+    assert off.tolist() == [0] and len(hits) == 0
+    bad_s = qs.astype(np.uint32).copy()
+    bad_s[17] = np.uint32(qe[17] + 5)
+    with pytest.raises(gg.GGError) as ei:
+        idx.intersect_batch_compact(qc, bad_s, qe.astype(np.uint32))
+    assert ei.value.status == 4
+
+
+def test_tma_emit_many_blocks_per_warp(gg, oracle):
+    """intersect_emit_tma_kernel with a grid pinned to one CTA per SM: every warp owns many 128-query blocks, so the TMA
+    ring wraps and the block hop of its tile sequence runs (the default grid gives small batches one block per warp)."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(97)
+    chrom, start, end = random_index(rng, 150_000, 4, span=2_000_000, max_len=3000, nested=True)
+    exp = None
+    for nbytes in (4, 8):
+        for mode, cps in ((0, 0), (1, 1), (2, 1), (1, 0)):
+            idx = gg.DeviceIndex(0)
+            idx.set_option("fused_kernel", 0)
+            idx.set_option("emit_tma", mode)
+            idx.set_option("emit_ctas_per_sm", cps)
+            idx.build(chrom, start, end, 4)
+            qc, qs, qe = random_queries(np.random.default_rng(98), 1_300_021, 4, span=2_000_000, max_len=300)
+            order = np.lexsort((qs, qc))
+            qc, qs, qe = qc[order], qs[order], qe[order]
+            dev = torch.device("cuda:0")
+            dt, tt = (np.uint32, torch.int32) if nbytes == 4 else (np.uint64, torch.int64)
+            d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
+            d_s = torch.from_numpy(qs.astype(dt).view(np.int32 if nbytes == 4 else np.int64)).to(dev)
+            d_e = torch.from_numpy(qe.astype(dt).view(np.int32 if nbytes == 4 else np.int64)).to(dev)
+            nq = len(qc)
+            d_off = torch.zeros(nq + 1, dtype=torch.int64, device=dev)
+            st = torch.cuda.current_stream().cuda_stream
+            tot = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nbytes, nq, d_off.data_ptr(), st, sync_total=True)
+            d_hits = torch.full((tot + 8,), -1, dtype=torch.int32, device=dev)
+            d_off.zero_()
+            got = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), nbytes, nq, d_off.data_ptr(), d_hits.data_ptr(), tot, st, sync_total=True)
+            assert got == tot
+            if exp is None:  # the emit_scan result, itself checked against the oracle on a prefix
+                exp = (d_off.cpu().numpy(), d_hits.cpu().numpy())
+                o_off, o_hits = oracle_csr(chrom, start, end, 4, qc[:20_000], qs[:20_000], qe[:20_000])
+                assert np.array_equal(exp[0][:20_001].view(np.uint64), o_off)
+                assert np.array_equal(exp[1][:len(o_hits)].view(np.uint32), o_hits)
+            else:
+                assert np.array_equal(d_off.cpu().numpy(), exp[0]) and np.array_equal(d_hits.cpu().numpy(), exp[1])
+
+
 def test_fused_host_pipeline_regrows_on_dense_chunks(gg, oracle):
     """Host-buffer call, fused mode: chunks whose hit count exceeds the running estimate are re-run exactly;
     very long hit lists (> 512 per warp tile) take the direct-to-global walk."""
@@ -346,6 +440,24 @@ def test_many_contigs_offset_table_outside_shared_memory(gg, oracle):
     idx = gg.DeviceIndex(0)
     idx.build(chrom, start, end, n_chrom)
     _check(idx, chrom, start, end, n_chrom, random_queries(rng, 60_000, n_chrom, span=50_000))
+
+
+@pytest.mark.parametrize("host_mode", [0, 1])
+def test_scaffold_level_assembly_two_phase(gg, oracle, host_mode):
+    # 60 000 contigs x 2 levels = 480 KB of level offsets: more than any CTA's shared memory.  The two-phase API
+    # (gg_intersect_count / _emit, host_mode 1) must read the table through L1 like the single-call path does.
+    rng = np.random.default_rng(59)
+    n_chrom = 60_000
+    chrom, start, end = random_index(rng, 300_000, n_chrom, span=20_000)
+    chrom[:3000] = 11  # one contig deep enough for a second level
+    idx = gg.DeviceIndex(0)
+    idx.set_option("host_mode", host_mode)
+    idx.build(chrom, start, end, n_chrom)
+    q = random_queries(rng, 50_000, n_chrom, span=20_000)
+    _check(idx, chrom, start, end, n_chrom, q)
+    _check(idx, chrom, start, end, n_chrom, q, two_phase=True)
+    idx.set_option("count_mode", 1)  # the TMA-window count kernel keeps the table in shared memory: falls back, same results
+    _check(idx, chrom, start, end, n_chrom, q, two_phase=True)
 
 
 def test_long_nested_intervals_use_max_end_pruning(gg, oracle):

@@ -177,3 +177,32 @@ def test_gpu_stranded_errors_and_device_buffers():
     idx.build(np.zeros(3, np.uint32), s, e, 1)  # a rebuild drops the strands
     with pytest.raises(GGError):
         idx.intersect_batch_stranded(z, [0], [5], b"+")
+
+
+@pytest.mark.gpu
+def test_set_strands_failure_leaves_no_strands():
+    """A device allocation that fails inside gg_index_set_strands must fail the call and leave the handle without
+    strand records (the stranded entry points then refuse to run) — ADVICE r1: the error used to be swallowed."""
+    import genogrove_b200 as gg
+    rng = np.random.default_rng(3)
+    n = 5000
+    start = np.sort(rng.integers(0, 100_000, n)).astype(np.uint64)
+    end = start + rng.integers(1, 500, n).astype(np.uint64)
+    idx = gg.DeviceIndex(0)
+    idx.build(np.zeros(n, np.uint32), start, end, 1)
+    strands = np.frombuffer(b"+-.*", dtype=np.uint8)[rng.integers(0, 4, n)]
+    q = (np.zeros(10, np.uint32), start[:10], end[:10], strands[:10])
+    idx.set_strands(strands)
+    idx.intersect_batch_stranded(*q)
+    for k in (1, 2, 3, 5):  # the k-th allocation of the call fails
+        idx.set_option("inject_alloc_failure", k)
+        with pytest.raises(gg.GGError) as ei:
+            idx.set_strands(strands)
+        assert ei.value.status in (2, 3)
+        idx.set_option("inject_alloc_failure", 0)
+        with pytest.raises(gg.GGError) as ei:
+            idx.intersect_batch_stranded(*q)
+        assert ei.value.status == 5  # GG_ERR_NOT_BUILT: no strands attached
+    idx.set_strands(strands)
+    off, hits = idx.intersect_batch_stranded(*q)
+    assert off[-1] >= 10
