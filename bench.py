@@ -10,14 +10,20 @@ A step = one pass of the hot path over the rank's 100M-query batch through the s
 (fused.cuh), --two-phase the count / scan / emit kernels of the two-phase API.
 
   value : whole-job queries/s with queries and results resident in HBM (device-buffer C ABI).
-  e2e   : the same metric through the host-buffer C ABI call (gg_intersect_batch, u64 coordinates as the
-          reference's interval uses), pinned host buffers, H2D + D2H inside the timed region.
+  e2e   : the same metric through the host-buffer C ABI call with pinned host buffers, H2D + D2H inside the timed
+          region: gg_intersect_batch_compact (u32 coordinates up, 8 B per query + a 1-byte back-delta per hit down — every
+          hit is delivered; e2e.full_csr is gg_intersect_batch_u32 with u64 offsets + u32 ranks, e2e.u64_api the round-1
+          call with u64 coordinates); e2e.copy_ceiling = the same bytes moved by bare concurrent cudaMemcpyAsync.
+  strong / chrom_shard (N > 1): the same 100M-query batch cut into N slices (BASELINE cfg4 as written), and the grove
+          sharded by chromosome with queries routed to the owner over NVLink (gg_group_*, rank form, NCCL).
+  --mode cfg5 : BASELINE configs[4] — 200M-interval chromosome-sharded build + 1B routed queries over N GPUs.
   --impl reference : the reference's own CPU intersect loop (oracle/_ref = unmodified genogrove) on this
           box's host cores, all threads, on a bounded sample of the same workload.
 """
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -54,6 +60,12 @@ def parse_args():
     ap.add_argument("--one-kernel", action="store_true", help="single-call path as ONE kernel (decoupled look-back scan)")
     ap.add_argument("--regs40", action="store_true", help="40-register build of the one-kernel form")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--mode", default="cfg4", choices=["cfg4", "cfg5"],
+                    help="cfg5: chromosome-sharded 200M-interval build + 1B-query batch over --gpus ranks (BASELINE configs[4])")
+    ap.add_argument("--cfg5-intervals", type=int, default=200_000_000)
+    ap.add_argument("--cfg5-queries", type=int, default=1_000_000_000)
+    ap.add_argument("--cfg5-chunk", type=int, default=16_000_000, help="queries per rank and routed call")
+    ap.add_argument("--no-multi", action="store_true", help="skip the strong-scaling / chromosome-sharded side measurements (N > 1)")
     ap.add_argument("--emit-tma", type=int, default=-1, help="pass 2 kernel: 1 TMA ring + bulk store [default], 2 TMA ring + vector stores, 0 emit_scan")
     ap.add_argument("--emit-ctas-per-sm", type=int, default=0)
     return ap.parse_args()
@@ -68,6 +80,7 @@ def workload_config(args, world):
         "query_order": "shuffled" if args.shuffled else "sorted",
         "parallelism": f"index replicated, query batch sharded x{world}",
         "l2_policy": "inputs+outputs per step (>4 GB) exceed the 126 MB L2; no flush needed",
+        "scaling_note": "headline: weak (100M queries per GPU); 'strong' holds the fixed 100M-query batch cut into N slices",
     }
 
 
@@ -177,6 +190,233 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(out))
 
 
+def timed_ms(torch, fn, n, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / n
+
+
+def copy_ceiling(torch, dev, h2d_bytes, d2h_bytes, barrier, dist, reps=3):
+    """Bare concurrent pinned copies of the e2e call's byte counts on two streams (all ranks at once): the box's ceiling for
+    that result form.  Returns per-rank GB/s both ways and the queries/s it would allow (filled in by the caller's ratio)."""
+    try:
+        up_h = torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory()
+        dn_h = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
+        up_d = torch.empty(h2d_bytes, dtype=torch.uint8, device=dev)
+        dn_d = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
+    except Exception as ex:  # noqa: BLE001
+        return {"error": repr(ex)}
+    s_up, s_dn = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    best = None
+    for _ in range(reps):
+        barrier()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(s_up):
+            up_d.copy_(up_h, non_blocking=True)
+        with torch.cuda.stream(s_dn):
+            dn_h.copy_(dn_d, non_blocking=True)
+        s_up.synchronize()
+        s_dn.synchronize()
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    t = torch.tensor([best], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt = float(t.item())
+    world = dist.get_world_size() if dist is not None else 1
+    nq = h2d_bytes // 12
+    return {"ms": dt * 1e3, "h2d_gbs_per_gpu": h2d_bytes / dt / 1e9, "d2h_gbs_per_gpu": d2h_bytes / dt / 1e9,
+            "aggregate_gbs": (h2d_bytes + d2h_bytes) * world / dt / 1e9, "queries_per_sec": nq * world / dt,
+            "note": "concurrent cudaMemcpyAsync H2D + D2H of exactly the e2e call's bytes, pinned buffers, max over ranks"}
+
+
+def make_group(torch, dist, dev, rank, world):
+    """gg_group in the rank form: the NCCL unique id travels over torch.distributed (plumbing), the communicator is the library's."""
+    from genogrove_b200 import DeviceGroup
+    idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        idt.copy_(torch.frombuffer(bytearray(DeviceGroup.unique_id()), dtype=torch.uint8))
+    if world > 1:
+        dist.broadcast(idt, 0)
+    return DeviceGroup.from_rank(dev.index, rank, world, bytes(idt.cpu().numpy().tobytes()))
+
+
+def chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e, nq, steps=5):
+    """The cfg4 grove sharded by chromosome over the N ranks (gg_group_*, GG_SHARD_CHROM): every rank passes its slice of the
+    interval input (records routed to their owners), then its own 100M-query batch is routed to the owners and answered there
+    (hit lists stay on the owner: return_to_source = 0), and — second number — returned to the source in original order."""
+    from genogrove_b200 import SHARD_CHROM
+    grp = make_group(torch, dist, dev, rank, world)
+    lo, hi = rank * len(c) // world, (rank + 1) * len(c) // world
+    grp.build(SHARD_CHROM, c[lo:hi], s[lo:hi], e[lo:hi], 24, want_perm=False)
+    grp.build(SHARD_CHROM, c[lo:hi], s[lo:hi], e[lo:hi], 24, want_perm=False)  # warm buffers; report the second
+    build_ms = torch.tensor([grp.stats().build_ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(build_ms, op=dist.ReduceOp.MAX)
+    out = {"build_ms": float(build_ms.item()), "intervals": int(len(c)),
+           "owners": grp.owners(24).tolist()}
+    for back in (False, True):
+        def step():
+            return grp.intersect_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, return_to_source=back)
+        for _ in range(2):
+            step()
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            res = step()
+        torch.cuda.synchronize()
+        dt = torch.tensor([(time.perf_counter() - t0) / steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        st = grp.stats()
+        per = torch.tensor([st.n_answered, st.n_hits, st.bytes_sent, st.route_ms, st.exchange_ms, st.intersect_ms, st.return_ms],
+                           dtype=torch.float64, device=dev)
+        allp = [torch.zeros_like(per) for _ in range(world)]
+        dist.all_gather(allp, per)
+        allp = torch.stack(allp).cpu().numpy()
+        hits_job = float(allp[:, 1].sum())
+        out["results_on_owner" if not back else "returned_to_source"] = {
+            "ms_per_step": float(dt.item()) * 1e3, "queries_per_sec": nq * world / float(dt.item()),
+            "hit_pairs_per_sec": hits_job / float(dt.item()),
+            "answered_imbalance_max_over_mean": float(allp[:, 0].max() / max(allp[:, 0].mean(), 1.0)),
+            "nvlink_bytes_sent_per_step": float(allp[:, 2].sum()),
+            "phase_ms_max_over_ranks": {"route": float(allp[:, 3].max()), "exchange": float(allp[:, 4].max()),
+                                        "intersect": float(allp[:, 5].max()), "return": float(allp[:, 6].max())},
+            "timer": "host wall clock around the synchronising C ABI call, max over ranks (the call reads count matrices and hit totals back)"}
+        del res
+    out["note"] = ("gg_group rank form over NCCL: LPT chromosome owners, device-side stable partition by owner, all-to-all-v of "
+                   "(chrom, start, end) as grouped ncclSend/ncclRecv, gg_intersect_fused_device on the owner")
+    grp.close()
+    return out
+
+
+def run_cfg5(args, rank, local_rank, world):
+    """BASELINE configs[4]: bulk build of 200M intervals + 1B-query batch, chromosome-sharded over the N ranks.
+    Every rank holds 1/N of the (unsorted) interval input and 1/N of the query batch — as if each had read its slice of the
+    files — and everything else happens behind the C ABI (gg_group_*, rank form): records are routed to the owner of their
+    chromosome over NVLink and each rank sorts / builds what it owns; queries are partitioned by owner on the device,
+    exchanged, answered on the owner, and the hit lists stay there (1B queries x ~140 hits do not fit anywhere else)."""
+    import torch
+    import torch.distributed as dist
+    from genogrove_b200 import SHARD_CHROM, synth
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29517")
+    dist.init_process_group("nccl", device_id=dev, rank=rank, world_size=world)
+    grp = make_group(torch, dist, dev, rank, world)
+    N, Q, chunk = args.cfg5_intervals, args.cfg5_queries, args.cfg5_chunk
+    c, s, e = synth.hg38_intervals_part(N, rank, world, 42)
+    dist.barrier()
+    t0 = time.perf_counter()
+    grp.build(SHARD_CHROM, c, s, e, 24, want_perm=False)
+    t_build = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(t_build, op=dist.ReduceOp.MAX)
+    dist.barrier()
+    t0 = time.perf_counter()
+    grp.build(SHARD_CHROM, c, s, e, 24, want_perm=False)  # second build: warm allocations (both reported)
+    t_build2 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(t_build2, op=dist.ReduceOp.MAX)
+    ist = IndexStats_of(grp)
+    owned = torch.tensor([float(grp.n_owned), ist.sort_ms, ist.levels_ms, ist.total_ms], dtype=torch.float64, device=dev)
+    owned_all = [torch.zeros_like(owned) for _ in range(world)]
+    dist.all_gather(owned_all, owned)
+    owned_all = torch.stack(owned_all).cpu().numpy()
+    del c, s, e
+
+    lo, hi = rank * Q // world, (rank + 1) * Q // world
+    per_rank_max = -(-Q // world)
+    n_chunks = -(-per_rank_max // chunk)
+    times, answered, hits, sent = [], 0, 0, 0
+    phase = np.zeros(4)
+    for k in range(n_chunks):
+        a, b = min(lo + k * chunk, hi), min(lo + (k + 1) * chunk, hi)
+        m = b - a
+        qc, qs, qe = synth.hg38_queries(m, 150, 1000 + rank * 4096 + k, True) if m else (np.zeros(0, np.uint32),) * 3
+        d_c = torch.from_numpy(np.ascontiguousarray(qc).view(np.int32)).to(dev)
+        d_s = torch.from_numpy(qs.astype(np.uint32).view(np.int32)).to(dev)
+        d_e = torch.from_numpy(qe.astype(np.uint32).view(np.int32)).to(dev)
+        reps = 2 if k == 0 else 1  # first chunk once untimed: buffer growth
+        for r_ in range(reps):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            res = grp.intersect_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, m, return_to_source=False)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+        times.append(dt)
+        st = grp.stats()
+        answered += int(res.n_queries)
+        hits += int(res.n_hits)
+        sent += int(st.bytes_sent)
+        phase += np.array([st.route_ms, st.exchange_ms, st.intersect_ms, st.return_ms])
+        del d_c, d_s, d_e
+    t = torch.tensor(times, dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    job_s = float(t.sum().item())
+    tot = torch.tensor([float(answered), float(hits), float(sent)] + phase.tolist(), dtype=torch.float64, device=dev)
+    tot_all = [torch.zeros_like(tot) for _ in range(world)]
+    dist.all_gather(tot_all, tot)
+    tot_all = torch.stack(tot_all).cpu().numpy()
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        H = float(tot_all[:, 1].sum())
+        bytes_path = 12 * Q + 8 * (Q + world) + 4 * H
+        out = {"metric": METRIC, "value": Q / job_s, "unit": UNIT, "n_gpus": world, "steps": 1, "warmup": 1,
+               "ms_per_step": job_s * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32",
+               "data": "synthetic", "hit_pairs_per_sec": H / job_s, "hits_per_query": H / Q,
+               "config": {"workload": "cfg5: bulk build of %d hg38-shaped intervals (unsorted input, 1/N per rank) + %d 150bp queries, "
+                                      "chromosome-sharded over %d B200 (LPT on interval count), hit lists stay on the owner" % (N, Q, world),
+                          "intervals": N, "queries": Q, "chunk_queries_per_rank": chunk, "chunks": n_chunks,
+                          "parallelism": f"chromosome-sharded x{world} (gg_group rank form, NCCL)"},
+               "build": {"seconds_first": float(t_build.item()), "seconds": float(t_build2.item()),
+                         "intervals_per_sec": N / float(t_build2.item()),
+                         "algorithmic_bytes": 32.3 * N, "frac_of_hbm_peak": 32.3 * N / float(t_build2.item()) / 1e9 / (peak * world),
+                         "per_rank_owned_intervals": owned_all[:, 0].tolist(),
+                         "per_rank_device_ms": {"sort": owned_all[:, 1].tolist(), "levels": owned_all[:, 2].tolist(),
+                                                "build_total": owned_all[:, 3].tolist()},
+                         "note": "wall time of gg_group_build, max over ranks: H2D of the rank's records, routing over NVLink, "
+                                 "device sort + level construction of the owned chromosomes"},
+               "per_rank": {"answered_queries": tot_all[:, 0].tolist(), "hits": tot_all[:, 1].tolist(),
+                            "imbalance_answered_max_over_mean": float(tot_all[:, 0].max() / tot_all[:, 0].mean()),
+                            "imbalance_hits_max_over_mean": float(tot_all[:, 1].max() / max(tot_all[:, 1].mean(), 1.0))},
+               "nvlink_bytes_sent_total": float(tot_all[:, 2].sum()),
+               "nvlink_bytes_per_query": float(tot_all[:, 2].sum()) / Q,
+               "phase_ms_sum_over_chunks_max_over_ranks": {"route": float(tot_all[:, 3].max()), "exchange": float(tot_all[:, 4].max()),
+                                                           "intersect": float(tot_all[:, 5].max()), "return": float(tot_all[:, 6].max())},
+               "roofline": {"bound": "hbm", "kernel": "whole path (route + exchange + count + scan + emit)", "achieved": bytes_path / job_s / 1e9,
+                            "peak": peak * world, "unit": "GB/s", "frac": bytes_path / job_s / 1e9 / (peak * world), "traffic": None,
+                            "algorithmic_bytes": bytes_path},
+               "timer": "host wall clock around each synchronising gg_group_intersect_device call (queries resident on the source GPU), "
+                        "max over ranks per chunk, summed over chunks",
+               "gpu_launches": None}
+        print(json.dumps(out))
+    grp.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def IndexStats_of(grp):
+    """gg_index_stats of the group's local index (ctypes)."""
+    from genogrove_b200._lib import IndexStats
+    st = IndexStats()
+    L = grp._L
+    L.gg_index_get_stats(L.gg_group_index(grp._h, 0), ctypes.byref(st))
+    return st
+
+
 # ----------------------------------------------------------------------------------------- B200 arm
 def main():
     args = parse_args()
@@ -185,6 +425,9 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
+        return
+    if args.mode == "cfg5":
+        run_cfg5(args, rank, local_rank, world)
         return
 
     import torch
@@ -324,12 +567,21 @@ def main():
             traffic = tj[key]["dram_bytes_per_launch"]
     except Exception:
         pass
-    achieved = dom_bytes / (dom_ms / 1e3) / 1e9
+    # achieved / frac: SURVEY §8(d)'s ALGORITHMIC bytes of the path (12 Q read + 8 (Q + 1) + 4 H written, every datum once)
+    # over the dominant kernel's launch time.  What that kernel itself moves — including the cnt / hi scratch round trip
+    # and the second read of chrom / start that the two-pass design adds — is reported separately as kernel_bytes.
+    achieved = bytes_path / (dom_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_kind,
-                "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kernel_ms,
+                "algorithmic_bytes_per_launch": bytes_path, "kernel_bytes_per_launch": dom_bytes,
+                "kernel_bytes_gbs": dom_bytes / (dom_ms / 1e3) / 1e9, "kernel_ms": kernel_ms,
                 "path_achieved_gbs": bytes_path / (ms_per_step / 1e3) / 1e9,
-                "path_frac": bytes_path / (ms_per_step / 1e3) / 1e9 / peak}
+                "path_frac": bytes_path / (ms_per_step / 1e3) / 1e9 / peak,
+                "build": {"algorithmic_bytes": 32.3 * ist.n_intervals, "sort_ms": ist.sort_ms, "levels_ms": ist.levels_ms,
+                          "device_ms": ist.sort_ms + ist.levels_ms,
+                          "achieved_gbs": 32.3 * ist.n_intervals / ((ist.sort_ms + ist.levels_ms) / 1e3) / 1e9,
+                          "frac": 32.3 * ist.n_intervals / ((ist.sort_ms + ist.levels_ms) / 1e3) / 1e9 / peak,
+                          "note": "gg_index_build device time (sorts + level construction) over SURVEY 8(d)'s 32.3 B per interval"}}
 
     # ---- side measurements (not the headline): the two other query kinds on the same index and batch, device-resident
     extras = None
@@ -376,35 +628,134 @@ def main():
                                "strands": "index: uniform over + - . ; queries: uniform over + -"},
                   "note": "per-rank device time, same index and query batch as the headline; steps=%d" % ex_steps}
 
-    # ---- e2e: host-buffer C ABI call (u64 coordinates, pinned buffers), H2D + D2H inside the timed region
+    # ---- side measurements that need the headline buffers: the shuffled batch, strong scaling, the chromosome-sharded grove
+    shuffled = None
+    if not args.no_extras and not args.shuffled:
+        perm_t = torch.randperm(nq, device=dev)
+        s_c, s_s, s_e = d_c[perm_t].contiguous(), d_s[perm_t].contiguous(), d_e[perm_t].contiguous()
+        del perm_t
+
+        def shuf_step():
+            idx.fused_device(s_c.data_ptr(), s_s.data_ptr(), s_e.data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(),
+                             d_hits.numel(), stream, sync_total=True)
+
+        sh_ms = timed_ms(torch, shuf_step, 5)
+        shuffled = {"ms_per_step": sh_ms, "queries_per_sec": nq * world / (sh_ms / 1e3),
+                    "path_frac": bytes_path / (sh_ms / 1e3) / 1e9 / peak,
+                    "note": "the same 100M queries per GPU in random order (SURVEY 8(d) lists both orders); per-rank device time"}
+        del s_c, s_s, s_e
+
+    strong = None
+    if world > 1 and not args.no_multi:
+        # BASELINE cfg4 as written: ONE 100M-query batch (rank 0's) cut into N contiguous slices, index replicated
+        gc_, gs_, ge_ = synth.hg38_queries(args.queries, 150, 43, not args.shuffled)
+        lo, hi = shard.query_shard(len(gc_), rank, world)
+        m = hi - lo
+        t_c = torch.from_numpy(gc_[lo:hi].view(np.int32)).to(dev)
+        t_s = torch.from_numpy(gs_[lo:hi].astype(np.uint32).view(np.int32)).to(dev)
+        t_e = torch.from_numpy(ge_[lo:hi].astype(np.uint32).view(np.int32)).to(dev)
+        del gc_, gs_, ge_
+
+        def strong_step():
+            idx.fused_device(t_c.data_ptr(), t_s.data_ptr(), t_e.data_ptr(), 4, m, d_off.data_ptr(), d_hits.data_ptr(),
+                             d_hits.numel(), stream, sync_total=True)
+            d_tot.copy_(d_off[m:m + 1])
+            dist.all_gather_into_tensor(d_all, d_tot)  # global CSR base of the slice
+
+        for _ in range(3):
+            strong_step()
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(args.steps):
+            strong_step()
+        a1.record()
+        barrier()
+        t_st = torch.tensor([a0.elapsed_time(a1) / args.steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t_st, op=dist.ReduceOp.MAX)
+        strong = {"scaling": "strong", "queries_total": int(args.queries), "queries_per_gpu": m,
+                  "ms_per_step": float(t_st.item()), "queries_per_sec": args.queries / (float(t_st.item()) / 1e3),
+                  "note": "one 100M-query cfg4 batch cut into N contiguous slices, index replicated; device time, max over ranks"}
+        del t_c, t_s, t_e
+
+    chrom_shard = None
+    if world > 1 and not args.no_multi:
+        chrom_shard = chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e, nq)
+
+    # ---- e2e: host-buffer C ABI calls with pinned buffers, H2D + D2H inside the timed region
     e2e = None
     if not args.no_e2e:
-        p_c, p_s, p_e = PinnedArray(nq, np.uint32), PinnedArray(nq, np.uint64), PinnedArray(nq, np.uint64)
-        p_off = PinnedArray(nq + 1, np.uint64)
-        p_c.array[:], p_s.array[:], p_e.array[:] = qc, qs, qe
-        del d_hits
+        del d_hits, d_off
         torch.cuda.empty_cache()
+        p_c, p_s32, p_e32 = PinnedArray(nq, np.uint32), PinnedArray(nq, np.uint32), PinnedArray(nq, np.uint32)
+        p_c.array[:], p_s32.array[:], p_e32.array[:] = qc, qs, qe
 
-        def e2e_step():
-            off, hits = idx.intersect_batch(p_c.array, p_s.array, p_e.array, offsets_out=p_off.array, copy_hits=False)
+        def host_timed(fn):
+            fn()  # warm-up: grows the pinned result buffers and the pipeline slots
+            fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.e2e_steps):
+                h = fn()
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) / args.e2e_steps
+            assert h == total, (h, total)
+            t_e = torch.tensor([dt], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+            return float(t_e.item())
+
+        cres = {}
+
+        def compact_step():
+            cres["r"] = idx.intersect_batch_compact(p_c.array, p_s32.array, p_e32.array, expand=False)
+            return int(cres["r"].n_hits)
+
+        dt_c = host_timed(compact_step)
+        r = cres["r"]
+        d2h_c = int(nq * 8 + r.delta_bytes_total)
+        widths = sorted({int(r.chunks[k].delta_bytes) for k in range(r.n_chunks)})
+        # the same bytes moved by bare concurrent copies on two streams: what the link allows for this result form
+        ceiling = copy_ceiling(torch, dev, nq * 12, d2h_c, barrier, dist if world > 1 else None)
+        # host-side decode into the plain CSR, for callers that want it (not needed to read hits: gg_compact_rank)
+        off_x, hits_x = np.empty(nq + 1, np.uint64), np.empty(total, np.uint32)
+        t0 = time.perf_counter()
+        st = idx._L.gg_compact_expand(ctypes.byref(r), ctypes.c_void_p(p_c.array.ctypes.data), ctypes.c_void_p(off_x.ctypes.data),
+                                      ctypes.c_void_p(hits_x.ctypes.data), 0)
+        expand_s = time.perf_counter() - t0
+        assert st == 0 and int(off_x[-1]) == total
+        del off_x, hits_x
+
+        p_off = PinnedArray(nq + 1, np.uint64)
+
+        def full_step():
+            off, _ = idx.intersect_batch(p_c.array, p_s32.array, p_e32.array, offsets_out=p_off.array, copy_hits=False)
             return int(off[-1])
 
-        e2e_step()  # warm-up: grows the pinned result buffer and the pipeline slots
-        e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            h = e2e_step()
-        torch.cuda.synchronize()
-        dt = (time.perf_counter() - t0) / args.e2e_steps
-        assert h == total
-        t_e = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-        e2e = {"value": job_q / float(t_e.item()), "unit": UNIT, "h2d_bytes_per_step": int(nq * 20),
-               "d2h_bytes_per_step": int((nq + 1) * 8 + total * 4), "ms_per_step": float(t_e.item()) * 1e3,
-               "steps": args.e2e_steps, "api": "gg_intersect_batch (u64 coordinates, pinned host buffers)",
-               "timer": "host wall clock around the blocking C ABI call, max over ranks"}
+        dt_f = host_timed(full_step)
+        e2e = {"value": job_q / dt_c, "unit": UNIT, "h2d_bytes_per_step": int(nq * 12), "d2h_bytes_per_step": d2h_c,
+               "ms_per_step": dt_c * 1e3, "steps": args.e2e_steps,
+               "api": "gg_intersect_batch_compact (u32 coordinates; per query {offset, hi slot}, per hit a back-delta of "
+                      + "/".join(str(w) for w in widths) + " byte(s); pinned host buffers)",
+               "timer": "host wall clock around the blocking C ABI call, max over ranks",
+               "copy_ceiling": ceiling,
+               "frac_of_copy_ceiling": (job_q / dt_c) / ceiling["queries_per_sec"] if ceiling else None,
+               "host_expand_to_csr_ms": expand_s * 1e3,
+               "full_csr": {"value": job_q / dt_f, "ms_per_step": dt_f * 1e3, "h2d_bytes_per_step": int(nq * 12),
+                            "d2h_bytes_per_step": int((nq + 1) * 8 + total * 4),
+                            "api": "gg_intersect_batch_u32 (u64 offsets + u32 ranks)"}}
+        if world == 1:  # the round-1 e2e call (u64 coordinates up), kept for comparison
+            p_s, p_e = PinnedArray(nq, np.uint64), PinnedArray(nq, np.uint64)
+            p_s.array[:], p_e.array[:] = qs, qe
+
+            def u64_step():
+                off, _ = idx.intersect_batch(p_c.array, p_s.array, p_e.array, offsets_out=p_off.array, copy_hits=False)
+                return int(off[-1])
+
+            dt_u = host_timed(u64_step)
+            e2e["u64_api"] = {"value": job_q / dt_u, "ms_per_step": dt_u * 1e3, "h2d_bytes_per_step": int(nq * 20),
+                              "d2h_bytes_per_step": int((nq + 1) * 8 + total * 4), "api": "gg_intersect_batch (u64 coordinates)"}
+            del p_s, p_e
 
     # ---- CPU baseline beside it (rank 0, N=1 only): the unmodified reference on a bounded sample
     cpu = None
@@ -422,7 +773,8 @@ def main():
                "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
                "config": workload_config(args, world), "hit_pairs_per_sec": job_hits / (ms_per_step / 1e3),
                "hits_per_query": job_hits / job_q, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
-               "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "extras": extras,
+               "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "extras": extras, "shuffled": shuffled,
+               "strong": strong, "chrom_shard": chrom_shard,
                "index": {"levels": ist.n_levels, "fanout": ist.fanout, "staged_levels": ist.staged_levels,
                          "coord_bytes": ist.coord_bytes, "device_mb": ist.device_bytes / 1e6,
                          "build_sort_ms": ist.sort_ms, "build_levels_ms": ist.levels_ms, "build_total_ms": ist.total_ms}}

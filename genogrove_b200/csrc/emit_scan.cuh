@@ -43,6 +43,14 @@ constexpr uint32_t kDenseSeg = kEmitStage / 32;  // stage entries per lane (16)
 // (skewed lists: a few long ones among short ones — GENCODE-shaped data — gain nothing from the segment flush);
 // from 64 hits per query on average the 8x saving in L2 write transactions wins (cfg5: 201 -> 89 ms).
 constexpr uint32_t kDenseMin = 2048;
+// Between the stage size and kDenseMin the choice depends on the SHAPE of the tile: 32 lists of similar length (a uniformly
+// dense index: 16-64 hits per query) still want the segment flush — the direct walk writes them at 1e10 hits/s, measured on
+// a 50 M-interval grove — while one long list among short ones does not.  Both kernels evaluate this same predicate on the
+// tile's 32 counts, so exactly one of them writes the tile.
+__device__ __forceinline__ bool dense_tile(uint64_t wtotal, uint32_t cmax, uint32_t stage_entries) {
+    if (wtotal <= stage_entries || wtotal >= (1ull << 31)) return false;
+    return wtotal >= kDenseMin || static_cast<uint64_t>(cmax) * 4u <= wtotal;
+}
 
 template <typename C, bool kStrand>
 __device__ __forceinline__ void emit_dense_tile(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
@@ -198,7 +206,8 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
             const uint32_t c = in ? cnt_in[q] : 0u;
             // exclusive warp scan of the 32 counts: 32-bit when the sum cannot overflow, else 64-bit
             uint64_t excl, wtotal;
-            if (__reduce_max_sync(0xffffffffu, c) < (1u << 27)) {
+            const uint32_t cmax = __reduce_max_sync(0xffffffffu, c);
+            if (cmax < (1u << 27)) {
                 uint32_t inc = c;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
@@ -261,7 +270,7 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                         if (wbase + i < capacity) hits[wbase + i] = lds32(sa);
                 }
                 __syncwarp();
-            } else if (kDense && wtotal >= kDenseMin && wtotal < (1ull << 31)) {
+            } else if (kDense && dense_tile(wtotal, cmax, kStage)) {
                 // a dense tile: intersect_emit_dense_kernel finds it from the per-tile totals of the count pass and writes it
             } else if (c != 0 && wbase + excl + c <= capacity) {  // too large for the stage but not dense: straight to global memory
                 if (kStrand)
@@ -284,7 +293,8 @@ __global__ void __launch_bounds__(kQueryThreads, 5)
 intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
                             const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
                             const uint64_t* __restrict__ block_prefix, const uint32_t* __restrict__ tile_total,
-                            uint32_t blk_q, uint32_t* __restrict__ hits, uint64_t capacity, StrandArgs sa) {
+                            uint32_t blk_q, uint32_t* __restrict__ hits, uint64_t capacity, StrandArgs sa,
+                            uint32_t stage_entries /* of the intersect_emit_scan_kernel build that ran before */) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStageWords = kEmitStage + kEmitScanSlack;
     constexpr uint32_t kWarps = kQueryThreads / 32;
@@ -299,7 +309,7 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
     // 32 tiles per warp step: one coalesced read of their totals, then the dense ones (rare) one after the other
     for (size_t t0 = (static_cast<size_t>(blockIdx.x) * kWarps + warp) * 32; t0 < n_tiles; t0 += warps_total * 32) {
         const uint32_t my_total = t0 + lane < n_tiles ? tile_total[t0 + lane] : 0u;
-        uint32_t dense = __ballot_sync(0xffffffffu, my_total >= kDenseMin);
+        uint32_t dense = __ballot_sync(0xffffffffu, my_total > stage_entries);  // candidates; dense_tile() below decides
         while (dense != 0) {
             const uint32_t j = __ffs(dense) - 1;
             dense &= dense - 1;
@@ -329,7 +339,7 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
                 if (lane >= static_cast<uint32_t>(d)) inc += o;
             }
             const uint64_t excl = inc - c, wtotal = __shfl_sync(0xffffffffu, inc, 31);
-            if (wtotal >= (1ull << 31)) continue;  // written by intersect_emit_scan_kernel itself
+            if (!dense_tile(wtotal, __reduce_max_sync(0xffffffffu, c), stage_entries)) continue;  // written by intersect_emit_scan_kernel itself
             const uint64_t wbase = tile_base - block_prefix[0];
             uint32_t chrom = 0, hi = 0, qst = 0;
             C qs = 0;

@@ -6,6 +6,8 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -71,6 +73,20 @@ struct gg_index {
     DeviceBuf ER;           // chain rank of each sorted end (flanking.cuh), indexed by level-0 slot - er_base
     uint32_t er_base = 0;   // = tab[0][0]
     DeviceBuf cbegin;       // [n_chrom + 1] first concatenated chain rank of each chromosome
+    // build workspace, kept between builds (a facade re-syncs after every mutation: cudaMalloc / cudaFree of ~600 MB of sort
+    // buffers cost 60 of the 100 ms of a 10 M-interval rebuild); option "keep_build_workspace" = 0 frees it after each build
+    struct BuildWs {
+        DeviceBuf chrom, start, end, tie, stats, perm, perm_alt, perm_end, perm_end_alt, keys_a, keys_b, hist, scan, s32, e32, inv;
+        std::vector<DeviceBuf*> all() {
+            return {&chrom, &start, &end, &tie, &stats, &perm, &perm_alt, &perm_end, &perm_end_alt, &keys_a, &keys_b, &hist, &scan, &s32, &e32, &inv};
+        }
+    } bw;
+    int64_t keep_build_workspace = 1;
+    // pinned staging ring for host -> device copies of pageable caller memory (parallel memcpy into it, see staged_h2d)
+    static constexpr int kStageSlots = 4;
+    static constexpr size_t kStageBytes = 16u << 20;
+    char* h_stage = nullptr;
+    cudaEvent_t ev_stage[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
     DeviceBuf flat[kFlatLevels];  // flat max-end hierarchy over the level-0 slots (emit_tma.cuh)
     DeviceBuf cslot;        // [n_chrom + 1] first level-0 slot of each chromosome (= tab[0][c] - tab[0][0])
     int n_flat = 0;
@@ -424,7 +440,7 @@ gg_status launch_emit_dense(gg_index* idx, const uint32_t* d_chrom, const Q* d_s
     const size_t ctas = div_up(div_up(nq, 32 * 32), kQueryThreads / 32);  // a warp step covers 32 tiles
     const unsigned grid = static_cast<unsigned>(std::min<size_t>(std::max<size_t>(ctas, 1), static_cast<size_t>(idx->sm_count) * per_sm));
     kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix, d_tile,
-                                            static_cast<uint32_t>(kBatchBlockQ), d_hits, capacity, sa);
+                                            static_cast<uint32_t>(kBatchBlockQ), d_hits, capacity, sa, emit_stage_entries(kStrand, true));
     GG_CUDA(cudaGetLastError());
     idx->bstats.kernel_launches++;
     return GG_OK;
@@ -545,6 +561,22 @@ gg_status dispatch_fused(gg_index* idx, const uint32_t* d_chrom, const void* d_s
 
 // ------------------------------------------------------------------------------------------ build
 
+// GG_TRACE_BUILD=1: host timestamps of the build stages on stderr (each after a stream synchronise), for profiling the
+// host-side cost of a build (allocations, pageable copies) that CUDA events on the stream do not attribute
+struct BuildTrace {
+    bool on;
+    cudaStream_t st;
+    std::chrono::steady_clock::time_point t0;
+    explicit BuildTrace(cudaStream_t s) : on(std::getenv("GG_TRACE_BUILD") != nullptr), st(s), t0(std::chrono::steady_clock::now()) {}
+    void mark(const char* what) {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[gg build] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 // Level geometry from per-chromosome counts (host; C is small).  Fills h_tab / h_lvbase / n_levels.
 gg_status plan_levels(gg_index* idx) {
     const uint32_t C = idx->n_chrom;
@@ -611,6 +643,51 @@ gg_status sort_by_field(gg_index* idx, const Field* d_field, int nbits, Key* key
     return GG_OK;
 }
 
+// Host -> device copy of PAGEABLE caller memory through a ring of pinned 16 MB slots: a few host threads memcpy the next
+// slot while the previous one is on the wire (a plain cudaMemcpyAsync from pageable memory runs at ~7 GB/s on this box: 27
+// of the 35 ms of a warm 10 M-interval build).  Small copies go straight through the driver.
+gg_status staged_h2d(gg_index* idx, void* dst, const void* src, size_t bytes, cudaStream_t st) {
+    constexpr size_t kSlot = gg_index::kStageBytes;
+    constexpr int kSlots_ = gg_index::kStageSlots;
+    if (bytes < (4u << 20)) {
+        GG_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+        return GG_OK;
+    }
+    if (!idx->h_stage) {
+        cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&idx->h_stage), kSlot * kSlots_, cudaHostAllocDefault);
+        if (e != cudaSuccess) {  // no pinned memory to be had: the driver's own staging still works
+            cudaGetLastError();
+            idx->h_stage = nullptr;
+            GG_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+            return GG_OK;
+        }
+        for (auto& ev : idx->ev_stage) GG_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    }
+    const unsigned T = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+    const char* s8 = static_cast<const char*>(src);
+    char* d8 = static_cast<char*>(dst);
+    size_t k = 0;
+    for (size_t off = 0; off < bytes; off += kSlot, ++k) {
+        const size_t m = std::min(kSlot, bytes - off);
+        const int slot = static_cast<int>(k % kSlots_);
+        char* h = idx->h_stage + static_cast<size_t>(slot) * kSlot;
+        if (k >= static_cast<size_t>(kSlots_)) GG_CUDA(cudaEventSynchronize(idx->ev_stage[slot]));  // its previous copy has left
+        const size_t part = round_up(div_up(m, T), 4096);
+        std::vector<std::thread> th;
+        for (unsigned t = 1; t < T; ++t) {
+            const size_t a = std::min(m, t * part), b = std::min(m, (t + 1) * part);
+            if (b > a) th.emplace_back([=] { std::memcpy(h + a, s8 + off + a, b - a); });
+        }
+        std::memcpy(h, s8 + off, std::min(m, part));
+        for (auto& x : th) x.join();
+        GG_CUDA(cudaMemcpyAsync(d8 + off, h, m, cudaMemcpyHostToDevice, st));
+        GG_CUDA(cudaEventRecord(idx->ev_stage[slot], st));
+    }
+    // the ring may be reused by the next call right away: wait until this call's copies have read it
+    for (int i = 0; i < kSlots_; ++i) GG_CUDA(cudaEventSynchronize(idx->ev_stage[i]));
+    return GG_OK;
+}
+
 // Shared by gg_index_build (do_sort = true) and gg_index_upload_sorted (do_sort = false).
 // dev_input: chrom / start / end / tie_key / rank_to_input are DEVICE pointers (gg_index_build_device).
 gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
@@ -634,23 +711,27 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     GG_CUDA(cudaEventCreate(&e2));
     GG_CUDA(cudaEventCreate(&e3));
 
-    // temporaries (freed on every exit path by the guard)
-    DeviceBuf d_chrom, d_start, d_end, d_tie, d_stats, d_perm, d_perm_alt, d_perm_end, d_perm_end_alt, d_keys_a, d_keys_b,
-        d_hist, d_scan, d_s32, d_e32, d_inv;
+    // workspace of the build (grow-only, kept in the handle unless keep_build_workspace = 0; borrowed device inputs are
+    // always dropped on exit)
+    gg_index::BuildWs& w = idx->bw;
+    DeviceBuf &d_chrom = w.chrom, &d_start = w.start, &d_end = w.end, &d_tie = w.tie, &d_stats = w.stats, &d_perm = w.perm,
+              &d_perm_alt = w.perm_alt, &d_perm_end = w.perm_end, &d_perm_end_alt = w.perm_end_alt, &d_keys_a = w.keys_a,
+              &d_keys_b = w.keys_b, &d_hist = w.hist, &d_scan = w.scan, &d_s32 = w.s32, &d_e32 = w.e32, &d_inv = w.inv;
     DeviceBuf& d_cbegin = idx->cbegin;  // kept: the flanking / stranded paths index per-rank side arrays with it
     struct Guard {
-        std::vector<DeviceBuf*> bufs;
+        gg_index* idx;
         std::vector<cudaEvent_t> evs;
         ~Guard() {
-            for (auto* b : bufs) b->release();
+            for (auto* b : idx->bw.all())
+                if (!b->own || !idx->keep_build_workspace) b->release();
             for (auto e : evs) cudaEventDestroy(e);
         }
-    } guard;
-    guard.bufs = {&d_chrom, &d_start, &d_end, &d_tie, &d_stats, &d_perm, &d_perm_alt, &d_perm_end, &d_perm_end_alt,
-                  &d_keys_a, &d_keys_b, &d_hist, &d_scan, &d_s32, &d_e32, &d_inv};
-    guard.evs = {e0, e1, e2, e3};
+    } guard{idx, {e0, e1, e2, e3}};
+    for (auto* b : w.all())
+        if (!b->own) b->release();  // (a borrowed view left by an earlier failed call)
 
     const size_t nn = n ? n : 1;
+    BuildTrace trace(st);
     GG_CUDA(cudaEventRecord(e0, st));
     if (dev_input && n) {
         d_chrom.borrow(chrom, n * 4);
@@ -668,13 +749,14 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     GG_CUDA(cudaMemsetAsync(idx->cnt.p, 0, static_cast<size_t>(n_chrom) * 4, st));
     if (n) {
         if (!dev_input) {
-            GG_CUDA(cudaMemcpyAsync(d_chrom.p, chrom, n * 4, cudaMemcpyHostToDevice, st));
-            GG_CUDA(cudaMemcpyAsync(d_start.p, start, n * 8, cudaMemcpyHostToDevice, st));
-            GG_CUDA(cudaMemcpyAsync(d_end.p, end, n * 8, cudaMemcpyHostToDevice, st));
-            if (tie_mode == GG_TIE_EXPLICIT) {
+            gg_status hs_ = staged_h2d(idx, d_chrom.p, chrom, n * 4, st);
+            if (hs_ == GG_OK) hs_ = staged_h2d(idx, d_start.p, start, n * 8, st);
+            if (hs_ == GG_OK) hs_ = staged_h2d(idx, d_end.p, end, n * 8, st);
+            if (hs_ == GG_OK && tie_mode == GG_TIE_EXPLICIT) {
                 GG_CUDA(d_tie.ensure(n * 8));
-                GG_CUDA(cudaMemcpyAsync(d_tie.p, tie_key, n * 8, cudaMemcpyHostToDevice, st));
+                hs_ = staged_h2d(idx, d_tie.p, tie_key, n * 8, st);
             }
+            if (hs_ != GG_OK) return hs_;
         }
         index_stats_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(),
                                                               d_end.as<uint64_t>(), d_tie.as<uint64_t>(), n, n_chrom,
@@ -683,6 +765,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
             check_chain_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(), n,
                                                                   d_stats.as<BuildStats>());
     }
+    trace.mark("alloc + H2D + stats");
     BuildStats hs{};
     std::vector<uint32_t> h_cnt32(n_chrom);
     GG_CUDA(cudaMemcpyAsync(&hs, d_stats.p, sizeof(BuildStats), cudaMemcpyDeviceToHost, st));
@@ -737,6 +820,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
         src_e = d_e32.p;
     }
 
+    trace.mark("plan + sort buffers + narrow");
     GG_CUDA(cudaEventRecord(e1, st));
     uint32_t* perm = d_perm.as<uint32_t>();
     uint32_t* perm_alt = d_perm_alt.as<uint32_t>();
@@ -772,6 +856,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
         if (s == GG_OK) s = sort_by_field<uint32_t, uint32_t>(idx, d_chrom.as<uint32_t>(), chrom_bits, d_keys_a.as<uint32_t>(), d_keys_b.as<uint32_t>(), perm_end, perm_end_alt, n, ws, st);
         if (s != GG_OK) return s;
     }
+    trace.mark("sorts");
     GG_CUDA(cudaEventRecord(e2, st));
 
     // ---- padded SoA leaf level + upper levels
@@ -809,6 +894,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
                 idx->S.as<uint32_t>(), idx->E.as<uint32_t>(), idx->M.as<uint32_t>(), row, row_below, C);
     }
     GG_CUDA(cudaGetLastError());
+    trace.mark("leaf + levels");
     {
         // flat max-end hierarchy over the level-0 slots of all chromosomes (emit_tma.cuh) + first slot per chromosome
         std::vector<uint32_t>& h_cslot = idx->h_cslot;
@@ -836,6 +922,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
         }
         GG_CUDA(cudaGetLastError());
     }
+    trace.mark("flat max hierarchy");
     if (rank_to_input && n)
         GG_CUDA(cudaMemcpyAsync(rank_to_input, perm, n * 4, dev_input ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
     {
@@ -885,6 +972,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     }
     GG_CUDA(cudaEventRecord(e3, st));
     GG_CUDA(cudaStreamSynchronize(st));
+    trace.mark("perm D2H + directory");
 
     float ms_sort = 0, ms_levels = 0, ms_total = 0;
     cudaEventElapsedTime(&ms_sort, e1, e2);
@@ -1474,6 +1562,10 @@ void gg_index_destroy(gg_index* idx) {
     if (idx->pinned_delta) cudaFreeHost(idx->pinned_delta);
     if (idx->h_err) cudaFreeHost(idx->h_err);
     if (idx->h_lazy) cudaFreeHost(idx->h_lazy);
+    if (idx->h_stage) cudaFreeHost(idx->h_stage);
+    for (auto& ev : idx->ev_stage)
+        if (ev) cudaEventDestroy(ev);
+    for (auto* b : idx->bw.all()) b->release();
     if (idx->ev_lazy) cudaEventDestroy(idx->ev_lazy);
     for (auto& e : idx->ev)
         if (e) cudaEventDestroy(e);
@@ -1808,6 +1900,11 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "dense_emit" && value >= -1 && value <= 1) idx->dense_emit = value;
     else if (k == "emit_walk" && (value == 8 || value == 16)) idx->emit_walk = value;
     else if (k == "emit_tma" && value >= 0 && value <= 2) idx->emit_tma = value;
+    else if (k == "keep_build_workspace" && (value == 0 || value == 1)) {
+        idx->keep_build_workspace = value;
+        if (!value)
+            for (auto* b : idx->bw.all()) b->release();
+    }
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;

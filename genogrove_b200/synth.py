@@ -53,6 +53,22 @@ def hg38_intervals(n: int, seed: int = 42, min_len: int = 100, max_len: int = 10
     return chrom[shuffle], start[shuffle].astype(np.uint64), end[shuffle].astype(np.uint64)
 
 
+def hg38_intervals_part(n_total: int, part: int, parts: int, seed: int = 42, min_len: int = 100, max_len: int = 10000,
+                        n_chrom: int = 24):
+    """Part `part` of `parts` of an unsorted n_total-interval input (cfg5: every rank reads its slice of the file): the same
+    recipe as hg38_intervals, drawn record by record — chromosome proportional to length, uniform start, log-uniform length
+    — from a generator seeded per part, so the parts are independent, reproducible and any chromosome occurs in any part."""
+    lo, hi = part * n_total // parts, (part + 1) * n_total // parts
+    n = hi - lo
+    rng = np.random.default_rng([seed, part, parts])
+    lengths = HG38_LENGTHS[:n_chrom]
+    cdf = np.cumsum(lengths / lengths.sum())
+    chrom = np.minimum(np.searchsorted(cdf, rng.random(n), side="right"), n_chrom - 1).astype(np.uint32)
+    ln = np.exp(rng.uniform(np.log(min_len), np.log(max_len), n)).astype(np.int64)
+    start = (rng.random(n) * (lengths[chrom] - ln - 1)).astype(np.int64)
+    return chrom, start.astype(np.uint64), (start + ln - 1).astype(np.uint64)
+
+
 def hg38_queries(q: int, length: int, seed: int = 43, sorted_by_coord: bool = True, n_chrom: int = 24):
     """q queries of fixed length, chromosome proportional to length, uniform start.  sorted_by_coord:
     coordinate-sorted inside each chromosome, chromosomes in id order (BAM-like); else shuffled."""

@@ -361,6 +361,8 @@ void gg_host_free(void* p);
  * "stage_bytes" (shared-memory budget for TMA-staged upper levels, default 16384) and "count_threads" (128..1024));
  * "count_ctas_per_sm", "emit_ctas_per_sm" (0 = occupancy API); "timing" (0/1: record CUDA events around the kernels of
  * the device-buffer calls for gg_last_batch_stats); "compact_delta_bytes" (1, 2, 4: width the compact call starts with);
+ * "keep_build_workspace" (1 [default]: the sort buffers of gg_index_build stay allocated between builds — a facade that
+ * re-syncs after every mutation saves 60 % of a rebuild; 0: freed after each build);
  * "inject_alloc_failure" (debug: the k-th device allocation from now on fails, to drive the error paths). */
 gg_status gg_set_option(gg_index* idx, const char* key, int64_t value);
 

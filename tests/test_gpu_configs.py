@@ -213,3 +213,67 @@ def test_cfg5_one_gpu_share_of_chromosome_sharded_build(gg):
     s, e, cbegin = _chain(chrom, start, end, perm, len(mine))
     d_off, d_hits = _run_device(torch, idx, qc, qs, qe)
     _verify(torch, s, e, cbegin, len(mine), qc, qs, qe, d_off, d_hits, sample=2000)
+
+
+@pytest.mark.parametrize("cfg", ["cfg4", "cfg3"])
+def test_full_size_groves_against_the_live_reference(gg, cfg):
+    """The CUDA path against the UNMODIFIED reference itself (oracle/_ref/libgg_ref.so: grove<interval, uint32_t>::intersect
+    per query, order 32) on the full-size cfg4 / cfg3 groves, id for id and in order, for 2 M / 1 M queries taken from the
+    middle of the real batches — not against the flat restatement the other tests use."""
+    import oracle as O
+    if not O.ref_available():
+        pytest.skip("oracle/_ref/libgg_ref.so not built")
+    from genogrove_b200 import synth
+    w = synth.cfg4(q=20_000_000) if cfg == "cfg4" else synth.cfg3(q=5_000_000)
+    nq = 2_000_000 if cfg == "cfg4" else 1_000_000
+    lo = (len(w.q_chrom) - nq) // 2
+    qc, qs, qe = w.q_chrom[lo:lo + nq], w.q_start[lo:lo + nq], w.q_end[lo:lo + nq]
+    ref = O.RefGrove(32)
+    ids = np.arange(len(w.chrom), dtype=np.uint32)
+    for c in range(w.n_chrom):
+        m = w.chrom == c
+        # cfg3 holds many equal (start, end) keys (cfg4 possibly a few): the reference's sorted-bulk path keeps equal keys in
+        # input order, which is what the stable device sort does; its unsorted-bulk path runs an unstable std::sort
+        order = np.lexsort((w.end[m], w.start[m]))
+        ref.insert_bulk(c, w.start[m][order], w.end[m][order], ids[m][order], presorted=True)
+    r_off, r_ids, _ = ref.intersect_batch(qc, qs, qe, threads=ref.hardware_threads())
+    idx = gg.DeviceIndex(0)
+    perm = idx.build(w.chrom, w.start, w.end, w.n_chrom)  # stable: equal keys in input order, like sorted-bulk above
+    cbegin = np.concatenate([[0], np.cumsum(np.bincount(w.chrom, minlength=w.n_chrom))]).astype(np.int64)
+    for form in ("csr", "compact"):
+        if form == "csr":
+            off, hits = idx.intersect_batch(qc, qs, qe)
+        else:
+            off, hits = idx.intersect_batch_compact(qc, qs.astype(np.uint32), qe.astype(np.uint32))
+        assert np.array_equal(off, r_off)
+        counts = np.diff(off).astype(np.int64)
+        got_ids = perm[np.repeat(cbegin[qc], counts) + hits]
+        assert np.array_equal(got_ids, r_ids), f"{cfg} {form}: hit ids differ from the reference's"
+    ref.close()
+
+
+@pytest.mark.parametrize("dense_emit", [-1, 1, 0])
+def test_uniformly_dense_tiles_between_stage_and_dense_threshold(gg, dense_emit):
+    """~36 hits per query on every query (a 50 M-interval hg38-shaped grove has this density): warp tiles of ~1150 hits exceed
+    the emit stage but stay below the 2048-hit threshold of the dense kernel.  The shape test (dense_tile, emit_scan.cuh)
+    sends them to the segment-flush kernel; a tile with one long list among short ones keeps the direct walk."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(131)
+    n, span = 2_500_000, 150_000_000
+    ln = np.exp(rng.uniform(np.log(100), np.log(10000), n)).astype(np.int64)
+    start = (rng.random(n) * (span - ln - 1)).astype(np.int64)
+    end = start + ln - 1
+    end[::100_000] = start[::100_000] + 40_000_000   # a few huge intervals: skewed tiles among the uniform ones
+    chrom = np.zeros(n, np.uint32)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("dense_emit", dense_emit)
+    perm = idx.build(chrom, start.astype(np.uint64), end.astype(np.uint64), 1)
+    s, e, cbegin = _chain(chrom, start.astype(np.uint64), end.astype(np.uint64), perm, 1)
+    nq = 2_000_000
+    qs = np.sort(rng.integers(0, span - 150, nq, dtype=np.int64)).astype(np.uint64)
+    qs[::7] = rng.integers(0, span - 150, len(qs[::7]), dtype=np.int64).astype(np.uint64)  # and some out-of-order ones
+    qc, qe = np.zeros(nq, np.uint32), qs + np.uint64(149)
+    for _ in range(2):  # the second pass runs with the density the first one reported (dense_emit = -1)
+        d_off, d_hits = _run_device(torch, idx, qc, qs, qe)
+        total = _verify(torch, s, e, cbegin, 1, qc, qs, qe, d_off, d_hits, sample=1500)
+    assert total > 30 * nq
