@@ -32,10 +32,12 @@
 //   insert_data(idx, vec, bulk)          device radix sort, stable: equal keys keep input order (the reference
 //                                        runs an UNSTABLE std::sort here, grove_insert.ipp:167-168, so it does
 //                                        not define that order itself)
-//   insert_data(idx, k, d, sorted)       lower_bound inside the rightmost leaf, leaf split leaves one key right
-//                                        (grove_insert.ipp:316,501-531); rightmost-leaf bounds are tracked while
-//                                        the history is bulk/sorted-only and approximated by the whole chain
-//                                        after regular inserts or removals (exact whenever keys are distinct)
+//   insert_data(idx, k, d, sorted)       lower_bound inside the RIGHTMOST LEAF only (grove_insert.ipp:501-531), so
+//                                        the place among equal keys depends on that leaf's key count.  The count is
+//                                        exact for every history: closed form while an index has only seen bulk /
+//                                        sorted / adopted input, and from a counts-only replay of the reference's
+//                                        split / borrow / merge rules (chain_shape.hpp) once a regular insert or a
+//                                        removal touched it
 #ifndef GENOGROVE_B200_GROVE_HPP
 #define GENOGROVE_B200_GROVE_HPP
 
@@ -59,6 +61,7 @@
 #include <vector>
 
 #include "../gg_b200.h"
+#include "chain_shape.hpp"
 
 namespace genogrove_b200 {
 
@@ -248,6 +251,12 @@ struct sorted_t {};
 struct bulk_t {};
 inline constexpr sorted_t sorted{};
 inline constexpr bulk_t bulk{};
+/// Tag for a grove WITHOUT a device handle: host bookkeeping only (keys, leaf chains, tree shape — chain(),
+/// shape_tokens()), so that host-side ordering logic can be tested where no GPU exists.  Anything that needs an
+/// overlap computed — intersect, flanking, the device-sorted unsorted bulk — throws device_error: there is no CPU
+/// search path.
+struct detached_t {};
+inline constexpr detached_t detached{};
 
 /// Result of grove::intersect_batch: CSR over the batch.  Query q's hits are ranks()[offsets()[q] ..
 /// offsets()[q+1]) — leaf-chain ranks inside the query's index, ascending — and key(q, j) maps them back to the
@@ -307,6 +316,9 @@ class grove {
         if (st != GG_OK) throw device_error(st, "gg_index_create: no usable CUDA device (there is no CPU fallback)");
         dev.reset(h);
     }
+    grove(int order, detached_t) : order(order) {
+        if (order < 3) throw std::invalid_argument("grove order must be >= 3");
+    }
     grove() : grove(3) {}
     ~grove() = default;
     grove(const grove&) = delete;
@@ -345,7 +357,6 @@ class grove {
         chain_state& ch = chain_for(index);
         key_ptr p = allocate_key(k);
         ch.pending.push_back(p);
-        ch.leaf_known = false;
         ++leaf_key_count;
         dirty = true;
         return p;
@@ -369,6 +380,7 @@ class grove {
         requires(!std::is_void_v<data_type> && std::ranges::random_access_range<Container> && std::ranges::sized_range<Container>) {
         const std::size_t n = std::ranges::size(data);
         if (n == 0) return {};
+        need_device();
         std::vector<std::uint64_t> s(n), e(n);
         for (std::size_t i = 0; i < n; ++i) {
             s[i] = data[i].first.get_start();
@@ -409,8 +421,10 @@ class grove {
             pos = std::find(ch.chain.begin(), ch.chain.end(), key_to_remove);
             if (pos == ch.chain.end()) return false;
         }
+        materialise(ch);
+        ch.shape.remove_at(static_cast<std::size_t>(pos - ch.chain.begin()));
         ch.chain.erase(pos);
-        ch.leaf_known = false;
+        ch.leaf_begin = ch.chain.size() - ch.shape.rightmost_leaf_keys();
         --leaf_key_count;
         dirty = true;
         if (ch.chain.empty()) indices.erase(it);  // the reference erases an emptied root (grove_remove.ipp:44-50)
@@ -550,6 +564,46 @@ class grove {
         check(gg_flanking_batch(dev.get(), q_index, q_start, q_end, nq, pred, succ));
     }
 
+    /// Take over one index whose keys are already in LEAF-CHAIN order — what a serialized grove's leaf blocks
+    /// hold (gg_loader.hpp) or what a caller flattened from a reference grove.  make_key() is called n times and
+    /// yields the keys in chain order; `shape` is the tree in pre-order tokens (leaf: chain_shape::leaf_bit | key
+    /// count, internal node: child count; bottom_up_shape() gives the tokens of a freshly bulk-built tree), which
+    /// later sorted appends, regular inserts and removals need to place tied keys exactly where the reference
+    /// does.  The index must not exist yet; n == 0 creates nothing.
+    template <typename MakeKey>
+    std::vector<key_ptr> adopt_chain(std::string_view index, std::size_t n, std::span<const std::uint32_t> shape, MakeKey&& make_key) {
+        if (indices.find(index) != indices.end()) throw std::invalid_argument("adopt_chain: index already exists");
+        std::size_t leaf_keys = 0, last_leaf = 0;
+        for (const std::uint32_t t : shape)
+            if ((t & detail::chain_shape::leaf_bit) != 0) leaf_keys += (last_leaf = t & ~detail::chain_shape::leaf_bit);
+        if (leaf_keys != n) throw std::invalid_argument("adopt_chain: the shape's leaves do not hold n keys");
+        std::vector<key_ptr> adopted;
+        if (n == 0) return adopted;
+        adopted.reserve(n);
+        for (std::size_t i = 0; i < n; ++i) adopted.push_back(allocate_key(make_key()));
+        chain_state& ch = chain_for(index);
+        ch.chain = adopted;
+        ch.lazy_tokens.assign(shape.begin(), shape.end());
+        ch.leaf_begin = n - last_leaf;
+        leaf_key_count += n;
+        dirty = true;
+        return adopted;
+    }
+    /// pre-order tokens of the tree a sorted bulk insert of n keys builds on an empty index
+    [[nodiscard]] std::vector<std::uint32_t> bottom_up_shape(std::size_t n) const {
+        detail::chain_shape s(order);
+        s.build_bottom_up(n);
+        return s.tokens();
+    }
+    /// pre-order tokens of one index's tree as this side tracks it (tests compare them with the reference's real tree)
+    [[nodiscard]] std::vector<std::uint32_t> shape_tokens(std::string_view index) {
+        auto it = indices.find(index);
+        if (it == indices.end()) return {};
+        flush_pending(it->second);
+        materialise(it->second);
+        return it->second.shape.tokens();
+    }
+
     /// Leaf chain of one index as the device sees it (rank -> key*); empty when the index does not exist.
     [[nodiscard]] const std::vector<key_ptr>& chain(std::string_view index) {
         static const std::vector<key_ptr> none;
@@ -561,15 +615,27 @@ class grove {
 
   private:
     struct chain_state {
+        explicit chain_state(int order) : shape(order) {}
         std::vector<key_ptr> chain;    // leaf-chain order
         std::vector<key_ptr> pending;  // regular inserts not yet merged into the chain, in insertion order
-        std::size_t leaf_begin = 0;    // first rank of the rightmost leaf (sorted-append emulation)
-        bool leaf_known = true;        // false once a path ran whose leaf boundaries are not tracked
+        std::size_t leaf_begin = 0;    // first rank of the rightmost leaf: where a sorted append starts its lower_bound
+        // Tree shape.  While an index has only seen bulk / sorted / adopted input its shape has a closed description
+        // (tokens or a bottom-up build, then lazy_appends sorted appends) and leaf_begin follows from the append rule
+        // alone; the first regular insert or removal replays that description into `shape`, which is kept from then on.
+        detail::chain_shape shape;
+        bool shape_live = false;
+        std::size_t lazy_bottom_up = 0;
+        std::vector<std::uint32_t> lazy_tokens;
+        std::size_t lazy_appends = 0;
         std::uint32_t id = 0;          // chromosome id in the device snapshot
     };
     struct handle_deleter {
         void operator()(gg_index* h) const noexcept { gg_index_destroy(h); }
     };
+
+    void need_device() const {
+        if (!dev) throw device_error(GG_ERR_NOT_BUILT, "genogrove_b200::grove: detached grove has no device (there is no CPU search path)");
+    }
 
     void check(gg_status st) const {
         if (st == GG_OK) return;
@@ -587,7 +653,7 @@ class grove {
         auto it = indices.find(index);
         if (it != indices.end()) return it->second;
         dirty = true;
-        return indices.emplace(std::string(index), chain_state{}).first->second;
+        return indices.emplace(std::string(index), chain_state{order}).first->second;
     }
 
     bool all_pending_empty() const {
@@ -605,18 +671,55 @@ class grove {
         if (ch.pending.empty()) return;
         std::vector<key_ptr> p(ch.pending.rbegin(), ch.pending.rend());
         std::stable_sort(p.begin(), p.end(), value_less);
+        // replay the inserts on the tree shape, in insertion order: each landed at its lower_bound rank over the keys
+        // present at that moment = chain keys below it + earlier pending keys below it (Fenwick tree over value order)
+        materialise(ch);
+        std::vector<std::size_t> fenwick(p.size() + 1, 0);
+        for (const key_ptr k : ch.pending) {
+            const std::size_t in_chain = static_cast<std::size_t>(std::lower_bound(ch.chain.begin(), ch.chain.end(), k, value_less) - ch.chain.begin());
+            const std::size_t slot = static_cast<std::size_t>(std::lower_bound(p.begin(), p.end(), k, value_less) - p.begin());
+            std::size_t earlier_below = 0;
+            for (std::size_t i = slot; i > 0; i -= i & (~i + 1)) earlier_below += fenwick[i];
+            ch.shape.insert_at(in_chain + earlier_below);
+            for (std::size_t i = slot + 1; i <= p.size(); i += i & (~i + 1)) ++fenwick[i];
+        }
         std::vector<key_ptr> merged;
         merged.reserve(ch.chain.size() + p.size());
         // std::merge is stable with the FIRST range winning ties: pending first
         std::merge(p.begin(), p.end(), ch.chain.begin(), ch.chain.end(), std::back_inserter(merged), value_less);
         ch.chain.swap(merged);
         ch.pending.clear();
+        ch.leaf_begin = ch.chain.size() - ch.shape.rightmost_leaf_keys();
+    }
+
+    /// make ch.shape the explicit twin of the index's tree (see chain_state)
+    void materialise(chain_state& ch) {
+        if (ch.shape_live) return;
+        if (!ch.lazy_tokens.empty()) ch.shape.build_from_tokens(ch.lazy_tokens);
+        else ch.shape.build_bottom_up(ch.lazy_bottom_up);
+        for (std::size_t i = 0; i < ch.lazy_appends; ++i) ch.shape.append_sorted();
+        if (ch.shape.size() != ch.chain.size() || ch.chain.size() - ch.shape.rightmost_leaf_keys() != ch.leaf_begin)
+            throw std::logic_error("genogrove_b200::grove: tree shape out of step with the leaf chain");
+        ch.lazy_tokens.clear();
+        ch.lazy_tokens.shrink_to_fit();
+        ch.lazy_bottom_up = ch.lazy_appends = 0;
+        ch.shape_live = true;
+    }
+
+    /// one key was appended through the sorted path: the rightmost leaf grew, and splits leaving ONE key right at `order`
+    void note_sorted_append(chain_state& ch) {
+        if (ch.shape_live) {
+            ch.shape.append_sorted();
+            ch.leaf_begin = ch.chain.size() - ch.shape.rightmost_leaf_keys();
+        } else {
+            ++ch.lazy_appends;
+            if (ch.chain.size() - ch.leaf_begin == static_cast<std::size_t>(order)) ch.leaf_begin = ch.chain.size() - 1;
+        }
     }
 
     /// position of a sorted append: lower_bound inside the rightmost leaf (node::insert_key_ptr on it)
     std::size_t sorted_position(const chain_state& ch, const key_ptr k) const {
-        const std::size_t lo = ch.leaf_known ? ch.leaf_begin : 0;
-        return static_cast<std::size_t>(std::lower_bound(ch.chain.begin() + static_cast<std::ptrdiff_t>(lo), ch.chain.end(), k, value_less) -
+        return static_cast<std::size_t>(std::lower_bound(ch.chain.begin() + static_cast<std::ptrdiff_t>(ch.leaf_begin), ch.chain.end(), k, value_less) -
                                         ch.chain.begin());
     }
 
@@ -624,8 +727,7 @@ class grove {
         chain_state& ch = chain_for(index);
         flush_pending(ch);
         ch.chain.insert(ch.chain.begin() + static_cast<std::ptrdiff_t>(sorted_position(ch, k)), k);
-        if (ch.leaf_known && ch.chain.size() - ch.leaf_begin == static_cast<std::size_t>(order))
-            ch.leaf_begin = ch.chain.size() - 1;  // overflowing rightmost leaf splits leaving one key on the right
+        note_sorted_append(ch);
         ++leaf_key_count;
         dirty = true;
         return k;
@@ -642,12 +744,15 @@ class grove {
             const std::size_t groups = n / cap + (n % cap != 0 ? 1 : 0);
             ch.chain = run;
             ch.leaf_begin = n - n / groups;
-            ch.leaf_known = true;
+            ch.shape.clear();
+            ch.shape_live = false;
+            ch.lazy_tokens.clear();
+            ch.lazy_bottom_up = n;
+            ch.lazy_appends = 0;
         } else {
             for (key_ptr k : run) {
                 ch.chain.insert(ch.chain.begin() + static_cast<std::ptrdiff_t>(sorted_position(ch, k)), k);
-                if (ch.leaf_known && ch.chain.size() - ch.leaf_begin == static_cast<std::size_t>(order))
-                    ch.leaf_begin = ch.chain.size() - 1;
+                note_sorted_append(ch);
             }
         }
         leaf_key_count += run.size();
@@ -661,6 +766,7 @@ class grove {
 
     /// Re-flatten the host chains into the device snapshot (gg_index_upload_sorted) when anything changed.
     void sync() {
+        need_device();
         if (!dirty) return;
         std::size_t n = 0;
         for (auto& [name, ch] : indices) {

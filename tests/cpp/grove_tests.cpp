@@ -10,7 +10,10 @@
 //     reference-side binding of INTEGRATION.md (device snapshot taken by walking the reference's real leaf
 //     chain) checked pointer-for-pointer against the reference's own intersect.
 // All overlap computation on the facade side runs on the GPU (no CPU path exists); needs a CUDA device.
+#include <unistd.h>
+
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -19,10 +22,12 @@
 #include <set>
 #include <sstream>
 #include <string>
+#include <unordered_map>
 #include <utility>
 #include <vector>
 
 #include "genogrove_b200/grove.hpp"
+#include "genogrove_b200/gg_loader.hpp"
 
 #ifdef WITH_REFERENCE
 #include <genogrove/data_type/genomic_coordinate.hpp>
@@ -749,6 +754,203 @@ static void test_batch_entry_point() {
     CHECK(h.intersect(qv[0], "chr1").get_keys() == b2k0);
 }
 
+// ------------------------------------------------------------------------------------------- .gg fast path
+// a serialized grove (format 0.3) goes to the device through genogrove_b200::io::load_gg, which
+// reads the leaf chain out of the blocks without building a pointer tree.  A "script" is a list of text lines:
+//   Q <index|*> <strand> <start> <end> | <payload> ...   query and the reference's answer, in the reference's order
+//   A <index> <strand> <start> <end> <payload>            sorted single append applied AFTER loading
+//   I <index> <strand> <start> <end> <payload>            regular insert applied AFTER loading
+//   R <index> <payload>                                   remove_key of the key inserted with that payload
+//   S|U <index> <n> n x (<strand> <start> <end> <payload>) sorted / unsorted bulk insert of a run
+//   T <index> L<keys>|N<children> ...                     the reference's real tree in pre-order (shape check)
+// The reference writes the stream and the script (live in ref_parity.bin; committed under tests/golden/gg/ by
+// `ref_parity.bin --write-gg-fixtures DIR`); replay() runs the script against the loaded facade grove.
+namespace ggfast {
+namespace fio = genogrove_b200::io;
+
+template <typename K>
+K make_value(char strand, std::size_t s, std::size_t e) {
+    if constexpr (requires { K('+', s, e); }) return K(strand, s, e);
+    else return K(s, e);
+}
+template <typename K>
+char strand_of(const K& k) {
+    if constexpr (requires { k.get_strand(); }) return k.get_strand();
+    else return '.';
+}
+template <typename D>
+std::string show(const D& d) {
+    if constexpr (std::is_same_v<D, std::string>) return d;
+    else return std::to_string(d);
+}
+template <typename D>
+D parse_payload(const std::string& s) {
+    if constexpr (std::is_same_v<D, std::string>) return s;
+    else return static_cast<D>(std::stoll(s));
+}
+
+template <typename G, typename K>
+std::string answer_line(G& g, const std::string& index, const K& q) {
+    std::ostringstream os;
+    os << "Q " << index << ' ' << strand_of(q) << ' ' << q.get_start() << ' ' << q.get_end() << " |";
+    auto r = index == "*" ? g.intersect(q) : g.intersect(q, index);
+    for (auto* k : r.get_keys()) os << ' ' << show(k->get_data());
+    return os.str();
+}
+
+/// run a script against the facade grove restored from `stream`; returns the number of Q lines checked
+/// run a script against a facade grove: restored from `stream`, or empty (order given) when the stream is empty
+/// host_only: a detached grove (no device) — only the lines that need no overlap computed are checked: tree shapes,
+/// and queries wide enough to return the whole chain, answered from chain()
+template <typename K, typename D>
+std::size_t replay(const std::string& stream, const std::vector<std::string>& script, fio::gg_stream_info* info = nullptr, int order = 3,
+                   bool host_only = false) {
+    using grove_t = genogrove_b200::structure::grove<K, D>;
+    std::istringstream is(stream, std::ios::binary);
+    grove_t g = host_only ? grove_t(order, genogrove_b200::structure::detached)
+                          : (stream.empty() ? grove_t(order) : fio::load_gg<K, D>(is, 0, info));
+    std::unordered_map<std::string, typename grove_t::key_ptr> by_payload;  // R lines name keys by payload
+    std::size_t checked = 0, bad = 0;
+    for (const std::string& line : script) {
+        std::istringstream ls(line);
+        std::string op, index;
+        ls >> op >> index;
+        if (op == "T") {  // the reference's real tree, pre-order: 'L<keys>' / 'N<children>'
+            std::ostringstream os;
+            os << "T " << index;
+            for (const std::uint32_t t : g.shape_tokens(index)) {
+                if ((t & 0x80000000u) != 0) os << " L" << (t & 0x7FFFFFFFu);
+                else os << " N" << t;
+            }
+            if (os.str() != line && bad++ < 5) std::fprintf(stderr, "tree shape differs\n  reference: %.300s\n  facade   : %.300s\n", line.c_str(), os.str().c_str());
+            ++checked;
+            continue;
+        }
+        if (op == "R") {
+            std::string payload;
+            ls >> payload;
+            auto it = by_payload.find(index + "/" + payload);
+            CHECK(it != by_payload.end());
+            if (it != by_payload.end()) {
+                CHECK(g.remove_key(index, it->second));
+                by_payload.erase(it);
+            }
+            continue;
+        }
+        if (op == "S" || op == "U") {  // sorted / unsorted bulk run: count, then count x (strand start end payload)
+            std::size_t count;
+            ls >> count;
+            std::vector<std::pair<K, D>> run;
+            std::vector<std::string> names;
+            for (std::size_t i = 0; i < count; ++i) {
+                char strand;
+                std::size_t s, e;
+                std::string payload;
+                ls >> strand >> s >> e >> payload;
+                run.push_back({make_value<K>(strand, s, e), parse_payload<D>(payload)});
+            }
+            auto keys = op == "S" ? g.insert_data(index, run, genogrove_b200::structure::sorted, genogrove_b200::structure::bulk)
+                                  : g.insert_data(index, run, genogrove_b200::structure::bulk);
+            for (auto* k : keys) by_payload[index + "/" + show(k->get_data())] = k;
+            continue;
+        }
+        char strand;
+        std::size_t s, e;
+        ls >> strand >> s >> e;
+        if (op == "Q" && host_only) {
+            if (s != 0 || e < (1u << 30)) continue;
+            std::ostringstream os;
+            os << "Q " << index << ' ' << strand << ' ' << s << ' ' << e << " |";
+            for (auto* k : g.chain(index)) os << ' ' << show(k->get_data());
+            if (os.str() != line && bad++ < 5) std::fprintf(stderr, "chain order differs\n  reference: %.300s\n  facade   : %.300s\n", line.c_str(), os.str().c_str());
+            ++checked;
+        } else if (op == "Q") {
+            const std::string got = answer_line(g, index, make_value<K>(strand, s, e));
+            if (got != line && bad++ < 5) std::fprintf(stderr, "hit order differs\n  reference: %.300s\n  facade   : %.300s\n", line.c_str(), got.c_str());
+            ++checked;
+        } else {
+            std::string payload;
+            ls >> payload;
+            auto* k = op == "A" ? g.insert_data(index, make_value<K>(strand, s, e), parse_payload<D>(payload), genogrove_b200::structure::sorted)
+                                : g.insert_data(index, make_value<K>(strand, s, e), parse_payload<D>(payload));
+            by_payload[index + "/" + payload] = k;
+        }
+    }
+    CHECK(bad == 0);
+    CHECK(checked > 0);
+    return checked;
+}
+
+static std::string slurp(const std::string& path) {
+    std::FILE* f = std::fopen(path.c_str(), "rb");
+    if (f == nullptr) return {};
+    std::string out;
+    char buf[1 << 16];
+    for (std::size_t n; (n = std::fread(buf, 1, sizeof(buf), f)) > 0;) out.append(buf, n);
+    std::fclose(f);
+    return out;
+}
+static std::vector<std::string> lines_of(const std::string& text) {
+    std::vector<std::string> v;
+    std::istringstream is(text);
+    for (std::string l; std::getline(is, l);)
+        if (!l.empty()) v.push_back(l);
+    return v;
+}
+
+/// committed fixtures: streams written by the reference itself + its answers (tests/golden/gg/)
+static void test_fixtures(const std::string& dir) {
+    namespace fdt = genogrove_b200::data_type;
+    struct fx { const char* stem; int kind; };
+    std::size_t total = 0;
+    for (const fx& f : {fx{"interval_int_o3", 0}, fx{"interval_int_o32", 0}, fx{"interval_str_o5", 1}, fx{"gcoord_int_o4", 2}, fx{"gcoord_str_o16", 3}}) {
+        const std::string stream = slurp(dir + "/" + f.stem + ".gg"), script = slurp(dir + "/" + f.stem + ".script");
+        CHECK(!stream.empty() && !script.empty());
+        if (stream.empty() || script.empty()) {
+            std::fprintf(stderr, "missing fixture %s/%s.{gg,script}\n", dir.c_str(), f.stem);
+            continue;
+        }
+        const auto lines = lines_of(script);
+        if (f.kind == 0) total += replay<fdt::interval, int>(stream, lines);
+        if (f.kind == 1) total += replay<fdt::interval, std::string>(stream, lines);
+        if (f.kind == 2) total += replay<fdt::genomic_coordinate, int>(stream, lines);
+        if (f.kind == 3) total += replay<fdt::genomic_coordinate, std::string>(stream, lines);
+    }
+    std::printf("gg fast path: %zu fixture queries identical to the reference's answers\n", total);
+    // mixed insert histories from an EMPTY grove (row f1): hit order AND tree shape after every step
+    std::size_t mixed = 0;
+    for (const char* stem : {"mixed_o3", "mixed_o4", "mixed_o5", "mixed_o8"}) {
+        const std::string script = slurp(dir + "/" + stem + ".script");
+        CHECK(!script.empty());
+        if (script.empty()) continue;
+        mixed += replay<fdt::interval, int>(std::string(), lines_of(script), nullptr, std::atoi(stem + 7));
+    }
+    std::printf("mixed histories: %zu fixture lines (hit order + tree shape) identical to the reference\n", mixed);
+    // malformed input is reported the way the reference reports it: std::runtime_error
+    const std::string good = slurp(dir + "/interval_int_o3.gg");
+    if (!good.empty()) {
+        auto load = [](const std::string& bytes) {
+            std::istringstream is(bytes, std::ios::binary);
+            return fio::load_gg<fdt::interval, int>(is).size();
+        };
+        CHECK_THROWS(load("GGB\x02" + good.substr(4)), std::runtime_error);       // wrong format version in the magic
+        CHECK_THROWS(load(good.substr(0, good.size() / 2)), std::runtime_error);  // truncated
+        CHECK_THROWS(load(std::string()), std::runtime_error);
+        std::string flipped = good;
+        flipped[flipped.size() - 9] = static_cast<char>(flipped[flipped.size() - 9] ^ 0x5a);  // inside the last deflate stream
+        CHECK_THROWS(load(flipped), std::runtime_error);
+        // the CLI's 12-byte wrapper (io/gg_format.hpp:24-40) in front of the same stream is skipped
+        const std::string wrapped = std::string("GROV\x00\x03\x00\x01\x00\x01\x00\x00", 12) + good;
+        fio::gg_stream_info info;
+        std::istringstream is(wrapped, std::ios::binary);
+        auto g = fio::load_gg<fdt::interval, int>(is, 0, &info);
+        CHECK(info.cli_wrapper && info.payload_type == 1);
+        CHECK(g.size() == info.leaf_keys && g.size() > 0);
+        CHECK(g.get_order() == 3);
+    }
+}
+}  // namespace ggfast
+
 #ifdef WITH_REFERENCE
 // ------------------------------------------------------------------------------------------- reference-side binding
 // what a genogrove maintainer adds — flatten the reference grove's REAL leaf chain into SoA
@@ -846,13 +1048,324 @@ static void test_reference_binding() {
     }
 }
 }  // namespace binding
+// ------------------------------------------------------------------------------------------- .gg fast path, reference side
+// The reference builds groves through every insert path, serializes them, restores them with ITS deserialize()
+// and answers the script; the facade restores the same bytes through load_gg (no pointer tree) and must give the
+// same payload sequences — including after sorted appends of tied keys, which depend on the key count of the
+// rightmost leaf in the file.
+namespace ggfast {
+namespace rdt = genogrove::data_type;
+namespace rst = genogrove::structure;
+
+template <typename RK, typename D>
+std::vector<std::string> write_script(int order, std::uint64_t seed, int n, std::string& stream_out) {
+    std::mt19937_64 rng(seed);
+    rst::grove<RK, D> g(order);
+    int next_id = 0;
+    auto payload = [&]() -> D {
+        const int v = next_id++;
+        if constexpr (std::is_same_v<D, std::string>) return (v % 17 == 0 ? std::string() : "p" + std::to_string(v) + std::string(v % 5, 'x'));
+        else return static_cast<D>(v);
+    };
+    const char sym[4] = {'+', '-', '.', '*'};
+    auto value = [&](bool dup) {
+        std::size_t s = rng() % 300000, len = rng() % 40 == 0 ? 50000 : rng() % 500;
+        if (dup) s = s / 1000 * 1000, len = 100;
+        return make_value<RK>(sym[rng() % 4], s, s + len);
+    };
+    // chr1: regular inserts (ties resolved by insertion history) and removals (leaf merges / borrows)
+    std::vector<rdt::key<RK, D>*> ins;
+    for (int i = 0; i < n; ++i) ins.push_back(g.insert_data("chr1", value(i % 7 == 0), payload()));
+    for (int i = 0; i < n; i += 5) g.remove_key("chr1", ins[static_cast<std::size_t>(i)]);
+    // chr2: unsorted bulk — the reference's std::sort leaves equal keys in an order only the stream records
+    std::vector<std::pair<RK, D>> v;
+    for (int i = 0; i < n; ++i) v.push_back({value(i % 11 == 0), payload()});
+    g.insert_data("chr2", v, rst::bulk);
+    // chrX: sorted bulk, then sorted single appends of the maximum (rightmost leaf fills and splits)
+    v.clear();
+    for (int i = 0; i < n; ++i) v.push_back({value(i % 9 == 0), payload()});
+    std::stable_sort(v.begin(), v.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    g.insert_data("chrX", v, rst::sorted, rst::bulk);
+    const RK top = v.back().first;
+    for (int j = 0; j < order / 2 + 1; ++j) g.insert_data("chrX", top, payload(), rst::sorted);
+    // scaffold_7: a root that is still a leaf; "gone": created and emptied again
+    g.insert_data("scaffold_7", make_value<RK>('+', 5, 9), payload(), rst::sorted);
+    g.insert_data("scaffold_7", make_value<RK>('-', 7, 70), payload(), rst::sorted);
+    auto* lone = g.insert_data("gone", make_value<RK>('.', 1, 2), payload());
+    g.remove_key("gone", lone);
+
+    std::ostringstream os(std::ios::binary);
+    g.serialize(os);
+    stream_out = os.str();
+    std::istringstream is(stream_out, std::ios::binary);
+    auto r = rst::grove<RK, D>::deserialize(is);
+
+    std::vector<std::string> script;
+    const char* names[] = {"chr1", "chr2", "chrX", "scaffold_7", "gone", "never", "*"};
+    auto ask = [&](int count) {
+        for (int k = 0; k < count; ++k) {
+            const std::size_t a = rng() % 310000, b = a + (rng() % 25 == 0 ? rng() % 60000 : rng() % 400);
+            script.push_back(answer_line(r, names[rng() % 7], make_value<RK>(sym[rng() % 4], k % 50 == 0 ? 0 : a, k % 50 == 0 ? 400000 : b)));
+        }
+    };
+    ask(150);
+    // sorted appends of tied keys on the restored grove: more than one leaf's worth, on the index built by
+    // regular inserts + removals too (its rightmost-leaf key count is only known from the stream)
+    auto apply = [&](const char* op, const char* index, const RK& k) {
+        const D d = payload();
+        std::ostringstream ls;
+        ls << op << ' ' << index << ' ' << strand_of(k) << ' ' << k.get_start() << ' ' << k.get_end() << ' ' << (show(d).empty() ? std::string("-") : show(d));
+        if (op[0] == 'A') r.insert_data(index, k, show(d).empty() ? parse_payload<D>("-") : d, rst::sorted);
+        else r.insert_data(index, k, show(d).empty() ? parse_payload<D>("-") : d);
+        script.push_back(ls.str());
+    };
+    const RK far1 = make_value<RK>('+', 400000, 400100), far2 = make_value<RK>('+', 400000, 400200);
+    for (int j = 0; j < 2 * order + 1; ++j) {
+        apply("A", "chr1", far1);
+        apply("A", "chrX", j < order ? far1 : far2);
+        if (j % 3 == 0) apply("A", "chr2", far1);
+    }
+    apply("A", "fresh", far1);
+    ask(120);
+    script.push_back(answer_line(r, "chr1", make_value<RK>('*', 399999, 400001)));
+    script.push_back(answer_line(r, "chrX", make_value<RK>('*', 399999, 400001)));
+    script.push_back(answer_line(r, "chr2", make_value<RK>('*', 399999, 400001)));
+    // regular inserts after that land in front of every equal key
+    for (int j = 0; j < order + 2; ++j) {
+        apply("I", "chr1", far1);
+        apply("I", "chr2", value(true));
+    }
+    ask(80);
+    script.push_back(answer_line(r, "chr1", make_value<RK>('*', 399999, 400001)));
+    return script;
+}
+
+/// the reference's real tree of one index in pre-order
+template <typename G>
+std::string tree_line(const G& g, const std::string& index) {
+    std::ostringstream os;
+    os << "T " << index;
+    auto it = g.get_root_nodes().find(index);
+    if (it == g.get_root_nodes().end()) return os.str();
+    auto walk = [&](auto* n, auto&& self) -> void {
+        if (n->get_is_leaf()) {
+            os << " L" << n->get_keys().size();
+            return;
+        }
+        os << " N" << n->get_children().size();
+        for (auto* c : n->get_children()) self(c, self);
+    };
+    walk(it->second, walk);
+    return os.str();
+}
+
+/// Random MIXED history on an empty reference grove — regular inserts, sorted appends of the running maximum,
+/// sorted bulk runs, removals, all over a handful of coordinates so that most keys are tied — recording after every
+/// few steps the whole chain (one wide query) and the real tree's shape.
+static std::vector<std::string> write_mixed_script(int order, std::uint64_t seed, int steps) {
+    std::mt19937_64 rng(seed);
+    rst::grove<rdt::interval, int> g(order);
+    std::vector<std::string> script;
+    const char* names[] = {"a", "b"};
+    struct live { std::vector<std::pair<rdt::key<rdt::interval, int>*, int>> keys; std::size_t top = 0; };
+    live state[2];
+    int next_id = 0;
+    auto line = [&](const char* op, const char* index, std::size_t s, std::size_t e, int id) {
+        std::ostringstream os;
+        os << op << ' ' << index << " . " << s << ' ' << e << ' ' << id;
+        script.push_back(os.str());
+    };
+    for (int step = 0; step < steps; ++step) {
+        const int c = static_cast<int>(rng() % 2);
+        live& st = state[c];
+        const unsigned dice = static_cast<unsigned>(rng() % 100);
+        if (dice < 35 || st.keys.empty()) {  // regular insert; coordinates on a coarse grid -> many ties, some above the top
+            const std::size_t s = (rng() % (st.top / 10 + 3)) * 10;
+            const int id = next_id++;
+            st.keys.push_back({g.insert_data(names[c], rdt::interval(s, s + 5), id), id});
+            st.top = std::max(st.top, s);
+            line("I", names[c], s, s + 5, id);
+        } else if (dice < 65) {  // sorted append: the running maximum again, or the next grid point
+            const std::size_t s = rng() % 3 == 0 ? st.top + 10 : st.top;
+            const int id = next_id++;
+            st.keys.push_back({g.insert_data(names[c], rdt::interval(s, s + 5), id, rst::sorted), id});
+            st.top = s;
+            line("A", names[c], s, s + 5, id);
+        } else if (dice < 72) {  // sorted bulk run onto the tail
+            const std::size_t count = 1 + rng() % (2 * static_cast<std::size_t>(order));
+            std::vector<std::pair<rdt::interval, int>> run;
+            std::ostringstream os;
+            os << "S " << names[c] << ' ' << count;
+            std::size_t s = st.top;
+            for (std::size_t i = 0; i < count; ++i) {
+                if (rng() % 3 == 0) s += 10;
+                run.push_back({rdt::interval(s, s + 5), next_id});
+                os << " . " << s << ' ' << s + 5 << ' ' << next_id++;
+            }
+            auto keys = g.insert_data(names[c], run, rst::sorted, rst::bulk);
+            for (std::size_t i = 0; i < keys.size(); ++i) st.keys.push_back({keys[i], run[i].second});
+            st.top = s;
+            script.push_back(os.str());
+        } else {  // removal of a random live key (sometimes draining most of the index)
+            const int burst = dice > 97 ? static_cast<int>(st.keys.size() * 3 / 4) : 1;
+            for (int b = 0; b < burst && !st.keys.empty(); ++b) {
+                const std::size_t at = rng() % st.keys.size();
+                g.remove_key(names[c], st.keys[at].first);
+                std::ostringstream os;
+                os << "R " << names[c] << ' ' << st.keys[at].second;
+                script.push_back(os.str());
+                st.keys[at] = st.keys.back();
+                st.keys.pop_back();
+            }
+            if (st.keys.empty()) st.top = 0;
+        }
+        if (step % 3 == 2 || step + 1 == steps) {
+            script.push_back(answer_line(g, names[c], rdt::interval(0, 1u << 30)));
+            script.push_back(tree_line(g, names[c]));
+        }
+    }
+    return script;
+}
+
+template <typename RK, typename FK, typename D>
+void live_case(int order, std::uint64_t seed, int n) {
+    std::string stream;
+    const auto script = write_script<RK, D>(order, seed, n, stream);
+    replay<FK, D>(stream, script);
+}
+
+/// row f1: mixed histories, many seeds, small orders (deep trees, constant splits / borrows / merges)
+static void test_mixed_live(bool host_only) {
+    namespace fdt = genogrove_b200::data_type;
+    std::size_t lines = 0;
+    for (int order : {3, 4, 5, 6, 7, 8, 16})
+        for (std::uint64_t seed = 1; seed <= 6; ++seed)
+            lines += replay<fdt::interval, int>(std::string(), write_mixed_script(order, 1000 * static_cast<std::uint64_t>(order) + seed, 1500), nullptr, order, host_only);
+    std::printf("mixed histories%s: %zu lines (%s + tree shape) checked against the live reference\n", host_only ? " (host bookkeeping only)" : "", lines,
+                host_only ? "chain order" : "hit order");
+}
+
+static void test_live() {
+    namespace fdt = genogrove_b200::data_type;
+    test_mixed_live(false);
+    for (int order : {3, 4, 7, 50}) {
+        live_case<rdt::interval, fdt::interval, int>(order, 100 + order, 700);
+        live_case<rdt::genomic_coordinate, fdt::genomic_coordinate, int>(order, 200 + order, 500);
+    }
+    live_case<rdt::interval, fdt::interval, std::string>(5, 31, 400);
+    live_case<rdt::genomic_coordinate, fdt::genomic_coordinate, std::string>(16, 32, 400);
+
+    // load cost: reference deserialize() + leaf-chain walk + upload against load_gg + upload
+    using clock = std::chrono::steady_clock;
+    auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    for (int order : {8, 128}) {
+        const std::size_t n = 1000000;
+        std::mt19937_64 rng(5);
+        std::vector<std::pair<rdt::interval, int>> v;
+        v.reserve(n);
+        std::size_t pos = 0;
+        for (std::size_t i = 0; i < n; ++i) {
+            pos += rng() % 200;
+            v.push_back({rdt::interval(pos, pos + rng() % 3000), static_cast<int>(i)});
+        }
+        rst::grove<rdt::interval, int> g(order);
+        g.insert_data("chr1", v, rst::sorted, rst::bulk);
+        std::ostringstream os(std::ios::binary);
+        g.serialize(os);
+        const std::string stream = os.str();
+        const auto t0 = clock::now();
+        std::istringstream is(stream, std::ios::binary);
+        auto restored = rst::grove<rdt::interval, int>::deserialize(is);
+        const auto t1 = clock::now();
+        binding::device_snapshot<int> snap(restored);
+        const auto t2 = clock::now();
+        fio::gg_stream_info info;
+        std::istringstream is2(stream, std::ios::binary);
+        auto fast = fio::load_gg<fdt::interval, int>(is2, 0, &info);
+        const auto t3 = clock::now();
+        gg_index* h = fast.device_handle();
+        const auto t4 = clock::now();
+        CHECK(h != nullptr && fast.size() == n);
+        // same device content: one batch over both handles
+        const std::size_t nq = 20000;
+        std::vector<std::uint32_t> qc(nq, 0);
+        std::vector<std::uint64_t> qs(nq), qe(nq), off_a(nq + 1), off_b(nq + 1);
+        for (std::size_t i = 0; i < nq; ++i) qs[i] = rng() % (pos + 1000), qe[i] = qs[i] + rng() % 5000;
+        const std::uint32_t *ha = nullptr, *hb = nullptr;
+        std::uint64_t na = 0, nb = 0;
+        CHECK(gg_intersect_batch(snap.handle, qc.data(), qs.data(), qe.data(), nq, off_a.data(), &ha, &na) == GG_OK);
+        std::vector<std::uint32_t> keep(ha, ha + na);
+        CHECK(gg_intersect_batch(h, qc.data(), qs.data(), qe.data(), nq, off_b.data(), &hb, &nb) == GG_OK);
+        CHECK(na == nb && off_a == off_b && std::equal(keep.begin(), keep.end(), hb));
+        bool payloads_equal = true;
+        const auto& chain = fast.chain("chr1");
+        for (std::size_t i = 0; i < n; i += 997) payloads_equal = payloads_equal && chain[i]->get_data() == snap.rank_to_key[0][i]->get_data();
+        CHECK(payloads_equal);
+        std::printf("gg load, 1M keys order %d (%zu blocks, %.1f MB deflated): reference deserialize %.0f ms + chain walk/upload %.0f ms;"
+                    " load_gg %.0f ms (read %.0f, inflate+parse %.0f on %u threads, adopt %.0f) + upload %.0f ms\n",
+                    order, static_cast<std::size_t>(info.ext_block_begin), stream.size() / 1e6, ms(t0, t1), ms(t1, t2), ms(t2, t3), info.read_ms,
+                    info.parse_ms, info.threads, info.adopt_ms, ms(t3, t4));
+    }
+}
+
+static int write_fixtures(const std::string& dir) {
+    auto put = [&](const char* stem, const std::string& stream, const std::vector<std::string>& script) {
+        std::FILE* f = std::fopen((dir + "/" + stem + ".gg").c_str(), "wb");
+        if (f == nullptr) return false;
+        std::fwrite(stream.data(), 1, stream.size(), f);
+        std::fclose(f);
+        f = std::fopen((dir + "/" + stem + ".script").c_str(), "w");
+        if (f == nullptr) return false;
+        for (const auto& l : script) std::fprintf(f, "%s\n", l.c_str());
+        std::fclose(f);
+        std::printf("%s: %zu stream bytes, %zu script lines\n", stem, stream.size(), script.size());
+        return true;
+    };
+    std::string stream;
+    bool ok = true;
+    for (int order : {3, 4, 5, 8}) {
+        const std::string stem = "mixed_o" + std::to_string(order);
+        std::FILE* f = std::fopen((dir + "/" + stem + ".script").c_str(), "w");
+        if (f == nullptr) return 1;
+        const auto script = write_mixed_script(order, 77 + static_cast<std::uint64_t>(order), 400);
+        for (const auto& l : script) std::fprintf(f, "%s\n", l.c_str());
+        std::fclose(f);
+        std::printf("%s: %zu script lines\n", stem.c_str(), script.size());
+    }
+    auto s1 = write_script<rdt::interval, int>(3, 11, 120, stream);
+    ok = ok && put("interval_int_o3", stream, s1);
+    auto s2 = write_script<rdt::interval, int>(32, 12, 400, stream);
+    ok = ok && put("interval_int_o32", stream, s2);
+    auto s3 = write_script<rdt::interval, std::string>(5, 13, 150, stream);
+    ok = ok && put("interval_str_o5", stream, s3);
+    auto s4 = write_script<rdt::genomic_coordinate, int>(4, 14, 150, stream);
+    ok = ok && put("gcoord_int_o4", stream, s4);
+    auto s5 = write_script<rdt::genomic_coordinate, std::string>(16, 15, 300, stream);
+    ok = ok && put("gcoord_str_o16", stream, s5);
+    return ok ? 0 : 1;
+}
+}  // namespace ggfast
 #endif
 
-int main() {
+static std::string golden_gg_dir() {
+    if (const char* env = std::getenv("GG_GOLDEN_DIR")) return env;
+    char buf[4096];
+    const ssize_t n = readlink("/proc/self/exe", buf, sizeof(buf) - 1);
+    std::string exe = n > 0 ? std::string(buf, static_cast<std::size_t>(n)) : std::string("tests/cpp/x");
+    return exe.substr(0, exe.rfind('/')) + "/../golden/gg";
+}
+
+int main(int argc, char** argv) {
+#ifdef WITH_REFERENCE
+    if (argc == 3 && std::string(argv[1]) == "--write-gg-fixtures") return ggfast::write_fixtures(argv[2]);
+#endif
+    (void)argc;
+    (void)argv;
     if (gg_device_count() < 1) {
 #ifdef WITH_REFERENCE
         // no GPU: only check that the scenarios' own expectations hold on the unmodified reference
         trace_t ref_only = run_scenarios<reference_api>();
+        ggfast::test_mixed_live(/*host_only=*/true);
         std::printf("no CUDA device: reference-only run, %zu trace lines, %d checks, %d failures\n", ref_only.size(), g_checks, g_failures);
         return g_failures == 0 ? 77 : 1;
 #else
@@ -863,6 +1376,7 @@ int main() {
     test_interval_arithmetic();
     trace_t facade = run_scenarios<facade_api>();
     test_batch_entry_point();
+    ggfast::test_fixtures(golden_gg_dir());
     std::printf("facade scenarios: %zu trace lines\n", facade.size());
 #ifdef WITH_REFERENCE
     const int before = g_failures;
@@ -877,6 +1391,7 @@ int main() {
     CHECK(diff == 0);
     std::printf("reference parity: %zu trace lines compared, %zu differ\n", ref.size(), diff);
     binding::test_reference_binding();
+    ggfast::test_live();
 #endif
     std::printf("%d checks, %d failures\n", g_checks, g_failures);
     return g_failures == 0 ? 0 : 1;
