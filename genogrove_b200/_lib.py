@@ -30,7 +30,7 @@ TIE_INPUT_ORDER, TIE_REVERSE_INPUT, TIE_EXPLICIT = 0, 1, 2
 # every symbol include/gg_b200.h declares (tests check the library exports exactly these)
 EXPORTS = (
     "gg_version", "gg_device_count", "gg_index_create", "gg_index_destroy", "gg_last_error",
-    "gg_index_build", "gg_index_build_device", "gg_index_upload_sorted", "gg_index_get_stats", "gg_index_chrom_counts",
+    "gg_index_build", "gg_index_build_device", "gg_index_upload_sorted", "gg_index_update_chrom", "gg_index_get_stats", "gg_index_chrom_counts",
     "gg_intersect_batch", "gg_intersect_batch_u32", "gg_intersect_batch_compact", "gg_compact_count", "gg_compact_rank",
     "gg_compact_expand", "gg_intersect_count", "gg_intersect_emit",
     "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_last_batch_stats",
@@ -48,7 +48,7 @@ class IndexStats(C.Structure):
         ("n_intervals", C.c_uint64), ("n_chrom", C.c_uint32), ("coord_bytes", C.c_uint32),
         ("n_levels", C.c_uint32), ("fanout", C.c_uint32), ("staged_levels", C.c_uint32),
         ("reserved", C.c_uint32), ("device_bytes", C.c_uint64), ("sort_ms", C.c_double),
-        ("levels_ms", C.c_double), ("total_ms", C.c_double),
+        ("levels_ms", C.c_double), ("total_ms", C.c_double), ("h2d_bytes", C.c_uint64),
     ]
 
 
@@ -103,6 +103,7 @@ def lib():
     L.gg_last_error.restype = C.c_char_p
     L.gg_index_build.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_size_t, C.c_uint32, vp]
     L.gg_index_upload_sorted.argtypes = [vp, vp, vp, vp, C.c_size_t, C.c_uint32]
+    L.gg_index_update_chrom.argtypes = [vp, C.c_uint32, vp, vp, C.c_size_t]
     L.gg_index_get_stats.argtypes = [vp, C.POINTER(IndexStats)]
     L.gg_index_chrom_counts.argtypes = [vp, vp]
     L.gg_intersect_batch.argtypes = [vp, vp, vp, vp, C.c_size_t, vp, C.POINTER(_u32p), _u64p]

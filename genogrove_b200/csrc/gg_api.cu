@@ -82,6 +82,12 @@ struct gg_index {
         }
     } bw;
     int64_t keep_build_workspace = 1;
+    // what the kept workspace says about the snapshot's leaf chains (gg_index_update_chrom splices one chromosome into them):
+    // 0 nothing usable, 1 bw.chrom/start/end ARE the chains (upload_sorted / update_chrom), 2 they are the build input and
+    // chain_perm (inside bw.perm or bw.perm_alt) maps chain rank -> input index
+    int chain_src = 0;
+    const uint32_t* chain_perm = nullptr;
+    int64_t sort_legacy = 0;   // 1 = three-kernel radix passes (histogram, scan, scatter) instead of the onesweep form
     // pinned staging ring for host -> device copies of pageable caller memory (parallel memcpy into it, see staged_h2d)
     static constexpr int kStageSlots = 4;
     static constexpr size_t kStageBytes = 16u << 20;
@@ -635,7 +641,13 @@ template <typename Field, typename Key>
 gg_status sort_by_field(gg_index* idx, const Field* d_field, int nbits, Key* keys_a, Key* keys_b, uint32_t*& perm,
                         uint32_t*& perm_alt, size_t n, RadixWorkspace& ws, cudaStream_t st) {
     if (nbits <= 0 || n == 0) return GG_OK;
-    gather_field_kernel<Field, Key><<<blocks_for(n, 256), 256, 0, st>>>(d_field, perm, keys_a, n);
+    if (radix_uses_onesweep<Key>(n, ws)) {  // gather and count the digits of the gathered keys in one kernel
+        GG_CUDA(cudaMemsetAsync(ws.hist, 0, kOsMaxPasses * kRadix * 4, st));
+        gather_field_hist_kernel<Field, Key><<<onesweep_hist_blocks(n), kOsThreads, 0, st>>>(d_field, perm, keys_a, n, (nbits + 7) / 8, ws.hist);
+        ws.hist_ready = true;
+    } else {
+        gather_field_kernel<Field, Key><<<blocks_for(n, 256), 256, 0, st>>>(d_field, perm, keys_a, n);
+    }
     ws.launches++;
     bool in_alt = false;
     GG_CUDA(radix_sort_pairs<Key>(keys_a, keys_b, perm, perm_alt, n, nbits, ws, st, &in_alt));
@@ -692,10 +704,12 @@ gg_status staged_h2d(gg_index* idx, void* dst, const void* src, size_t bytes, cu
 // dev_input: chrom / start / end / tie_key / rank_to_input are DEVICE pointers (gg_index_build_device).
 gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start, const uint64_t* end,
                      const uint64_t* tie_key, int tie_mode, size_t n, uint32_t n_chrom, uint32_t* rank_to_input,
-                     bool do_sort, bool dev_input = false) {
+                     bool do_sort, bool dev_input = false, bool in_place = false) {
+    // in_place: the chains already sit in the handle's own workspace buffers (gg_index_update_chrom)
     if (!idx) return GG_ERR_INVALID_ARG;
     idx->err.clear();
     idx->built = false;
+    idx->chain_src = 0;
     idx->has_strand = false;
     idx->h2_valid = false;
     if (n_chrom == 0 || n_chrom == GG_NO_CHROM) return fail(idx, GG_ERR_INVALID_ARG, "n_chrom must be in [1, 2^32-2]");
@@ -733,7 +747,9 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     const size_t nn = n ? n : 1;
     BuildTrace trace(st);
     GG_CUDA(cudaEventRecord(e0, st));
-    if (dev_input && n) {
+    if (in_place) {
+        // nothing to fetch
+    } else if (dev_input && n) {
         d_chrom.borrow(chrom, n * 4);
         d_start.borrow(start, n * 8);
         d_end.borrow(end, n * 8);
@@ -748,7 +764,8 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     GG_CUDA(cudaMemsetAsync(d_stats.p, 0, sizeof(BuildStats), st));
     GG_CUDA(cudaMemsetAsync(idx->cnt.p, 0, static_cast<size_t>(n_chrom) * 4, st));
     if (n) {
-        if (!dev_input) {
+        if (!dev_input && !in_place) {
+            idx->istats.h2d_bytes = n * 20 + (tie_mode == GG_TIE_EXPLICIT ? n * 8 : 0);
             gg_status hs_ = staged_h2d(idx, d_chrom.p, chrom, n * 4, st);
             if (hs_ == GG_OK) hs_ = staged_h2d(idx, d_start.p, start, n * 8, st);
             if (hs_ == GG_OK) hs_ = staged_h2d(idx, d_end.p, end, n * 8, st);
@@ -758,7 +775,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
             }
             if (hs_ != GG_OK) return hs_;
         }
-        index_stats_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(),
+        index_stats_kernel<<<std::min<unsigned>(blocks_for(n, 256), 148 * 8), 256, 0, st>>>(d_chrom.as<uint32_t>(), d_start.as<uint64_t>(),
                                                               d_end.as<uint64_t>(), d_tie.as<uint64_t>(), n, n_chrom,
                                                               idx->cnt.as<uint32_t>(), d_stats.as<BuildStats>());
         if (!do_sort)
@@ -805,6 +822,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     GG_CUDA(d_scan.ensure(scan_state_bytes(radix_hist_entries(n))));
     ws.hist = d_hist.as<uint32_t>();
     ws.scan_scratch = d_scan.p;
+    ws.force_legacy = static_cast<int>(idx->sort_legacy);
 
     // narrowed copies of the coordinates (u32 layout) in input order
     const void* src_s = d_start.p;
@@ -989,8 +1007,91 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     idx->istats.sort_ms = ms_sort;
     idx->istats.levels_ms = ms_levels;
     idx->istats.total_ms = ms_total;
+    if (!dev_input && !in_place) idx->istats.h2d_bytes = n * 20 + (tie_mode == GG_TIE_EXPLICIT ? n * 8 : 0);
     idx->built = true;
+    if (idx->keep_build_workspace && (!dev_input || in_place)) {
+        idx->chain_src = do_sort ? 2 : 1;
+        idx->chain_perm = do_sort ? perm : nullptr;
+    }
     return GG_OK;
+}
+
+template <typename T>
+__global__ void chain_gather_kernel(const uint32_t* __restrict__ perm, const T* __restrict__ in, size_t n, T* __restrict__ out) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[perm[i]];
+}
+__global__ void fill_u32_kernel(uint32_t* __restrict__ p, size_t n, uint32_t v) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// gg_index_update_chrom: splice the n_c records of one chromosome into the chains kept on the device and rebuild the levels
+// there.  Only those records cross PCIe (16 B each); everything else is device-to-device at HBM speed.
+gg_status update_chrom_impl(gg_index* idx, uint32_t chrom, const uint64_t* start, const uint64_t* end, size_t n_c) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built || idx->chain_src == 0)
+        return fail(idx, GG_ERR_NOT_BUILT, "gg_index_update_chrom needs a snapshot whose chains are still on the device "
+                                           "(gg_index_upload_sorted / gg_index_build with keep_build_workspace = 1)");
+    if (chrom == GG_NO_CHROM || chrom > idx->n_chrom) return fail(idx, GG_ERR_INVALID_ARG, "chrom must be an existing id or n_chrom (append)");
+    if (n_c > 0 && (!start || !end)) return fail(idx, GG_ERR_INVALID_ARG, "null input array");
+    GG_CUDA(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    const uint32_t C_old = idx->n_chrom, C_new = std::max(C_old, chrom + 1);
+    const size_t n_old = idx->n;
+    std::vector<uint64_t> cb(C_old + 1, 0);
+    for (uint32_t c = 0; c < C_old; ++c) cb[c + 1] = cb[c] + idx->h_cnt[c];
+    const size_t before = chrom < C_old ? cb[chrom] : n_old;
+    const size_t old_c = chrom < C_old ? idx->h_cnt[chrom] : 0;
+    const size_t after = n_old - before - old_c;
+    const size_t n_new = before + n_c + after;
+    if (n_new >= 0xFFFFFFF0ull) return fail(idx, GG_ERR_CAPACITY, "more than 2^32-16 intervals per handle");
+    gg_index::BuildWs& w = idx->bw;
+    DeviceBuf t_chrom, t_start, t_end;
+    const size_t nn = n_new ? n_new : 1;
+    GG_CUDA(t_chrom.ensure(nn * 4));
+    GG_CUDA(t_start.ensure(nn * 8));
+    GG_CUDA(t_end.ensure(nn * 8));
+    auto fail_free = [&](cudaError_t e) {
+        t_chrom.release(), t_start.release(), t_end.release();
+        return fail(idx, GG_ERR_CUDA, "gg_index_update_chrom", e);
+    };
+    cudaError_t e = cudaSuccess;
+    auto move = [&](size_t dst, size_t src, size_t m) {  // m records of the old chains -> new position
+        if (m == 0 || e != cudaSuccess) return;
+        if (idx->chain_src == 1) {
+            e = cudaMemcpyAsync(t_chrom.as<uint32_t>() + dst, w.chrom.as<uint32_t>() + src, m * 4, cudaMemcpyDeviceToDevice, st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(t_start.as<uint64_t>() + dst, w.start.as<uint64_t>() + src, m * 8, cudaMemcpyDeviceToDevice, st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(t_end.as<uint64_t>() + dst, w.end.as<uint64_t>() + src, m * 8, cudaMemcpyDeviceToDevice, st);
+        } else {  // chains = build input gathered through the chain permutation
+            chain_gather_kernel<uint32_t><<<blocks_for(m, 256), 256, 0, st>>>(idx->chain_perm + src, w.chrom.as<uint32_t>(), m, t_chrom.as<uint32_t>() + dst);
+            chain_gather_kernel<uint64_t><<<blocks_for(m, 256), 256, 0, st>>>(idx->chain_perm + src, w.start.as<uint64_t>(), m, t_start.as<uint64_t>() + dst);
+            chain_gather_kernel<uint64_t><<<blocks_for(m, 256), 256, 0, st>>>(idx->chain_perm + src, w.end.as<uint64_t>(), m, t_end.as<uint64_t>() + dst);
+            e = cudaGetLastError();
+        }
+    };
+    move(0, 0, before);
+    move(before + n_c, before + old_c, after);
+    if (e != cudaSuccess) return fail_free(e);
+    if (n_c) {
+        gg_status hs = staged_h2d(idx, t_start.as<uint64_t>() + before, start, n_c * 8, st);
+        if (hs == GG_OK) hs = staged_h2d(idx, t_end.as<uint64_t>() + before, end, n_c * 8, st);
+        if (hs != GG_OK) {
+            t_chrom.release(), t_start.release(), t_end.release();
+            return hs;
+        }
+        fill_u32_kernel<<<blocks_for(n_c, 256), 256, 0, st>>>(t_chrom.as<uint32_t>() + before, n_c, chrom);
+    }
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return fail_free(e);
+    // the new chains become the workspace's input arrays, then the ordinary sorted-upload build runs on them in place
+    w.chrom.release(), w.start.release(), w.end.release();
+    w.chrom = t_chrom, w.start = t_start, w.end = t_end;  // (ownership moves: the temporaries are not released)
+    gg_status bs = build_impl(idx, w.chrom.as<uint32_t>(), w.start.as<uint64_t>(), w.end.as<uint64_t>(), nullptr, GG_TIE_INPUT_ORDER,
+                              n_new, C_new, nullptr, /*do_sort=*/false, /*dev_input=*/false, /*in_place=*/true);
+    if (bs == GG_OK) idx->istats.h2d_bytes = n_c * 16;
+    return bs;
 }
 
 // ------------------------------------------------------------------------------------------ device path
@@ -1591,6 +1692,10 @@ gg_status gg_index_upload_sorted(gg_index* idx, const uint32_t* chrom, const uin
     return build_impl(idx, chrom, start, end, nullptr, GG_TIE_INPUT_ORDER, n, n_chrom, nullptr, false);
 }
 
+gg_status gg_index_update_chrom(gg_index* idx, uint32_t chrom, const uint64_t* start, const uint64_t* end, size_t n) {
+    return update_chrom_impl(idx, chrom, start, end, n);
+}
+
 gg_status gg_index_get_stats(const gg_index* idx, gg_index_stats* out) {
     if (!idx || !out) return GG_ERR_INVALID_ARG;
     if (!idx->built) return GG_ERR_NOT_BUILT;
@@ -1902,10 +2007,13 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "emit_tma" && value >= 0 && value <= 2) idx->emit_tma = value;
     else if (k == "keep_build_workspace" && (value == 0 || value == 1)) {
         idx->keep_build_workspace = value;
-        if (!value)
+        if (!value) {
             for (auto* b : idx->bw.all()) b->release();
+            idx->chain_src = 0;
+        }
     }
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
+    else if (k == "sort_legacy" && (value == 0 || value == 1)) idx->sort_legacy = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;

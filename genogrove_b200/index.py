@@ -87,6 +87,11 @@ class DeviceIndex:
         c, s, e = _arr(chrom, np.uint32), _arr(start, np.uint64), _arr(end, np.uint64)
         self._check(self._L.gg_index_upload_sorted(self._h, _ptr(c), _ptr(s), _ptr(e), len(c), n_chrom))
 
+    def update_chrom(self, chrom: int, start, end):
+        """Replace one chromosome's leaf chain in the snapshot (chain order); only these records are uploaded."""
+        s, e = _arr(start, np.uint64), _arr(end, np.uint64)
+        self._check(self._L.gg_index_update_chrom(self._h, int(chrom), _ptr(s), _ptr(e), len(s)))
+
     def stats(self) -> IndexStats:
         st = IndexStats()
         self._check(self._L.gg_index_get_stats(self._h, C.byref(st)))

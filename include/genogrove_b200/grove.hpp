@@ -358,7 +358,7 @@ class grove {
         key_ptr p = allocate_key(k);
         ch.pending.push_back(p);
         ++leaf_key_count;
-        dirty = true;
+        touch(ch);
         return p;
     }
 
@@ -388,7 +388,7 @@ class grove {
         }
         const std::vector<std::uint32_t> zeros(n, 0u);
         std::vector<std::uint32_t> perm(n);
-        const bool was_empty = indices.empty() && all_pending_empty();
+        const bool was_empty = indices.empty() && next_id == 0;
         if constexpr (stranded) {  // third sort key: the strand's rank (genomic_coordinate.hpp:97-110), then input order
             std::vector<std::uint64_t> tie(n);
             for (std::size_t i = 0; i < n; ++i) tie[i] = key_type::strand_rank(data[i].first.get_strand());
@@ -396,12 +396,77 @@ class grove {
         } else {
             check(gg_index_build(dev.get(), zeros.data(), s.data(), e.data(), nullptr, GG_TIE_INPUT_ORDER, n, 1, perm.data()));
         }
+        ++device_builds;
         dirty = true;  // the handle now holds a snapshot of this batch alone
+        snapshot_valid = false;
         std::vector<key_ptr> inserted;
         inserted.reserve(n);
         for (std::size_t r = 0; r < n; ++r) inserted.push_back(allocate_key(key_t(data[perm[r]].first, data[perm[r]].second)));
         append_sorted_run(index, inserted, /*device_is_current=*/was_empty && !stranded);
         return inserted;
+    }
+
+    /// NEW: unsorted bulk load of SEVERAL indices at once — what a 24-chromosome annotation load is.  On an empty grove
+    /// this is ONE device build (gg_index_build over all indices: radix sort on (index, start, end), levels, max-end
+    /// augmentation) whose snapshot is the grove's: no second upload follows.  The per-index call above sorts each index on
+    /// the device and then has to re-upload everything (24 sorts + 1 upload).  Returns, per entry, the key pointers in
+    /// sorted order.  On a grove that already holds keys it is the per-index loop.
+    template <typename Container>
+    std::vector<std::vector<key_ptr>> insert_data(const std::vector<std::pair<std::string, Container>>& per_index, bulk_t)
+        requires(!std::is_void_v<data_type> && std::ranges::random_access_range<Container> && std::ranges::sized_range<Container>) {
+        std::vector<std::vector<key_ptr>> out(per_index.size());
+        bool one_build = indices.empty() && next_id == 0 && !per_index.empty();
+        std::size_t n = 0;
+        for (std::size_t a = 0; a < per_index.size() && one_build; ++a) {
+            if (std::ranges::size(per_index[a].second) == 0) one_build = false;
+            for (std::size_t b = 0; b < a; ++b)
+                if (per_index[a].first == per_index[b].first) one_build = false;
+            n += std::ranges::size(per_index[a].second);
+        }
+        if (!one_build) {
+            for (std::size_t a = 0; a < per_index.size(); ++a) out[a] = insert_data(per_index[a].first, per_index[a].second, bulk);
+            return out;
+        }
+        need_device();
+        std::vector<std::uint32_t> c(n), perm(n);
+        std::vector<std::uint64_t> s(n), e(n), tie;
+        if constexpr (stranded) tie.resize(n);
+        std::size_t p = 0;
+        for (std::size_t a = 0; a < per_index.size(); ++a)
+            for (const auto& [key_value, data_value] : per_index[a].second) {
+                c[p] = static_cast<std::uint32_t>(a);
+                s[p] = key_value.get_start();
+                e[p] = key_value.get_end();
+                if constexpr (stranded) tie[p] = key_type::strand_rank(key_value.get_strand());
+                ++p;
+            }
+        check(gg_index_build(dev.get(), c.data(), s.data(), e.data(), stranded ? tie.data() : nullptr,
+                             stranded ? GG_TIE_EXPLICIT : GG_TIE_INPUT_ORDER, n, static_cast<std::uint32_t>(per_index.size()), perm.data()));
+        ++device_builds;
+        std::size_t first = 0;  // of this index in the concatenated input, and in perm (grouped by id in id order)
+        for (std::size_t a = 0; a < per_index.size(); ++a) {
+            const Container& data = per_index[a].second;
+            const std::size_t m = std::ranges::size(data);
+            out[a].reserve(m);
+            for (std::size_t r = 0; r < m; ++r) {
+                const auto& rec = data[perm[first + r] - first];
+                out[a].push_back(allocate_key(key_t(rec.first, rec.second)));
+            }
+            append_sorted_run(per_index[a].first, out[a], /*device_is_current=*/false);
+            first += m;
+        }
+        if constexpr (stranded) {
+            std::vector<std::uint8_t> st;
+            st.reserve(n);
+            for (const auto& keys : out)
+                for (const key_ptr k : keys) st.push_back(static_cast<std::uint8_t>(k->get_value().get_strand()));
+            check(gg_index_set_strands(dev.get(), st.data(), st.size()));
+        }
+        for (auto& [name, ch] : indices) ch.dirty = false;  // the build's snapshot IS this grove
+        device_n_chrom = next_id;
+        snapshot_valid = true;
+        dirty = false;
+        return out;
     }
 
     // ------------------------------------------------------------------------------------------ removal
@@ -426,8 +491,12 @@ class grove {
         ch.chain.erase(pos);
         ch.leaf_begin = ch.chain.size() - ch.shape.rightmost_leaf_keys();
         --leaf_key_count;
-        dirty = true;
-        if (ch.chain.empty()) indices.erase(it);  // the reference erases an emptied root (grove_remove.ipp:44-50)
+        touch(ch);
+        if (ch.chain.empty()) {  // the reference erases an emptied root (grove_remove.ipp:44-50)
+            emptied_ids.push_back(ch.id);  // its id is retired: the snapshot keeps it as an empty chromosome
+            chain_by_id[ch.id] = &no_chain();
+            indices.erase(it);
+        }
         return true;
     }
 
@@ -486,8 +555,9 @@ class grove {
         return result;
     }
 
-    /// Id of an index name in the device snapshot, npos_index (== GG_NO_CHROM, "no hits") when absent.  Ids are
-    /// stable while no index is created or emptied.
+    /// Id of an index name in the device snapshot, npos_index (== GG_NO_CHROM, "no hits") when absent.  An id is
+    /// assigned when the index is created and never changes or gets reused while the grove lives: creating, filling or
+    /// emptying OTHER indices does not move it (ids cached before such a change stay valid).
     [[nodiscard]] std::uint32_t index_id(std::string_view index) {
         auto it = indices.find(index);
         if (it == indices.end()) return npos_index;
@@ -586,7 +656,7 @@ class grove {
         ch.lazy_tokens.assign(shape.begin(), shape.end());
         ch.leaf_begin = n - last_leaf;
         leaf_key_count += n;
-        dirty = true;
+        touch(ch);
         return adopted;
     }
     /// pre-order tokens of the tree a sorted bulk insert of n keys builds on an empty index
@@ -627,7 +697,8 @@ class grove {
         std::size_t lazy_bottom_up = 0;
         std::vector<std::uint32_t> lazy_tokens;
         std::size_t lazy_appends = 0;
-        std::uint32_t id = 0;          // chromosome id in the device snapshot
+        std::uint32_t id = 0;          // chromosome id in the device snapshot: assigned at creation, never renumbered
+        bool dirty = true;             // the snapshot does not hold this chain as it is now
     };
     struct handle_deleter {
         void operator()(gg_index* h) const noexcept { gg_index_destroy(h); }
@@ -653,7 +724,19 @@ class grove {
         auto it = indices.find(index);
         if (it != indices.end()) return it->second;
         dirty = true;
-        return indices.emplace(std::string(index), chain_state{order}).first->second;
+        chain_state& ch = indices.emplace(std::string(index), chain_state{order}).first->second;
+        ch.id = next_id++;
+        chain_by_id.push_back(&ch.chain);  // (map nodes do not move: the pointer stays valid until the index is erased)
+        return ch;
+    }
+
+    void touch(chain_state& ch) {
+        ch.dirty = true;
+        dirty = true;
+    }
+    static const std::vector<key_ptr>& no_chain() {
+        static const std::vector<key_ptr> none;
+        return none;
     }
 
     bool all_pending_empty() const {
@@ -729,14 +812,14 @@ class grove {
         ch.chain.insert(ch.chain.begin() + static_cast<std::ptrdiff_t>(sorted_position(ch, k)), k);
         note_sorted_append(ch);
         ++leaf_key_count;
-        dirty = true;
+        touch(ch);
         return k;
     }
 
     /// sorted-bulk: bottom-up build on an empty index (chain = input order, rightmost leaf = last group of the
     /// even distribution, grove.hpp:100-106), else the rightmost-append loop (grove_insert.ipp:106-126).
     void append_sorted_run(std::string_view index, const std::vector<key_ptr>& run, bool device_is_current) {
-        const bool fresh_grove = indices.empty();
+        const bool fresh_grove = indices.empty() && next_id == 0;
         chain_state& ch = chain_for(index);
         flush_pending(ch);
         if (ch.chain.empty()) {
@@ -756,64 +839,101 @@ class grove {
             }
         }
         leaf_key_count += run.size();
-        dirty = true;
+        touch(ch);
         if (device_is_current && fresh_grove) {  // the sort that ordered this batch already left its snapshot on the device
-            ch.id = 0;
-            chain_by_id.assign(1, &ch.chain);
+            ch.dirty = false;
             dirty = false;
+            snapshot_valid = true;
+            device_n_chrom = 1;
         }
     }
 
-    /// Re-flatten the host chains into the device snapshot (gg_index_upload_sorted) when anything changed.
+    /// Bring the device snapshot up to date.  Every index has its own dirty flag: when few of them changed (and they hold
+    /// at most half the keys) only those chains are flattened and uploaded, one gg_index_update_chrom each — the device
+    /// splices them in and rebuilds its levels at HBM speed; otherwise all chains go up in one gg_index_upload_sorted.
     void sync() {
         need_device();
         if (!dirty) return;
-        std::size_t n = 0;
+        std::size_t total = 0, changed = 0, n_changed = 0;
+        std::vector<chain_state*> by_id(next_id, nullptr);
         for (auto& [name, ch] : indices) {
             flush_pending(ch);
-            n += ch.chain.size();
-        }
-        // ids in name order: deterministic and independent of hash-table history
-        std::vector<std::pair<std::string_view, chain_state*>> order_by_name;
-        order_by_name.reserve(indices.size());
-        for (auto& [name, ch] : indices) order_by_name.emplace_back(name, &ch);
-        std::sort(order_by_name.begin(), order_by_name.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
-        std::vector<std::uint32_t> c(n);
-        std::vector<std::uint64_t> s(n), e(n);
-        chain_by_id.clear();
-        std::size_t p = 0;
-        std::uint32_t id = 0;
-        for (auto& [name, chp] : order_by_name) {
-            chp->id = id;
-            chain_by_id.push_back(&chp->chain);
-            for (const key_ptr k : chp->chain) {
-                c[p] = id;
-                s[p] = k->get_value().get_start();
-                e[p] = k->get_value().get_end();
-                ++p;
+            by_id[ch.id] = &ch;
+            total += ch.chain.size();
+            if (ch.dirty) {
+                changed += ch.chain.size();
+                ++n_changed;
             }
-            ++id;
         }
-        check(gg_index_upload_sorted(dev.get(), c.data(), s.data(), e.data(), n, std::max<std::uint32_t>(id, 1u)));
+        auto flatten = [](const chain_state& ch, std::vector<std::uint64_t>& s, std::vector<std::uint64_t>& e) {
+            for (const key_ptr k : ch.chain) {
+                s.push_back(k->get_value().get_start());
+                e.push_back(k->get_value().get_end());
+            }
+        };
+        const std::size_t new_ids = next_id - std::min(next_id, device_n_chrom);
+        if (snapshot_valid && n_changed + emptied_ids.size() + new_ids <= max_partial_updates && 2 * changed <= total) {
+            std::vector<std::uint64_t> s, e;
+            for (const std::uint32_t id : emptied_ids)
+                if (id < device_n_chrom) check(gg_index_update_chrom(dev.get(), id, nullptr, nullptr, 0));
+            for (std::uint32_t id = 0; id < next_id; ++id) {
+                chain_state* ch = by_id[id];
+                if (id < device_n_chrom && (ch == nullptr || !ch->dirty)) continue;
+                s.clear(), e.clear();
+                if (ch != nullptr) flatten(*ch, s, e);  // (an id created and retired between two syncs is appended empty)
+                check(gg_index_update_chrom(dev.get(), id, s.data(), e.data(), s.size()));
+                ++partial_updates;
+            }
+        } else {
+            std::vector<std::uint32_t> c;
+            std::vector<std::uint64_t> s, e;
+            c.reserve(total), s.reserve(total), e.reserve(total);
+            for (std::uint32_t id = 0; id < next_id; ++id) {
+                if (by_id[id] == nullptr) continue;
+                flatten(*by_id[id], s, e);
+                c.resize(s.size(), id);
+            }
+            check(gg_index_upload_sorted(dev.get(), c.data(), s.data(), e.data(), s.size(), std::max<std::uint32_t>(next_id, 1u)));
+            ++full_uploads;
+        }
         if constexpr (stranded) {
-            std::vector<std::uint8_t> st(n);
-            p = 0;
-            for (const auto* chain_ptr : chain_by_id)
-                for (const key_ptr k : *chain_ptr) st[p++] = static_cast<std::uint8_t>(k->get_value().get_strand());
-            check(gg_index_set_strands(dev.get(), st.data(), n));
+            std::vector<std::uint8_t> st;
+            st.reserve(total);
+            for (std::uint32_t id = 0; id < next_id; ++id)
+                if (by_id[id] != nullptr)
+                    for (const key_ptr k : by_id[id]->chain) st.push_back(static_cast<std::uint8_t>(k->get_value().get_strand()));
+            check(gg_index_set_strands(dev.get(), st.data(), st.size()));
         }
+        for (auto& [name, ch] : indices) ch.dirty = false;
+        emptied_ids.clear();
+        device_n_chrom = next_id;
+        snapshot_valid = true;
         dirty = false;
     }
 
+  public:
+    /// how the snapshot was refreshed so far (tests / cost accounting): whole-grove uploads and single-index updates
+    [[nodiscard]] std::size_t full_upload_count() const noexcept { return full_uploads; }
+    [[nodiscard]] std::size_t partial_update_count() const noexcept { return partial_updates; }
+    [[nodiscard]] std::size_t device_build_count() const noexcept { return device_builds; }
+    /// more changed indices than this between two queries -> one whole upload instead (each update rebuilds the levels)
+    std::size_t max_partial_updates = 4;
+
+  private:
     int order;
     std::unique_ptr<gg_index, handle_deleter> dev;
     /// index name -> chain; same key type, hash and insert/erase history as the reference's root_nodes map
     /// (grove.hpp:321), hence the same iteration order for intersect(query) across all indices
     std::unordered_map<std::string, chain_state, string_hash, std::equal_to<>> indices;
-    std::vector<const std::vector<key_ptr>*> chain_by_id;
+    std::vector<const std::vector<key_ptr>*> chain_by_id;  // index id -> chain (retired ids: an empty chain)
     std::deque<key_t> key_storage;
     std::size_t leaf_key_count = 0;
-    bool dirty = true;
+    bool dirty = true;             // some chain differs from the snapshot
+    bool snapshot_valid = false;   // the handle holds a snapshot of THIS grove (not of a lone bulk batch)
+    std::uint32_t next_id = 0;     // ids handed out so far
+    std::uint32_t device_n_chrom = 0;
+    std::vector<std::uint32_t> emptied_ids;
+    std::size_t full_uploads = 0, partial_updates = 0, device_builds = 0;
     std::vector<std::uint32_t> scratch_c;
     std::vector<std::uint64_t> scratch_s, scratch_e, scratch_off;
 };

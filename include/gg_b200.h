@@ -86,6 +86,7 @@ typedef struct gg_index_stats {
     double sort_ms;         /* device time of the radix sorts of the last build */
     double levels_ms;       /* device time of padding + level construction of the last build */
     double total_ms;        /* device time of the last build/upload incl. host<->device copies */
+    uint64_t h2d_bytes;     /* interval records copied host -> device by the last build / upload / update_chrom */
 } gg_index_stats;
 
 typedef struct gg_batch_stats {
@@ -126,6 +127,14 @@ gg_status gg_index_upload_sorted(gg_index* idx, const uint32_t* chrom, const uin
 gg_status gg_index_build_device(gg_index* idx, const uint32_t* d_chrom, const uint64_t* d_start, const uint64_t* d_end,
                                 const uint64_t* d_tie_key, int tie_mode, size_t n, uint32_t n_chrom,
                                 uint32_t* d_rank_to_input);
+/* Replace ONE chromosome of the snapshot (replaces the facade's "any mutation re-uploads everything": the reference's
+ * inserts and removals touch one tree, include/genogrove/structure/grove/grove_insert.ipp:182-274, grove_remove.ipp:24-62).
+ * start / end: the chromosome's n records in leaf-chain order (n = 0 empties it; ids of the other chromosomes do not
+ * move).  chrom may equal the current n_chrom: a new chromosome id is appended.  Only these n records cross PCIe; the
+ * handle splices them into the chain arrays it kept on the device from the last gg_index_upload_sorted / gg_index_build
+ * ("keep_build_workspace" = 1, the default) and rebuilds the levels there.  GG_ERR_NOT_BUILT when no such arrays exist
+ * (workspace dropped, or the snapshot came from gg_index_build_device).  Strands must be set again afterwards. */
+gg_status gg_index_update_chrom(gg_index* idx, uint32_t chrom, const uint64_t* start, const uint64_t* end, size_t n);
 gg_status gg_index_get_stats(const gg_index* idx, gg_index_stats* out);
 /* counts[c] = number of intervals of chromosome c (n_chrom entries) */
 gg_status gg_index_chrom_counts(const gg_index* idx, uint64_t* counts);
@@ -363,6 +372,8 @@ void gg_host_free(void* p);
  * the device-buffer calls for gg_last_batch_stats); "compact_delta_bytes" (1, 2, 4: width the compact call starts with);
  * "keep_build_workspace" (1 [default]: the sort buffers of gg_index_build stay allocated between builds — a facade that
  * re-syncs after every mutation saves 60 % of a rebuild; 0: freed after each build);
+ * "sort_legacy" (0 [default]: onesweep radix passes — one kernel per 8-bit digit with a decoupled look-back; 1: the
+ * three-kernel passes of round 1 (per-CTA histogram, scan, scatter), which builds of 2^30 intervals or more always use);
  * "inject_alloc_failure" (debug: the k-th device allocation from now on fails, to drive the error paths). */
 gg_status gg_set_option(gg_index* idx, const char* key, int64_t value);
 

@@ -754,6 +754,135 @@ static void test_batch_entry_point() {
     CHECK(h.intersect(qv[0], "chr1").get_keys() == b2k0);
 }
 
+// Cost model of the snapshot ("a dirty flag per chromosome"): a multi-index bulk load is ONE device
+// build, a mutation of one index re-uploads that index only (gg_index_update_chrom), index ids never move.
+static void test_snapshot_cost_model() {
+    using interval = facade_api::interval;
+    namespace gst = genogrove_b200::structure;
+    using grove_t = gst::grove<interval, int>;
+    std::mt19937_64 rng(99);
+    const int n_idx = 24;
+    std::vector<std::pair<std::string, std::vector<std::pair<interval, int>>>> load(n_idx);
+    for (int c = 0; c < n_idx; ++c) {
+        load[c].first = "chr" + std::to_string(c + 1);
+        const int m = 2000 + 300 * c;
+        for (int i = 0; i < m; ++i) {
+            const std::size_t s = (rng() % 400000) / 16 * 16;  // duplicates on purpose
+            load[c].second.push_back({interval(s, s + (rng() % 64) * 64), c * 100000 + i});
+        }
+    }
+    grove_t g(8), per_index(8);
+    auto keys = g.insert_data(load, gst::bulk);
+    CHECK(keys.size() == static_cast<std::size_t>(n_idx) && g.device_build_count() == 1);
+    for (auto& [name, v] : load) per_index.insert_data(name, v, gst::bulk);
+    CHECK(per_index.device_build_count() == static_cast<std::size_t>(n_idx));
+    auto same = [&](grove_t& a, grove_t& b, const interval& q, const std::string& name) {
+        auto ra = a.intersect(q, name), rb = b.intersect(q, name);
+        if (ra.get_keys().size() != rb.get_keys().size()) return false;
+        for (std::size_t i = 0; i < ra.get_keys().size(); ++i) {
+            const auto *ka = ra.get_keys()[i], *kb = rb.get_keys()[i];
+            if (!(ka->get_value() == kb->get_value()) || ka->get_data() != kb->get_data()) return false;
+        }
+        return true;
+    };
+    auto sweep = [&](grove_t& a, grove_t& b) {
+        bool ok = true;
+        for (int t = 0; t < 300; ++t) {
+            const std::size_t s = rng() % 400000;
+            ok = ok && same(a, b, interval(s, s + rng() % 5000), load[rng() % n_idx].first);
+        }
+        return ok;
+    };
+    CHECK(sweep(g, per_index));
+    CHECK(g.device_build_count() == 1 && g.full_upload_count() == 0 && g.partial_update_count() == 0);  // the build's snapshot served the queries
+    CHECK(per_index.full_upload_count() == 1);
+    // sorted key order came back per index
+    for (int c = 0; c < n_idx; ++c) {
+        CHECK(keys[c].size() == load[c].second.size());
+        for (std::size_t i = 1; i < keys[c].size(); ++i) CHECK(!(keys[c][i]->get_value() < keys[c][i - 1]->get_value()));
+    }
+
+    // a mutation of chr2 between two chr1 batches: only chr2 goes up again, ids stay put
+    const std::uint32_t id1 = g.index_id("chr1"), id2 = g.index_id("chr2"), id24 = g.index_id("chr24");
+    CHECK(id1 == 0 && id2 == 1 && id24 == 23);
+    std::vector<std::uint32_t> qc(500, id1);
+    std::vector<std::uint64_t> qs(500), qe(500);
+    for (std::size_t i = 0; i < qs.size(); ++i) {
+        qs[i] = rng() % 400000;
+        qe[i] = qs[i] + rng() % 3000;
+    }
+    std::vector<std::vector<grove_t::key_ptr>> before(qs.size());
+    {
+        auto br = g.intersect_batch(qc.data(), qs.data(), qe.data(), qs.size());
+        for (std::size_t i = 0; i < qs.size(); ++i) before[i] = br.get_keys(i);
+    }
+    for (int i = 0; i < 50; ++i) {
+        const std::size_t s = (rng() % 400000) / 16 * 16;
+        g.insert_data("chr2", interval(s, s + 640), 7000000 + i);
+        per_index.insert_data("chr2", interval(s, s + 640), 7000000 + i);
+    }
+    {
+        auto br = g.intersect_batch(qc.data(), qs.data(), qe.data(), qs.size());
+        bool ok = true;
+        for (std::size_t i = 0; i < qs.size(); ++i) ok = ok && br.get_keys(i) == before[i];
+        CHECK(ok);
+    }
+    CHECK(g.partial_update_count() == 1 && g.full_upload_count() == 0);
+    gg_index_stats st{};
+    CHECK(gg_index_get_stats(g.device_handle(), &st) == GG_OK);
+    CHECK(st.h2d_bytes == 16 * g.chain("chr2").size());
+    CHECK(g.index_id("chr1") == id1 && g.index_id("chr2") == id2 && g.index_id("chr24") == id24);
+    CHECK(sweep(g, per_index));
+
+    // a new index is appended (its id is the next one), an emptied index retires its id; nobody else moves
+    g.insert_data("chrM", interval(100, 200), 1);
+    per_index.insert_data("chrM", interval(100, 200), 1);
+    CHECK(g.index_id("chrM") == 24 && g.index_id("chr24") == id24);
+    CHECK(g.intersect(interval(150, 160), "chrM").get_keys().size() == 1);
+    auto victim = g.intersect(interval(0, 1000000), "chr3").get_keys();
+    auto victim2 = per_index.intersect(interval(0, 1000000), "chr3").get_keys();
+    CHECK(victim.size() == load[2].second.size());
+    for (auto* k : victim) CHECK(g.remove_key("chr3", k));
+    for (auto* k : victim2) CHECK(per_index.remove_key("chr3", k));
+    CHECK(g.index_id("chr3") == grove_t::npos_index && g.index_id("chr4") == 3 && g.index_id("chrM") == 24);
+    CHECK(g.intersect(interval(0, 1000000), "chr3").get_keys().empty());
+    CHECK(sweep(g, per_index));
+    g.insert_data("chr3", interval(5, 6), 2);  // the name comes back under a NEW id
+    CHECK(g.index_id("chr3") == 25 && g.intersect(interval(0, 10), "chr3").get_keys().size() == 1);
+    CHECK(g.full_upload_count() == 0);
+    // many indices changed at once -> one whole upload instead of a rebuild per index
+    for (int c = 5; c < 15; ++c) g.insert_data(load[c].first, interval(1, 2), -c);
+    CHECK(g.intersect(interval(0, 3), "chr6").get_keys().size() >= 1);
+    CHECK(g.full_upload_count() == 1);
+
+    // genomic_coordinate keys: the multi-index build leaves a usable stranded snapshot too
+    using gcoord = facade_api::genomic_coordinate;
+    gst::grove<gcoord, int> sg(5), sg_ref(5);
+    std::vector<std::pair<std::string, std::vector<std::pair<gcoord, int>>>> sload(3);
+    const char strands[4] = {'+', '-', '.', '*'};
+    for (int c = 0; c < 3; ++c) {
+        sload[c].first = "s" + std::to_string(c);
+        for (int i = 0; i < 3000; ++i) {
+            const std::size_t s = (rng() % 100000) / 8 * 8;
+            sload[c].second.push_back({gcoord(strands[rng() % 4], s, s + (rng() % 16) * 32), c * 10000 + i});
+        }
+    }
+    sg.insert_data(sload, gst::bulk);
+    for (auto& [name, v] : sload) sg_ref.insert_data(name, v, gst::bulk);
+    bool ok = true;
+    for (int t = 0; t < 400; ++t) {
+        const std::size_t s = rng() % 100000;
+        const gcoord q(strands[rng() % 4], s, s + rng() % 2000);
+        const std::string& name = sload[rng() % 3].first;
+        auto ra = sg.intersect(q, name), rb = sg_ref.intersect(q, name);
+        ok = ok && ra.get_keys().size() == rb.get_keys().size();
+        for (std::size_t i = 0; ok && i < ra.get_keys().size(); ++i)
+            ok = ra.get_keys()[i]->get_value() == rb.get_keys()[i]->get_value() && ra.get_keys()[i]->get_data() == rb.get_keys()[i]->get_data();
+    }
+    CHECK(ok);
+    CHECK(sg.device_build_count() == 1 && sg.full_upload_count() == 0);
+}
+
 // ------------------------------------------------------------------------------------------- .gg fast path
 // a serialized grove (format 0.3) goes to the device through genogrove_b200::io::load_gg, which
 // reads the leaf chain out of the blocks without building a pointer tree.  A "script" is a list of text lines:
@@ -1376,6 +1505,7 @@ int main(int argc, char** argv) {
     test_interval_arithmetic();
     trace_t facade = run_scenarios<facade_api>();
     test_batch_entry_point();
+    test_snapshot_cost_model();
     ggfast::test_fixtures(golden_gg_dir());
     std::printf("facade scenarios: %zu trace lines\n", facade.size());
 #ifdef WITH_REFERENCE

@@ -55,6 +55,68 @@ def test_multi_chrom_shapes(gg, oracle, n_chrom, dup, nested):
     assert np.array_equal(counts, np.bincount(chrom, minlength=n_chrom))
 
 
+@pytest.mark.parametrize("first", ["upload_sorted", "build"])
+def test_update_chrom_splices_one_chromosome(gg, oracle, first):
+    """gg_index_update_chrom: replacing, emptying, growing and appending single chromosomes leaves exactly the snapshot a
+    full gg_index_upload_sorted of the same chains gives, and uploads only the changed chromosome's records."""
+    rng = np.random.default_rng(321)
+    n_chrom = 6
+    chrom, start, end = random_index(rng, 50_000, n_chrom, span=300_000, dup=True, nested=True)
+    order = expected_chain(chrom, start, end)
+    chains = {c: (start[order][chrom[order] == c].copy(), end[order][chrom[order] == c].copy()) for c in range(n_chrom)}
+    idx = gg.DeviceIndex(0)
+    if first == "build":
+        idx.build(chrom, start, end, n_chrom)
+    else:
+        idx.upload_sorted(chrom[order], start[order], end[order], n_chrom)
+
+    def flat():
+        cs = sorted(chains)
+        c = np.concatenate([np.full(len(chains[k][0]), k, np.uint32) for k in cs])
+        return c, np.concatenate([chains[k][0] for k in cs]), np.concatenate([chains[k][1] for k in cs])
+
+    def new_chain(m, wide=False):
+        s = np.sort(rng.integers(0, 300_000, m).astype(np.uint64))
+        if wide:
+            s = s + np.uint64(2**33)
+        return s, s + rng.integers(0, 3000, m).astype(np.uint64)
+
+    steps = [(2, new_chain(20_000)), (0, new_chain(0)), (5, new_chain(7)), (6, new_chain(1000)), (8 - 1, new_chain(33)),
+             (3, new_chain(4000, wide=True)), (3, new_chain(10))]
+    for c, (s_c, e_c) in steps:
+        idx.update_chrom(c, s_c, e_c)
+        chains[c] = (s_c, e_c)
+        st = idx.stats()
+        fc, fs, fe = flat()
+        assert st.h2d_bytes == 16 * len(s_c) and st.n_intervals == len(fc) and st.n_chrom == max(chains) + 1
+        assert st.coord_bytes == (8 if fe.max() >= 2**32 else 4)
+        nc = st.n_chrom
+        q = random_queries(rng, 20_000, nc, span=300_000, extra_chrom=1, wide=bool(st.coord_bytes == 8))
+        coff = np.concatenate([[0], np.cumsum(np.bincount(fc, minlength=nc))]).astype(np.uint64)
+        exp_off, exp_hits = oracle.flat_intersect_batch(fs, fe, coff, *q)
+        off, hits = idx.intersect_batch(*q)
+        assert np.array_equal(off, exp_off) and np.array_equal(hits, exp_hits), (c, len(s_c))
+    idx.set_option("keep_build_workspace", 0)
+    with pytest.raises(Exception):
+        idx.update_chrom(1, *new_chain(5))
+
+
+@pytest.mark.parametrize("legacy", [0, 1])
+@pytest.mark.parametrize("wide", [False, True])
+def test_sort_forms_large(gg, oracle, legacy, wide):
+    """Both radix-sort forms (onesweep passes with a decoupled look-back over ~1000 tiles; the three-kernel passes) give the
+    stable (chrom, start, end) permutation on an input with heavy duplicates, constant high digits and a ragged last tile."""
+    rng = np.random.default_rng(77 + legacy + 2 * wide)
+    n = 3_000_017
+    chrom, start, end = random_index(rng, n, 7, span=3_000_000, dup=True, wide=wide)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("sort_legacy", legacy)
+    for tie_mode in (0, 1):
+        perm = idx.build(chrom, start, end, 7, tie_mode=tie_mode)
+        assert np.array_equal(perm, expected_chain(chrom, start, end, tie_mode))
+    _check(idx, chrom, start, end, 7, random_queries(rng, 20_000, 7, span=3_000_000, wide=wide), perm=perm)
+
+
 @pytest.mark.parametrize("tie_mode", [0, 1, 2])
 def test_tie_modes(gg, oracle, tie_mode):
     rng = np.random.default_rng(5 + tie_mode)

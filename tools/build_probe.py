@@ -7,6 +7,9 @@ from genogrove_b200 import DeviceIndex, synth
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
 c, s, e = synth.hg38_intervals(n, 42)
 idx = DeviceIndex(0)
+for kv in os.environ.get("GG_OPTS", "").split(","):  # e.g. GG_OPTS=sort_legacy=1
+    if kv:
+        idx.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 for k in range(3):
     t0 = time.perf_counter()
     idx.build(c, s, e, 24, want_perm=False)
