@@ -35,7 +35,7 @@ EXPORTS = (
     "gg_compact_expand", "gg_intersect_count", "gg_intersect_emit",
     "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_last_batch_stats",
     "gg_host_alloc", "gg_host_free", "gg_set_option",
-    "gg_flanking_batch", "gg_flanking_device",
+    "gg_flanking_batch", "gg_flanking_device", "gg_flanking_batch_stranded", "gg_flanking_stranded_device",
     "gg_index_set_strands", "gg_intersect_batch_stranded", "gg_intersect_stranded_device",
     "gg_group_create", "gg_group_unique_id", "gg_group_create_rank", "gg_group_destroy", "gg_group_last_error",
     "gg_group_world", "gg_group_index", "gg_shard_assign", "gg_group_build", "gg_group_owners", "gg_group_get_stats",
@@ -130,6 +130,8 @@ def lib():
     L.gg_intersect_stranded_device.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_uint64, _u64p, vp]
     L.gg_flanking_batch.argtypes = [vp, vp, vp, vp, C.c_size_t, vp, vp]
     L.gg_flanking_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_int, vp]
+    L.gg_flanking_batch_stranded.argtypes = [vp, vp, vp, vp, vp, C.c_size_t, vp, vp]
+    L.gg_flanking_stranded_device.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_int, vp]
     L.gg_group_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
     L.gg_group_unique_id.argtypes = [vp]
     L.gg_group_create_rank.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, vp]

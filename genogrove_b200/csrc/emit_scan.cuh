@@ -120,13 +120,92 @@ __device__ __forceinline__ uint64_t max_of8(const uint64_t (&e)[8]) {
     return max(max(max(e[0], e[1]), max(e[2], e[3])), max(max(e[4], e[5]), max(e[6], e[7])));
 }
 
+// ---- warp-cooperative walk (skewed hit lists: GENCODE-shaped annotations, one long list among short ones) ------------
+// One lane = one query lets the longest walk of a 32-query tile set the pace (cfg3, ncu: 6 of 32 threads active per
+// instruction).  Here the whole warp finishes ONE query: a coalesced load of 32 group maxima (M8: max end of every aligned
+// group of 8 level-0 slots) covers 256 slots per step, a ballot says which groups can hold a hit, and those are tested four
+// at a time, 8 lanes per group; the in-order write position of every hit falls out of the ballot.  At 1024-slot boundaries
+// 32 entries of the flat per-1024 maxima are tested at once, so a nested query jumps straight to the ancestor that
+// contains it.  Works on absolute level-0 slots (chromosome segments are padded to whole 32-slot nodes, pads hold end = 0
+// and sit above the query's hi or below its chromosome: the walk takes the topmost `rem` hits and exactly count(q) slots of
+// [cb, hi) pass the test, so it never reaches another chromosome).
+template <typename C>
+struct CoopArgs {
+    const C* leaf;          // ends in chain order by absolute level-0 slot
+    const C* m8;            // max end per 8 slots
+    const C* lv1;           // max end per 1024 slots (flat hierarchy level 1), valid when n_lv > 1
+    const uint32_t* cslot;  // [n_chrom + 1] first slot of each chromosome
+    uint32_t n_groups;      // entries of m8
+    int n_lv;
+    int budget;             // per-lane walk steps before a query is handed to the warp (0: per-lane walks only)
+};
+
+// dst[j] = max(src[8 j .. 8 j + 8)); src is padded to whole 32-slot nodes, so every group is complete
+template <typename C>
+__global__ void group8_max_kernel(const C* __restrict__ src, C* __restrict__ dst, uint32_t n_dst) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_dst) return;
+    C e[8];
+    load8(src + static_cast<size_t>(j) * 8, e);
+    dst[j] = max_of8(e);
+}
+
+__device__ __forceinline__ uint32_t strip_top_bit(uint32_t f) { return f != 0 ? f & ~(0x80000000u >> __clz(f)) : 0u; }
+
+// All 32 lanes call this with the same arguments.  Hits are slots < abs_hi with end >= qs, highest first; value stored =
+// slot - cb.  kShared: the next hit goes to shared address sp - 4, downwards.  Else: to dst[rem - 1] down to dst[0],
+// positions at or beyond `room` dropped (hit buffer too small; the caller has flagged it).
+template <typename C, bool kShared>
+__device__ __forceinline__ void coop_walk(const CoopArgs<C>& ca, C qs, uint32_t abs_hi, uint32_t cb, uint32_t sp, uint32_t rem,
+                                          uint32_t* __restrict__ dst, uint64_t room) {
+    const uint32_t lane = lane_id();
+    const uint32_t sub = 3u - (lane >> 3);  // lanes 24-31 take the highest flagged group, 16-23 the next, ...
+    uint32_t r_hi = abs_hi;
+    while (rem != 0 && r_hi != 0) {
+        if ((r_hi & 1023u) == 0 && ca.n_lv > 1) {  // 32 x 1024 slots below r_hi at once
+            const uint32_t i1 = r_hi >> 10;
+            const bool f = lane < i1 && !(ca.lv1[i1 - 1 - lane] < qs);
+            const uint32_t m = __ballot_sync(0xffffffffu, f);
+            if (m == 0) {
+                r_hi = i1 > 32 ? (i1 - 32) << 10 : 0u;
+                continue;
+            }
+            r_hi = (i1 - static_cast<uint32_t>(__ffs(m) - 1)) << 10;
+        }
+        const uint32_t blk = (r_hi - 1) >> 8;  // the 256-slot block holding slot r_hi - 1
+        const uint32_t g = blk * 32 + lane;
+        uint32_t flagged = __ballot_sync(0xffffffffu, g < ca.n_groups && g * 8 < r_hi && !(ca.m8[g] < qs));
+        while (flagged != 0 && rem != 0) {
+            uint32_t f = flagged;
+            if (sub >= 1) f = strip_top_bit(f);
+            if (sub >= 2) f = strip_top_bit(f);
+            if (sub >= 3) f = strip_top_bit(f);
+            const uint32_t slot = (blk * 32 + (31u - __clz(f | 1u))) * 8 + (lane & 7u);
+            const bool hit = f != 0 && slot < r_hi && !(ca.leaf[slot] < qs);
+            const uint32_t hm = __ballot_sync(0xffffffffu, hit);
+            const uint32_t k = __popc((hm >> 1) >> lane);  // hits in higher slots of this step
+            if (hit && k < rem) {
+                if (kShared) sts32(sp - 4u * (k + 1), slot - cb);
+                else if (rem - 1 - k < room) dst[rem - 1 - k] = slot - cb;
+            }
+            const uint32_t nh = min(static_cast<uint32_t>(__popc(hm)), rem);
+            sp -= 4u * nh;
+            rem -= nh;
+            flagged = strip_top_bit(strip_top_bit(strip_top_bit(strip_top_bit(flagged))));
+        }
+        r_hi = blk << 8;
+    }
+}
+
 // emit_walk_staged8 (intersect.cuh) for the dense-batch variant: a group of 8 ranks is first tested as a whole (max end
 // against q.start).  On nested annotations most groups of a visited node hold no hit (cfg3: 4.5 % of the walked ranks are
 // hits, 7 in 10 groups have none) and the 8 compare + predicated store triples are skipped.
+// budget > 0: at most that many loop steps (a skip or a group test each); the walk's state comes back through r_out / sp_out
+// (sp_out > s_begin: unfinished, the warp takes over from rank r_out).
 template <typename C>
 __device__ __forceinline__ void emit_walk_staged8m(const IndexView<C>& ix, const uint32_t* __restrict__ tabp, uint32_t stride,
                                                    int n_levels, uint32_t chrom, C qs, uint32_t hi, uint32_t s_begin,
-                                                   uint32_t s_end) {
+                                                   uint32_t s_end, int budget, uint32_t& r_out, uint32_t& sp_out) {
     const C* __restrict__ leaf_end = ix.M + tabp[chrom];
     const bool has_levels = n_levels > 1;
     const C* __restrict__ node_max = ix.M + tabp[(has_levels ? stride : 0u) + chrom];  // level 1: max end per leaf node
@@ -142,7 +221,8 @@ __device__ __forceinline__ void emit_walk_staged8m(const IndexView<C>& ix, const
         if (ea[0] >= qs) { sp -= 4; sts32(sp, g8); }
         r_hi = g8;
     }
-    while (sp > s_begin && r_hi != 0) {
+    int left = budget > 0 ? budget : 0x7fffffff;
+    while (sp > s_begin && r_hi != 0 && left-- > 0) {
         if ((r_hi & (kFanout - 1)) == 0 && has_levels) {
             const uint32_t b = (r_hi >> kFanoutLog2) - 1;  // leaf node about to be entered from its last key
             if (node_max[b] < qs) {  // nothing in it reaches q.start; at a parent boundary try to skip whole subtrees
@@ -160,6 +240,8 @@ __device__ __forceinline__ void emit_walk_staged8m(const IndexView<C>& ix, const
         }
         r_hi = g8;
     }
+    r_out = r_hi;
+    sp_out = sp;
 }
 
 template <typename C, typename Q, int kWalk, bool kStrand = false, bool kDense = false>
@@ -169,7 +251,7 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                            const uint64_t* __restrict__ block_prefix, uint32_t blk_q, uint64_t* __restrict__ offsets,
                            uint32_t* __restrict__ hits, uint64_t capacity, uint64_t* __restrict__ next_base_out,
                            uint64_t* __restrict__ total_out, uint32_t* __restrict__ err_flag, int tab_in_smem,
-                           StrandArgs sa = StrandArgs{nullptr, nullptr, 0}) {
+                           StrandArgs sa = StrandArgs{nullptr, nullptr, 0}, CoopArgs<C> ca = CoopArgs<C>{}) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStage = emit_stage_entries(kStrand, kDense);
     constexpr uint32_t kStageWords = kStage + kEmitScanSlack;
@@ -247,13 +329,25 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                 if (kStrand) qst = sa.qstrand[q];
             }
             if (wtotal <= kStage) {
-                if (c != 0) {
+                if (kDense && !kStrand) {
+                    // per-lane walks for a bounded number of steps, then the warp finishes the unfinished lists one by one
+                    const uint32_t s_begin = stage_addr + static_cast<uint32_t>(excl) * 4u;
+                    uint32_t r_stop = 0, sp_stop = s_begin;
+                    if (c != 0) emit_walk_staged8m<C>(ix, tabp, stride, n_levels, chrom, qs, hi, s_begin, s_begin + c * 4u, ca.budget, r_stop, sp_stop);
+                    uint32_t pend = ca.budget > 0 ? __ballot_sync(0xffffffffu, sp_stop > s_begin && r_stop != 0) : 0u;
+                    while (pend != 0) {
+                        const int j = __ffs(pend) - 1;
+                        pend &= pend - 1;
+                        const uint32_t cb = ca.cslot[__shfl_sync(0xffffffffu, chrom, j)];
+                        const uint32_t sp_j = __shfl_sync(0xffffffffu, sp_stop, j), sb_j = __shfl_sync(0xffffffffu, s_begin, j);
+                        coop_walk<C, true>(ca, static_cast<C>(__shfl_sync(0xffffffffu, qs, j)), cb + __shfl_sync(0xffffffffu, r_stop, j),
+                                           cb, sp_j, (sp_j - sb_j) >> 2, nullptr, 0);
+                    }
+                } else if (c != 0) {
                     const uint32_t s_begin = stage_addr + static_cast<uint32_t>(excl) * 4u;
                     if (kStrand)
                         emit_walk_staged8_strand<C>(ix, tabp, stride, n_levels, chrom, qs, hi,
                                                     sa.strands + (tabp[chrom] - sa.slot_base), qst, s_begin, s_begin + c * 4u);
-                    else if (kDense)
-                        emit_walk_staged8m<C>(ix, tabp, stride, n_levels, chrom, qs, hi, s_begin, s_begin + c * 4u);
                     else if (kWalk == 16)
                         emit_walk_staged16<C>(ix, tabp, stride, n_levels, chrom, qs, hi, s_begin, s_begin + c * 4u);
                     else
@@ -272,6 +366,19 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                 __syncwarp();
             } else if (kDense && dense_tile(wtotal, cmax, kStage)) {
                 // a dense tile: intersect_emit_dense_kernel finds it from the per-tile totals of the count pass and writes it
+            } else if (kDense && !kStrand && ca.budget > 0) {
+                // too large for the stage, one or a few long lists among short ones: every list by the whole warp, straight to
+                // global memory (a single lane walking a 100 k-hit list alone was the worst case of the per-lane form)
+                uint32_t todo = __ballot_sync(0xffffffffu, c != 0);
+                while (todo != 0) {
+                    const int j = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const uint32_t cb = ca.cslot[__shfl_sync(0xffffffffu, chrom, j)];
+                    const uint64_t o_j = wbase + __shfl_sync(0xffffffffu, excl, j);
+                    const uint64_t room = capacity > o_j ? capacity - o_j : 0ull;
+                    coop_walk<C, false>(ca, static_cast<C>(__shfl_sync(0xffffffffu, qs, j)), cb + __shfl_sync(0xffffffffu, hi, j), cb, 0u,
+                                        __shfl_sync(0xffffffffu, c, j), hits + o_j, room);
+                }
             } else if (c != 0 && wbase + excl + c <= capacity) {  // too large for the stage but not dense: straight to global memory
                 if (kStrand)
                     strand_walk<C, true>(ix, stride, n_levels, chrom, qs, hi, c, sa.strands + (tabp[chrom] - sa.slot_base), qst,

@@ -13,6 +13,7 @@
 // Same directory + finger search as the count pass of intersect (intersect.cuh), QPT consecutive queries per thread.
 #pragma once
 #include "intersect.cuh"
+#include "strand.cuh"
 
 namespace gg {
 
@@ -124,6 +125,125 @@ flanking_kernel(IndexView<C> ix, const uint32_t* __restrict__ ER, uint32_t er_ba
                 }
             }
         }
+    }
+}
+
+// ---- flanking on genomic_coordinate keys with the strand-compatible predicate -----------------------------------
+// grove<genomic_coordinate, T>::flanking(query, index, pred) with the predicate of the reference's own documentation
+// (grove_flanking.ipp:47-54: candidate and query have equal strands or either one is '*'; applied at the leaves,
+// query_engine.hpp:251).  Compatible candidates that do not overlap the query lie entirely before or after it, so the
+// pruning rule (flanking_could_descend, query_engine.hpp:176-199) only ever drops subtrees that cannot improve the
+// result and the answer does not depend on the tree's shape:
+//   successor   = the first key in the chain, among the compatible ones, whose start > q.end
+//   predecessor = the first key in the chain among the compatible ones with the largest end < q.start
+// (checked against the unmodified reference: tests/golden/flanking_strand_cases.json).  With the DEFAULT predicate the
+// reference's answer on genomic_coordinate keys depends on the tree shape — keys that overlap the query in coordinates
+// but not in strand are candidates, and the same pruning rule may or may not reach them (two groves holding the same
+// keys, built by different insert paths, disagree: tests/test_flanking.py) — so that form has no flat equivalent and
+// is not offered.
+// Device form: the per-node strand records of strand.cuh (class counts before each 32-slot node + membership masks, in
+// chain order SN and in sorted-end order EN) turn "next / previous compatible slot" into a mask test on the node at
+// hand and, when that node has none, a binary search over the monotone per-node class counts.
+__device__ __forceinline__ uint32_t node_mask_k(const StrandNode& n, uint32_t cls) {
+    return cls == 0 ? (n.bits[0] | n.bits[1] | n.bits[2] | n.bits[3]) : (n.bits[0] | n.bits[cls]);
+}
+__device__ __forceinline__ uint32_t node_pre_k(const StrandNode& n, uint32_t cls) {
+    return cls == 0 ? (n.pre[0] + n.pre[1] + n.pre[2] + n.pre[3]) : (n.pre[0] + n.pre[cls]);
+}
+__device__ __forceinline__ StrandNode load_node(const StrandNode* __restrict__ N, uint32_t j) {
+    const uint4 a = reinterpret_cast<const uint4*>(N + j)[0], b = reinterpret_cast<const uint4*>(N + j)[1];
+    StrandNode n;
+    n.pre[0] = a.x, n.pre[1] = a.y, n.pre[2] = a.z, n.pre[3] = a.w;
+    n.bits[0] = b.x, n.bits[1] = b.y, n.bits[2] = b.z, n.bits[3] = b.w;
+    return n;
+}
+// first level-0 slot in [from, end) whose key is compatible with class cls (0 = the wildcard query: any key); end is a
+// multiple of 32 (a chromosome's padded segment); kNoRank when there is none
+__device__ __forceinline__ uint32_t first_compatible_from(const StrandNode* __restrict__ N, uint32_t cls, uint32_t from, uint32_t end) {
+    if (from >= end) return kNoRank;
+    uint32_t node = from >> kFanoutLog2;
+    StrandNode n = load_node(N, node);
+    const uint32_t m = node_mask_k(n, cls) & ~((1u << (from & 31u)) - 1u);
+    if (m != 0) return (node << kFanoutLog2) + static_cast<uint32_t>(__ffs(m) - 1);
+    const uint32_t r = node_pre_k(n, cls) + __popc(node_mask_k(n, cls));  // compatible keys before node + 1
+    const uint32_t end_node = end >> kFanoutLog2;
+    if (node + 1 >= end_node || node_pre_k(load_node(N, end_node), cls) == r) return kNoRank;
+    uint32_t lo = node + 1, hi = end_node - 1;  // smallest j with pre[j + 1] > r
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (node_pre_k(load_node(N, mid + 1), cls) > r) hi = mid; else lo = mid + 1;
+    }
+    n = load_node(N, lo);
+    return (lo << kFanoutLog2) + static_cast<uint32_t>(__ffs(node_mask_k(n, cls)) - 1);
+}
+// last level-0 slot in [begin, to) whose key is compatible; begin is a multiple of 32
+__device__ __forceinline__ uint32_t last_compatible_before(const StrandNode* __restrict__ N, uint32_t cls, uint32_t to, uint32_t begin) {
+    if (to <= begin) return kNoRank;
+    const uint32_t node = (to - 1) >> kFanoutLog2, pos = to - (node << kFanoutLog2);  // 1..32 slots of the node are below `to`
+    StrandNode n = load_node(N, node);
+    const uint32_t m = node_mask_k(n, cls) & (pos == 32 ? 0xFFFFFFFFu : ((1u << pos) - 1u));
+    if (m != 0) return (node << kFanoutLog2) + 31u - static_cast<uint32_t>(__clz(m));
+    const uint32_t r = node_pre_k(n, cls);  // compatible keys before this node
+    const uint32_t begin_node = begin >> kFanoutLog2;
+    if (node == begin_node || node_pre_k(load_node(N, begin_node), cls) == r) return kNoRank;
+    uint32_t lo = begin_node, hi = node - 1;  // largest j with pre[j] < r
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (node_pre_k(load_node(N, mid), cls) < r) lo = mid; else hi = mid - 1;
+    }
+    n = load_node(N, lo);
+    return (lo << kFanoutLog2) + 31u - static_cast<uint32_t>(__clz(node_mask_k(n, cls)));
+}
+
+// one query per thread (every step after the two coordinate searches depends on the one before it)
+template <typename C, typename Q>
+__global__ void __launch_bounds__(kQueryThreads)
+flanking_strand_kernel(IndexView<C> ix, const uint32_t* __restrict__ ER, uint32_t er_base, const StrandNode* __restrict__ SN,
+                       const StrandNode* __restrict__ EN, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
+                       const Q* __restrict__ qend, const uint8_t* __restrict__ qstrand, size_t nq,
+                       uint32_t* __restrict__ pred_out, uint32_t* __restrict__ succ_out, uint32_t* __restrict__ err_flag) {
+    const int shift = ix.dir_shift;
+    for (size_t q = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; q < nq; q += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        uint32_t pred = kNoRank, succ = kNoRank;
+        const uint32_t chrom = qchrom[q], qst = qstrand[q];
+        const Q qs_raw = qstart[q], qe_raw = qend[q];
+        uint32_t flags = 0;
+        if (qs_raw > qe_raw) flags |= 1u;
+        if (!strand_valid(qst)) flags |= 4u;
+        if (flags) atomicOr(err_flag, flags);
+        if (flags == 0 && chrom < ix.n_chrom) {
+            const uint32_t cls = qst == '*' ? 0u : strand_class(qst);
+            const uint32_t d0 = ix.dir_off[chrom], last_bin = ix.dir_off[chrom + 1] - d0 - 2;
+            const uint32_t leaf = ix.tab[chrom], cs = leaf - er_base, ce = ix.tab[chrom + 1] - er_base;  // the chromosome's slots
+            Finger<C> fs, fe;
+            fs.valid = fe.valid = false;
+            const uint32_t hi = finger_upper_bound<C>(ix.S + leaf, ix.dirS + d0, last_bin, shift, clamp_coord<C, Q>(qe_raw), fs, true);
+            const uint32_t s_slot = first_compatible_from(SN, cls, cs + hi, ce);
+            if (s_slot != kNoRank) succ = s_slot - cs;
+            if (qs_raw != 0) {
+                const C x = clamp_coord<C, Q>(static_cast<Q>(qs_raw - 1));
+                const uint32_t p = finger_upper_bound<C>(ix.E + leaf, ix.dirE + d0, last_bin, shift, x, fe, true);
+                const uint32_t k_slot = last_compatible_before(EN, cls, cs + p, cs);  // compatible key with the largest end below q.start
+                if (k_slot != kNoRank) {
+                    const C* __restrict__ ends = ix.E + leaf;
+                    uint32_t f = k_slot - cs;
+                    const C v = ends[f];
+                    if (f != 0 && ends[f - 1] == v) {  // duplicated end value: its first slot, then the first compatible key from there
+                        if (v == 0) {
+                            f = 0;
+                        } else {
+                            const C bx = static_cast<C>(v - 1) >> shift;
+                            const uint32_t b = bx > static_cast<C>(last_bin) ? last_bin : static_cast<uint32_t>(bx);
+                            f = bracket_upper_bound<C>(ends, ix.dirE[d0 + b], ix.dirE[d0 + b + 1], static_cast<C>(v - 1), true);
+                        }
+                        f = first_compatible_from(EN, cls, cs + f, ce) - cs;  // exists: k_slot itself is one
+                    }
+                    pred = ER[cs + f];
+                }
+            }
+        }
+        pred_out[q] = pred;
+        succ_out[q] = succ;
     }
 }
 

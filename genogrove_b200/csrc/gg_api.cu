@@ -87,6 +87,8 @@ struct gg_index {
     // chain_perm (inside bw.perm or bw.perm_alt) maps chain rank -> input index
     int chain_src = 0;
     const uint32_t* chain_perm = nullptr;
+    int64_t coop_budget = 32;  // dense-batch emit: per-lane walk steps before the warp finishes a query together (0 = never)
+    int64_t sort_geom = 0;     // onesweep tile geometry (radix_sort.cuh)
     int64_t sort_legacy = 0;   // 1 = three-kernel radix passes (histogram, scan, scatter) instead of the onesweep form
     // pinned staging ring for host -> device copies of pageable caller memory (parallel memcpy into it, see staged_h2d)
     static constexpr int kStageSlots = 4;
@@ -94,6 +96,8 @@ struct gg_index {
     char* h_stage = nullptr;
     cudaEvent_t ev_stage[kStageSlots] = {nullptr, nullptr, nullptr, nullptr};
     DeviceBuf flat[kFlatLevels];  // flat max-end hierarchy over the level-0 slots (emit_tma.cuh)
+    DeviceBuf m8;           // max end per aligned group of 8 level-0 slots (warp-cooperative walk, emit_scan.cuh)
+    uint32_t n_m8 = 0;
     DeviceBuf cslot;        // [n_chrom + 1] first level-0 slot of each chromosome (= tab[0][c] - tab[0][0])
     int n_flat = 0;
     int dir_shift = 0;
@@ -254,6 +258,19 @@ IndexView<C> make_view(const gg_index* idx) {
     v.dir_shift = idx->dir_shift;
     v.base0 = idx->h_tab.empty() ? 0u : idx->h_tab[0];
     return v;
+}
+
+template <typename C>
+CoopArgs<C> make_coop(const gg_index* idx) {
+    CoopArgs<C> a;
+    a.leaf = idx->M.as<C>() + (idx->h_tab.empty() ? 0u : idx->h_tab[0]);
+    a.m8 = idx->m8.as<C>();
+    a.lv1 = idx->flat[1].as<C>();
+    a.cslot = idx->cslot.as<uint32_t>();
+    a.n_groups = idx->n_m8;
+    a.n_lv = idx->n_flat;
+    a.budget = static_cast<int>(idx->coop_budget);
+    return a;
 }
 
 template <typename C>
@@ -518,7 +535,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
         const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (emit_stage_entries(false, dense) + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
         void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
-                     uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs) =
+                     uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs, CoopArgs<C>) =
             dense ? intersect_emit_scan_kernel<C, Q, 8, false, true>
                   : (idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16> : intersect_emit_scan_kernel<C, Q, 8>);
         if (smem > 48 * 1024)
@@ -532,7 +549,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
         kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix,
                                                 static_cast<uint32_t>(kBatchBlockQ), d_off, d_hits, capacity, d_next_base, d_total,
-                                                d_err, tab_in_smem ? 1 : 0, StrandArgs{nullptr, nullptr, 0});
+                                                d_err, tab_in_smem ? 1 : 0, StrandArgs{nullptr, nullptr, 0}, dense ? make_coop<C>(idx) : CoopArgs<C>{});
         GG_CUDA(cudaGetLastError());
         idx->bstats.kernel_launches++;
     }
@@ -823,6 +840,7 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
     ws.hist = d_hist.as<uint32_t>();
     ws.scan_scratch = d_scan.p;
     ws.force_legacy = static_cast<int>(idx->sort_legacy);
+    ws.geom = static_cast<int>(idx->sort_geom);
 
     // narrowed copies of the coordinates (u32 layout) in input order
     const void* src_s = d_start.p;
@@ -937,6 +955,16 @@ gg_status build_impl(gg_index* idx, const uint32_t* chrom, const uint64_t* start
             src = idx->flat[k].as<char>();
             n_src = n_dst;
             if (n_dst <= 1) break;
+        }
+        // max end per group of 8 slots
+        idx->n_m8 = static_cast<uint32_t>(div_up(level0_elems, 8));
+        GG_CUDA(idx->m8.ensure(static_cast<size_t>(idx->n_m8 ? idx->n_m8 : 1) * idx->coord_bytes));
+        if (idx->n_m8) {
+            const char* leaf0 = idx->M.as<char>() + static_cast<size_t>(idx->h_tab[0]) * idx->coord_bytes;
+            if (wide)
+                group8_max_kernel<uint64_t><<<blocks_for(idx->n_m8, 256), 256, 0, st>>>(reinterpret_cast<const uint64_t*>(leaf0), idx->m8.as<uint64_t>(), idx->n_m8);
+            else
+                group8_max_kernel<uint32_t><<<blocks_for(idx->n_m8, 256), 256, 0, st>>>(reinterpret_cast<const uint32_t*>(leaf0), idx->m8.as<uint32_t>(), idx->n_m8);
         }
         GG_CUDA(cudaGetLastError());
     }
@@ -2014,6 +2042,8 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     }
     else if (k == "fused_regs40" && (value == 0 || value == 1)) idx->fused_regs40 = value;
     else if (k == "sort_legacy" && (value == 0 || value == 1)) idx->sort_legacy = value;
+    else if (k == "sort_geom" && value >= 0 && value <= 2) idx->sort_geom = value;
+    else if (k == "coop_budget" && value >= 0 && value <= 1000000) idx->coop_budget = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;
@@ -2044,8 +2074,33 @@ gg_status launch_flanking(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
     return GG_OK;
 }
 
+template <typename C, typename Q>
+gg_status launch_flanking_strand(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, const Q* d_end, const uint8_t* d_strand,
+                                 size_t nq, uint32_t* d_pred, uint32_t* d_succ, uint32_t* d_err, cudaStream_t st) {
+    if (nq == 0) return GG_OK;
+    int per_sm = 0;
+    GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, flanking_strand_kernel<C, Q>, kQueryThreads, 0));
+    const unsigned grid = static_cast<unsigned>(std::min<size_t>(div_up(nq, kQueryThreads), static_cast<size_t>(idx->sm_count) * std::max(per_sm, 1)));
+    flanking_strand_kernel<C, Q><<<grid, kQueryThreads, 0, st>>>(make_view<C>(idx), idx->ER.as<uint32_t>(), idx->er_base, idx->SN.as<StrandNode>(),
+                                                                idx->EN.as<StrandNode>(), d_chrom, d_start, d_end, d_strand, nq, d_pred, d_succ, d_err);
+    GG_CUDA(cudaGetLastError());
+    return GG_OK;
+}
+
+// d_strand != nullptr: genomic_coordinate keys with the strand-compatible predicate (flanking_strand_kernel)
 gg_status dispatch_flanking(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, int q_bytes,
-                            size_t nq, uint32_t* d_pred, uint32_t* d_succ, uint32_t* d_err, cudaStream_t st) {
+                            size_t nq, uint32_t* d_pred, uint32_t* d_succ, uint32_t* d_err, cudaStream_t st,
+                            const uint8_t* d_strand = nullptr) {
+    if (d_strand) {
+        if (idx->coord_bytes == 8)
+            return launch_flanking_strand<uint64_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start),
+                                                              static_cast<const uint64_t*>(d_end), d_strand, nq, d_pred, d_succ, d_err, st);
+        if (q_bytes == 8)
+            return launch_flanking_strand<uint32_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start),
+                                                              static_cast<const uint64_t*>(d_end), d_strand, nq, d_pred, d_succ, d_err, st);
+        return launch_flanking_strand<uint32_t, uint32_t>(idx, d_chrom, static_cast<const uint32_t*>(d_start),
+                                                          static_cast<const uint32_t*>(d_end), d_strand, nq, d_pred, d_succ, d_err, st);
+    }
     if (idx->coord_bytes == 8)
         return launch_flanking<uint64_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start),
                                                    static_cast<const uint64_t*>(d_end), nq, d_pred, d_succ, d_err, st);
@@ -2059,29 +2114,51 @@ gg_status dispatch_flanking(gg_index* idx, const uint32_t* d_chrom, const void* 
 
 extern "C" {
 
-gg_status gg_flanking_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
-                             int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync, void* stream) {
+static gg_status flanking_check(gg_index* idx, cudaStream_t st) {
+    uint32_t flag = 0;
+    GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
+    GG_CUDA(cudaStreamSynchronize(st));
+    if (flag & 4u) return fail(idx, GG_ERR_INVALID_ARG, "genomic_coordinate: strand must be one of '+', '-', '.', '*'");
+    if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+    return GG_OK;
+}
+
+static gg_status flanking_device_impl(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end, const uint8_t* d_strand,
+                                      bool stranded, int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync, void* stream) {
     if (!idx) return GG_ERR_INVALID_ARG;
     idx->err.clear();
     if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
-    if (nq && (!d_chrom || !d_start || !d_end || !d_pred || !d_succ)) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (stranded && !idx->has_strand) return fail(idx, GG_ERR_NOT_BUILT, "index has no strands (gg_index_set_strands)");
+    if (nq && (!d_chrom || !d_start || !d_end || !d_pred || !d_succ || (stranded && !d_strand))) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
     if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
     if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
     GG_CUDA(cudaSetDevice(idx->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     GG_CUDA(idx->err_flag.ensure(16));
     GG_CUDA(cudaMemsetAsync(idx->err_flag.p, 0, 4, st));
-    gg_status s = dispatch_flanking(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_pred, d_succ, idx->err_flag.as<uint32_t>(), st);
+    gg_status s = dispatch_flanking(idx, d_chrom, d_start, d_end, coord_bytes, nq, d_pred, d_succ, idx->err_flag.as<uint32_t>(), st,
+                                    stranded ? d_strand : nullptr);
     if (s != GG_OK) return s;
-    return sync ? check_query_error(idx, st) : GG_OK;
+    return sync ? flanking_check(idx, st) : GG_OK;
 }
 
-gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
-                            size_t nq, uint32_t* pred, uint32_t* succ) {
+gg_status gg_flanking_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                             int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync, void* stream) {
+    return flanking_device_impl(idx, d_chrom, d_start, d_end, nullptr, false, coord_bytes, nq, d_pred, d_succ, sync, stream);
+}
+gg_status gg_flanking_stranded_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                      const uint8_t* d_strand, int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ,
+                                      int sync, void* stream) {
+    return flanking_device_impl(idx, d_chrom, d_start, d_end, d_strand, true, coord_bytes, nq, d_pred, d_succ, sync, stream);
+}
+
+static gg_status flanking_batch_impl(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                                     const uint8_t* q_strand, bool stranded, size_t nq, uint32_t* pred, uint32_t* succ) {
     if (!idx) return GG_ERR_INVALID_ARG;
     idx->err.clear();
     if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
-    if (nq && (!q_chrom || !q_start || !q_end || !pred || !succ)) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (stranded && !idx->has_strand) return fail(idx, GG_ERR_NOT_BUILT, "index has no strands (gg_index_set_strands)");
+    if (nq && (!q_chrom || !q_start || !q_end || !pred || !succ || (stranded && !q_strand))) return fail(idx, GG_ERR_INVALID_ARG, "null argument");
     GG_CUDA(cudaSetDevice(idx->device));
     cudaStream_t st = idx->stream;
     GG_CUDA(idx->err_flag.ensure(16));
@@ -2106,14 +2183,27 @@ gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64
         GG_CUDA(cudaMemcpyAsync(sl.qc.p, q_chrom + q0, m * 4, cudaMemcpyHostToDevice, sl.st));
         GG_CUDA(cudaMemcpyAsync(sl.qs.p, q_start + q0, m * 8, cudaMemcpyHostToDevice, sl.st));
         GG_CUDA(cudaMemcpyAsync(sl.qe.p, q_end + q0, m * 8, cudaMemcpyHostToDevice, sl.st));
+        if (stranded) {  // (the slot's scan buffer is free in this call: it stages the strand bytes)
+            GG_CUDA(sl.scan.ensure(cap));
+            GG_CUDA(cudaMemcpyAsync(sl.scan.p, q_strand + q0, m, cudaMemcpyHostToDevice, sl.st));
+        }
         s = dispatch_flanking(idx, sl.qc.as<uint32_t>(), sl.qs.p, sl.qe.p, 8, m, sl.cnt.as<uint32_t>(), sl.hi.as<uint32_t>(),
-                              idx->err_flag.as<uint32_t>(), sl.st);
+                              idx->err_flag.as<uint32_t>(), sl.st, stranded ? sl.scan.as<uint8_t>() : nullptr);
         if (s != GG_OK) return s;
         GG_CUDA(cudaMemcpyAsync(pred + q0, sl.cnt.p, m * 4, cudaMemcpyDeviceToHost, sl.st));
         GG_CUDA(cudaMemcpyAsync(succ + q0, sl.hi.p, m * 4, cudaMemcpyDeviceToHost, sl.st));
     }
     for (int i = 0; i < kSlots; ++i) GG_CUDA(cudaStreamSynchronize(idx->slots[i].st));
-    return check_query_error(idx, st);  // synchronises the stream
+    return flanking_check(idx, st);  // synchronises the stream
+}
+
+gg_status gg_flanking_batch(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                            size_t nq, uint32_t* pred, uint32_t* succ) {
+    return flanking_batch_impl(idx, q_chrom, q_start, q_end, nullptr, false, nq, pred, succ);
+}
+gg_status gg_flanking_batch_stranded(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start, const uint64_t* q_end,
+                                     const uint8_t* q_strand, size_t nq, uint32_t* pred, uint32_t* succ) {
+    return flanking_batch_impl(idx, q_chrom, q_start, q_end, q_strand, true, nq, pred, succ);
 }
 
 }  // extern "C"
@@ -2167,7 +2257,7 @@ gg_status launch_stranded(gg_index* idx, const uint32_t* d_chrom, const Q* d_sta
     const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
     kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix,
                                             static_cast<uint32_t>(kBatchBlockQ), d_off, d_hits, capacity, nullptr, nullptr, d_err,
-                                            tab_in_smem ? 1 : 0, StrandArgs{idx->strand.as<uint8_t>(), d_strand, idx->er_base});
+                                            tab_in_smem ? 1 : 0, StrandArgs{idx->strand.as<uint8_t>(), d_strand, idx->er_base}, CoopArgs<C>{});
     GG_CUDA(cudaGetLastError());
     idx->bstats.kernel_launches++;
     if (!idx->s_dense) return GG_OK;

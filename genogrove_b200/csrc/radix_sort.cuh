@@ -120,7 +120,7 @@ template <typename Key>
 struct os_items {  // keys per thread: 48 bytes of keys + payloads either way
     static constexpr int value = sizeof(Key) == 8 ? 12 : 12;  // (16 for u32 keys spills at the 64 registers that 4 CTAs per SM allow)
 };
-constexpr int kOsTileMin = kOsThreads * 12;  // smallest tile of the instantiations (sizes the look-back table)
+constexpr int kOsTileMin = kOsThreads * 8;  // smallest tile of the instantiations (sizes the look-back table)
 constexpr uint32_t kOsFlagAgg = 1u << 30, kOsFlagIncl = 2u << 30, kOsValMask = (1u << 30) - 1u;
 constexpr int kOsWindow = 8;      // look-back words in flight per thread
 constexpr size_t kOsMaxN = 1ull << 30;  // above: three-kernel form (a digit's running count needs 30 bits here)
@@ -218,30 +218,30 @@ static __global__ void __launch_bounds__(kRadix) onesweep_bases_kernel(uint32_t*
     row[threadIdx.x] = before + inc - c;
 }
 
-template <typename Key>
+template <typename Key, int kThreads, int kItems>
 constexpr size_t onesweep_smem_bytes() {
-    return static_cast<size_t>(kOsThreads) * os_items<Key>::value * (sizeof(Key) + 4) + kOsWarps * kRadix * 4 + 2 * kRadix * 4 + 64;
+    return static_cast<size_t>(kThreads) * kItems * (sizeof(Key) + 4) + (kThreads / 32) * kRadix * 4 + 2 * kRadix * 4 + 128;
 }
 
 // One LSD pass over digit (key >> shift) & 255.  bases[d] = number of keys with a smaller digit (whole array);
 // state[tile][d] = look-back word of tile `tile` for digit d (zeroed before the launch); ticket zeroed likewise.
-template <typename Key>
-__global__ void __launch_bounds__(kOsThreads, 4)
+template <typename Key, int kThreads, int kItems, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
 onesweep_pass_kernel(const Key* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, Key* __restrict__ keys_out,
                      uint32_t* __restrict__ vals_out, size_t n, int shift, const uint32_t* __restrict__ bases,
                      uint32_t* __restrict__ ticket, volatile uint32_t* state) {
-    constexpr int kItems = os_items<Key>::value;
-    constexpr uint32_t kTile = kOsThreads * kItems;
+    constexpr int kWarps = kThreads / 32;
+    constexpr uint32_t kTile = kThreads * kItems;
     extern __shared__ __align__(16) unsigned char os_smem[];
     Key* skeys = reinterpret_cast<Key*>(os_smem);
     uint32_t* svals = reinterpret_cast<uint32_t*>(os_smem + static_cast<size_t>(kTile) * sizeof(Key));
     uint32_t(*cnt)[kRadix] = reinterpret_cast<uint32_t(*)[kRadix]>(svals + kTile);
-    uint32_t* lstart = &cnt[0][0] + kOsWarps * kRadix;  // first position of the digit's run in the sorted tile
+    uint32_t* lstart = &cnt[0][0] + kWarps * kRadix;  // first position of the digit's run in the sorted tile
     uint32_t* gdst = lstart + kRadix;                   // global position of that run minus lstart (mod 2^32)
     uint32_t* misc = gdst + kRadix;                     // [0] ticket, [1..8] warp sums of the digit scan
 
     if (threadIdx.x == 0) misc[0] = atomicAdd(ticket, 1u);
-    for (int i = threadIdx.x; i < kOsWarps * kRadix; i += kOsThreads) (&cnt[0][0])[i] = 0;
+    for (int i = threadIdx.x; i < kWarps * kRadix; i += kThreads) (&cnt[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = misc[0];
     const uint32_t warp = threadIdx.x >> 5, lane = lane_id();
@@ -272,19 +272,22 @@ onesweep_pass_kernel(const Key* __restrict__ keys_in, const uint32_t* __restrict
         rank[i] = prev + __popc(peers & lt_mask);
     }
     __syncthreads();
-    // thread t owns digit t: per-warp counts -> exclusive offsets across warps, tile count of the digit
+    // thread t < 256 owns digit t: per-warp counts -> exclusive offsets across warps, tile count of the digit
     const uint32_t t = threadIdx.x;
+    const bool owner = kThreads == kRadix || t < kRadix;
     uint32_t agg = 0;
+    if (owner) {
 #pragma unroll
-    for (int w = 0; w < kOsWarps; ++w) {
-        const uint32_t c = cnt[w][t];
-        cnt[w][t] = agg;
-        agg += c;
+        for (int w = 0; w < kWarps; ++w) {
+            const uint32_t c = cnt[w][t];
+            cnt[w][t] = agg;
+            agg += c;
+        }
     }
     // publish the tile's count of digit t right away; the tiles before this one are added up later, after the tile has
     // been reordered in shared memory — by then most of them have published too and the look-back rarely has to poll
     volatile uint32_t* my_state = state + static_cast<size_t>(tile) * kRadix + t;
-    *my_state = (tile == 0 ? kOsFlagIncl : kOsFlagAgg) | agg;
+    if (owner) *my_state = (tile == 0 ? kOsFlagIncl : kOsFlagAgg) | agg;
     // exclusive scan of the tile's digit counts -> lstart
     uint32_t inc = agg;
 #pragma unroll
@@ -292,14 +295,14 @@ onesweep_pass_kernel(const Key* __restrict__ keys_in, const uint32_t* __restrict
         const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
         if (lane >= static_cast<uint32_t>(d)) inc += o;
     }
-    if (lane == 31) misc[1 + warp] = inc;
+    if (lane == 31 && owner) misc[1 + warp] = inc;
     __syncthreads();
     uint32_t before = 0;
 #pragma unroll
-    for (int w = 0; w < kOsWarps; ++w)
+    for (int w = 0; w < kRadix / 32; ++w)
         if (static_cast<uint32_t>(w) < warp) before += misc[1 + w];
     const uint32_t ls = before + inc - agg;
-    lstart[t] = ls;
+    if (owner) lstart[t] = ls;
     __syncthreads();
     // the tile in sorted order in shared memory
 #pragma unroll
@@ -323,7 +326,7 @@ onesweep_pass_kernel(const Key* __restrict__ keys_in, const uint32_t* __restrict
     // one dependent L2 round trip at a time costs ~30 round trips per tile (the chain back to the nearest finished tile
     // grows like sqrt(tiles in flight)).
     uint32_t excl = 0;
-    if (tile != 0) {
+    if (tile != 0 && owner) {
         int64_t p = static_cast<int64_t>(tile) - 1;  // next tile to account for
         bool done = false;
         while (!done) {
@@ -350,10 +353,10 @@ onesweep_pass_kernel(const Key* __restrict__ keys_in, const uint32_t* __restrict
         }
         *my_state = kOsFlagIncl | (excl + agg);
     }
-    gdst[t] = bases[t] + excl - ls;
+    if (owner) gdst[t] = bases[t] + excl - ls;
     __syncthreads();
     const uint32_t count = n - tbase < kTile ? static_cast<uint32_t>(n - tbase) : kTile;
-    for (uint32_t j = threadIdx.x; j < count; j += kOsThreads) {
+    for (uint32_t j = threadIdx.x; j < count; j += kThreads) {
         const Key key = skeys[j];
         const uint32_t dst = gdst[static_cast<uint32_t>(key >> shift) & 0xFFu] + j;
         keys_out[dst] = key;
@@ -369,6 +372,7 @@ struct RadixWorkspace {
     void* scan_scratch = nullptr;  // scan_state_bytes(radix_hist_entries(n)) (three-kernel form only)
     int launches = 0;
     int force_legacy = 0;        // tests / A-B runs: the three-kernel form for any n
+    int geom = 0;                // onesweep tile: 0 = 256 threads x 12 keys (4 CTAs/SM), 1 = 512 x 12 (2), 2 = 256 x 8 (5)
     bool hist_ready = false;     // the caller filled the digit counts at hist[0 .. 8 x 256) (gather_field_hist_kernel); one sort only
 };
 template <typename Key>
@@ -397,6 +401,35 @@ inline cudaError_t radix_sort_pairs_legacy(Key* keys, Key* keys_alt, uint32_t* v
     return cudaGetLastError();
 }
 
+template <typename Key, int kThreads, int kItems, int kMinBlocks>
+inline cudaError_t onesweep_passes(Key* keys, Key* keys_alt, uint32_t* vals, uint32_t* vals_alt, size_t n, int n_pass,
+                                   RadixWorkspace& ws, cudaStream_t stream, bool* in_alt) {
+    constexpr uint32_t kTile = kThreads * kItems;
+    constexpr size_t kSmem = onesweep_smem_bytes<Key, kThreads, kItems>();
+    auto kern = onesweep_pass_kernel<Key, kThreads, kItems, kMinBlocks>;
+    // (per device, and a group handle may drive several devices from one process: set on every call, it costs microseconds)
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmem));
+    if (e != cudaSuccess) return e;
+    const uint32_t tiles = static_cast<uint32_t>(div_up(n, kTile));
+    uint32_t* ghist = ws.hist;
+    uint32_t* tickets = ws.hist + kOsMaxPasses * kRadix;
+    uint32_t* state = ws.hist + kOsHeadEntries;
+    Key* kin = keys;
+    Key* kout = keys_alt;
+    uint32_t* vin = vals;
+    uint32_t* vout = vals_alt;
+    for (int p = 0; p < n_pass; ++p) {
+        e = cudaMemsetAsync(state, 0, static_cast<size_t>(tiles) * kRadix * 4, stream);
+        if (e != cudaSuccess) return e;
+        kern<<<tiles, kThreads, kSmem, stream>>>(kin, vin, kout, vout, n, 8 * p, ghist + p * kRadix, tickets + p, state);
+        ws.launches += 1;
+        Key* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+        *in_alt = !*in_alt;
+    }
+    return cudaGetLastError();
+}
+
 // Stable sort of (keys, vals) by the low `nbits` bits of keys.  Ping-pongs between (keys, vals) and
 // (keys_alt, vals_alt); returns through *in_alt whether the result ended up in the alt buffers.
 template <typename Key>
@@ -405,16 +438,10 @@ inline cudaError_t radix_sort_pairs(Key* keys, Key* keys_alt, uint32_t* vals, ui
     *in_alt = false;
     if (n == 0 || nbits <= 0) return cudaSuccess;
     if (n >= kOsMaxN || ws.force_legacy) return radix_sort_pairs_legacy<Key>(keys, keys_alt, vals, vals_alt, n, nbits, ws, stream, in_alt);
-    constexpr uint32_t kTile = kOsThreads * os_items<Key>::value;
-    constexpr size_t kSmem = onesweep_smem_bytes<Key>();
-    // (per device, and a group handle may drive several devices from one process: set on every call, it costs microseconds)
-    cudaError_t e = cudaFuncSetAttribute(onesweep_pass_kernel<Key>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmem));
-    if (e != cudaSuccess) return e;
     const int n_pass = (nbits + 7) / 8;
-    const uint32_t tiles = static_cast<uint32_t>(div_up(n, kTile));
     uint32_t* ghist = ws.hist;
     uint32_t* tickets = ws.hist + kOsMaxPasses * kRadix;
-    uint32_t* state = ws.hist + kOsHeadEntries;
+    cudaError_t e;
     if (ws.hist_ready) {  // counts are in place; the tickets behind them still need zeroing
         e = cudaMemsetAsync(tickets, 0, 64 * 4, stream);
         if (e != cudaSuccess) return e;
@@ -427,21 +454,9 @@ inline cudaError_t radix_sort_pairs(Key* keys, Key* keys_alt, uint32_t* vals, ui
     }
     onesweep_bases_kernel<<<n_pass, kRadix, 0, stream>>>(ghist);
     ws.launches += 1;
-    Key* kin = keys;
-    Key* kout = keys_alt;
-    uint32_t* vin = vals;
-    uint32_t* vout = vals_alt;
-    for (int p = 0; p < n_pass; ++p) {
-        e = cudaMemsetAsync(state, 0, static_cast<size_t>(tiles) * kRadix * 4, stream);
-        if (e != cudaSuccess) return e;
-        onesweep_pass_kernel<Key><<<tiles, kOsThreads, kSmem, stream>>>(kin, vin, kout, vout, n, 8 * p, ghist + p * kRadix,
-                                                                        tickets + p, state);
-        ws.launches += 1;
-        Key* tk = kin; kin = kout; kout = tk;
-        uint32_t* tv = vin; vin = vout; vout = tv;
-        *in_alt = !*in_alt;
-    }
-    return cudaGetLastError();
+    if (ws.geom == 1) return onesweep_passes<Key, 512, 12, 2>(keys, keys_alt, vals, vals_alt, n, n_pass, ws, stream, in_alt);
+    if (ws.geom == 2) return onesweep_passes<Key, 256, 8, 5>(keys, keys_alt, vals, vals_alt, n, n_pass, ws, stream, in_alt);
+    return onesweep_passes<Key, 256, 12, 4>(keys, keys_alt, vals, vals_alt, n, n_pass, ws, stream, in_alt);
 }
 
 inline int bits_needed(uint64_t max_value) {

@@ -194,6 +194,21 @@ class DeviceIndex:
         self._check(self._L.gg_flanking_device(self._h, d_chrom, d_start, d_end, coord_bytes, nq, d_pred, d_succ,
                                                1 if sync else 0, stream or None))
 
+    def flanking_batch_stranded(self, q_chrom, q_start, q_end, q_strand):
+        """gg_flanking_batch_stranded: flanking on genomic_coordinate keys with the strand-compatible predicate."""
+        qc, a, b = _arr(q_chrom, np.uint32), _arr(q_start, np.uint64), _arr(q_end, np.uint64)
+        qst = _arr(np.frombuffer(q_strand, dtype=np.uint8) if isinstance(q_strand, (bytes, bytearray)) else q_strand, np.uint8)
+        nq = len(qc)
+        pred = np.empty(nq, dtype=np.uint32)
+        succ = np.empty(nq, dtype=np.uint32)
+        self._check(self._L.gg_flanking_batch_stranded(self._h, _ptr(qc), _ptr(a), _ptr(b), _ptr(qst), nq, _ptr(pred), _ptr(succ)))
+        return pred, succ
+
+    def flanking_stranded_device(self, d_chrom: int, d_start: int, d_end: int, d_strand: int, coord_bytes: int, nq: int,
+                                 d_pred: int, d_succ: int, stream: int = 0, sync: bool = True):
+        self._check(self._L.gg_flanking_stranded_device(self._h, d_chrom, d_start, d_end, d_strand, coord_bytes, nq, d_pred,
+                                                        d_succ, 1 if sync else 0, stream or None))
+
     # ------------------------------------------------------------------ strand-aware intersect (genomic_coordinate)
     def set_strands(self, strands):
         """One strand byte (b'+-.*') per indexed interval in chain order (chromosomes concatenated in id order)."""

@@ -251,6 +251,15 @@ struct sorted_t {};
 struct bulk_t {};
 inline constexpr sorted_t sorted{};
 inline constexpr bulk_t bulk{};
+/// The flanking predicate the reference documents for strand-aware keys (grove_flanking.ipp:47-54): candidate and query
+/// have equal strands, or either one is '*'.  Passed by tag (not as a callable) so that it can run on the device.
+struct strand_compatible_t {
+    template <typename K>
+    constexpr bool operator()(const K& candidate, const K& query) const noexcept {
+        return query.get_strand() == '*' || candidate.get_strand() == '*' || candidate.get_strand() == query.get_strand();
+    }
+};
+inline constexpr strand_compatible_t strand_compatible{};
 /// Tag for a grove WITHOUT a device handle: host bookkeeping only (keys, leaf chains, tree shape — chain(),
 /// shape_tokens()), so that host-side ordering logic can be tested where no GPU exists.  Anything that needs an
 /// overlap computed — intersect, flanking, the device-sorted unsorted bulk — throws device_error: there is no CPU
@@ -632,6 +641,32 @@ class grove {
         requires(!stranded) {
         sync();
         check(gg_flanking_batch(dev.get(), q_index, q_start, q_end, nq, pred, succ));
+    }
+
+    /// grove<genomic_coordinate, T>::flanking(query, index, pred) for pred = strand_compatible (grove_flanking.ipp:47-82):
+    /// nearest same-strand (or wildcard) neighbours on either side.  One gg_flanking_batch_stranded call of one query.
+    /// The default predicate is not offered on these keys: the reference's own answer depends on its tree's shape there
+    /// (see gg_b200.h), so there is nothing well-defined to reproduce.
+    [[nodiscard]] gdt::flanking_query_result<key_type, data_type> flanking(const key_type& query, std::string_view index, strand_compatible_t)
+        requires(stranded) {
+        gdt::flanking_query_result<key_type, data_type> result{};
+        auto it = indices.find(index);
+        if (it == indices.end()) return result;
+        sync();
+        const std::uint32_t c = it->second.id;
+        const std::uint64_t s = query.get_start(), e = query.get_end();
+        const std::uint8_t qst = static_cast<std::uint8_t>(query.get_strand());
+        std::uint32_t pred = GG_NO_RANK, succ = GG_NO_RANK;
+        check(gg_flanking_batch_stranded(dev.get(), &c, &s, &e, &qst, 1, &pred, &succ));
+        if (pred != GG_NO_RANK) result.set_predecessor(it->second.chain[pred]);
+        if (succ != GG_NO_RANK) result.set_successor(it->second.chain[succ]);
+        return result;
+    }
+    void flanking_batch(const std::uint32_t* q_index, const std::uint64_t* q_start, const std::uint64_t* q_end,
+                        const std::uint8_t* q_strand, std::size_t nq, std::uint32_t* pred, std::uint32_t* succ, strand_compatible_t)
+        requires(stranded) {
+        sync();
+        check(gg_flanking_batch_stranded(dev.get(), q_index, q_start, q_end, q_strand, nq, pred, succ));
     }
 
     /// Take over one index whose keys are already in LEAF-CHAIN order — what a serialized grove's leaf blocks

@@ -241,6 +241,22 @@ gg_status gg_flanking_device(gg_index* idx, const uint32_t* d_chrom, const void*
                              int coord_bytes, size_t nq, uint32_t* d_pred, uint32_t* d_succ, int sync,
                              void* stream);
 
+/* Flanking on genomic_coordinate keys with the strand-compatible predicate — grove<genomic_coordinate, T>::flanking(query,
+ * index, pred) with the predicate the reference documents (include/genogrove/structure/grove/grove_flanking.ipp:47-54: the
+ * candidate's strand equals the query's, or either is '*'; applied at the leaves, query_engine.hpp:251):
+ *   succ[i] = chain rank of the first compatible key whose start > q.end,
+ *   pred[i] = chain rank of the first key in the chain among the compatible ones with the largest end < q.start.
+ * Needs gg_index_set_strands.  (The reference's DEFAULT predicate on genomic_coordinate keys has no flat equivalent: keys
+ * that overlap in coordinates but not in strand become candidates and whether the pruning rule, query_engine.hpp:176-199,
+ * reaches them depends on the tree's shape — two groves with the same keys disagree, tests/test_flanking.py.)
+ * A strand byte outside "+-.*" -> GG_ERR_INVALID_ARG. */
+gg_status gg_flanking_batch_stranded(gg_index* idx, const uint32_t* q_chrom, const uint64_t* q_start,
+                                     const uint64_t* q_end, const uint8_t* q_strand, size_t nq, uint32_t* pred,
+                                     uint32_t* succ);
+gg_status gg_flanking_stranded_device(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                      const uint8_t* d_strand, int coord_bytes, size_t nq, uint32_t* d_pred,
+                                      uint32_t* d_succ, int sync, void* stream);
+
 /* ---- strand-aware intersect (genomic_coordinate keys) --------------------------------------------- */
 /* Replaces grove<genomic_coordinate, T>::intersect(query, index): hits must overlap in coordinates AND have an equal
  * strand, '*' on either side matching anything (include/genogrove/data_type/genomic_coordinate.hpp:156-160); same

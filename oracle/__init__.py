@@ -122,6 +122,8 @@ def ref_lib():
         L.ref_gc_insert_bulk.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, _u64p, _u64p, _u32p, C.c_size_t, C.c_int]
         L.ref_gc_intersect.argtypes = [C.c_void_p, C.c_uint32, C.c_char, C.c_uint64, C.c_uint64, _u32p, C.c_size_t]
         L.ref_gc_intersect.restype = C.c_size_t
+        L.ref_gc_flanking.argtypes = [C.c_void_p, C.c_uint32, C.c_char, C.c_uint64, C.c_uint64, C.c_int, _u32p]
+        L.ref_gc_flanking.restype = C.c_int
         for name in ("ref_gc_less", "ref_gc_overlaps"):
             getattr(L, name).argtypes = [C.c_char, C.c_uint64, C.c_uint64, C.c_char, C.c_uint64, C.c_uint64]
             getattr(L, name).restype = C.c_int
@@ -255,6 +257,35 @@ def flat_intersect_batch_stranded(start, end, strand, coff, qchrom, qs, qe, qstr
     return offsets, out[: int(offsets[-1])]
 
 
+def flat_flanking_batch_stranded(start, end, strand, coff, qchrom, qs, qe, qstrand):
+    """Flat restatement of grove<genomic_coordinate>::flanking(q, index, strand-compatible predicate)
+    (include/genogrove/structure/grove/grove_flanking.ipp:47-82 -> detail::search_flanking,
+    include/genogrove/structure/grove/query_engine.hpp:238-311; leaf rule :251-281) over chains (start, end, strand byte)
+    concatenated per chromosome: a candidate must be strand-compatible (equal strands, or either '*') and not overlap
+    the query; predecessor = FIRST key in the chain among the candidates with the largest end < q.start, successor =
+    first candidate in the chain whose start > q.end.  Returns (pred u32[Q], succ u32[Q]) per-chromosome ranks, NO_RANK
+    when absent.  Plain numpy, one vectorised pass per query (test infrastructure: small cases only)."""
+    s, e, co, st = _u64(start), _u64(end), _u64(coff), _u8(strand)
+    qc, a, b, qst = _u32(qchrom), _u64(qs), _u64(qe), _u8(qstrand)
+    nq, n_chrom = len(qc), len(co) - 1
+    pred = np.full(nq, NO_RANK, dtype=np.uint32)
+    succ = np.full(nq, NO_RANK, dtype=np.uint32)
+    star = np.uint8(ord("*"))
+    for i in range(nq):
+        if qc[i] >= n_chrom:
+            continue
+        lo, hi = int(co[qc[i]]), int(co[qc[i] + 1])
+        cs, ce, cst = s[lo:hi], e[lo:hi], st[lo:hi]
+        ok = np.ones(hi - lo, dtype=bool) if qst[i] == star else (cst == qst[i]) | (cst == star)
+        before = ok & (ce < a[i])
+        if before.any():
+            pred[i] = int(np.flatnonzero(before & (ce == ce[before].max()))[0])
+        after = np.flatnonzero(ok & (cs > b[i]))
+        if len(after):
+            succ[i] = int(after[0])
+    return pred, succ
+
+
 def gc_chain(start, end, strand, mode: str = "stable"):
     """Leaf-chain order of genomic_coordinate keys: ascending (start, end, strand order); equal keys in input order
     (mode 'stable': sorted bulk) or reverse input order (mode 'regular': one insert_data per record)."""
@@ -292,6 +323,13 @@ class RefGcGrove:
             if k <= cap:
                 return out[:k]
             cap = k
+
+    def flanking(self, chrom: int, strand: str, qs: int, qe: int, strand_predicate: bool = False):
+        """grove.flanking(q, chrom[, strand-compatible predicate]) -> (pred id, succ id), NO_RANK (0xFFFFFFFF) when absent."""
+        out = np.zeros(2, dtype=np.uint32)
+        if self._L.ref_gc_flanking(self._g, chrom, strand.encode(), qs, qe, 1 if strand_predicate else 0, _p32(out)) != 0:
+            raise ValueError("genomic_coordinate: invalid strand or start > end")
+        return int(out[0]), int(out[1])
 
     def close(self):
         if getattr(self, "_g", None):

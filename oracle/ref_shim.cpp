@@ -226,6 +226,25 @@ size_t ref_gc_intersect(ref_gc_grove* r, uint32_t chrom, char strand, uint64_t q
         return static_cast<size_t>(-1);
     }
 }
+// grove<genomic_coordinate>::flanking(q, idx[, pred]) -> payload ids {predecessor, successor}, 0xFFFFFFFF when absent.
+// pred_mode 0: the default predicate (always compatible) — grove_flanking.ipp:33-37; 1: the strand-compatible predicate of
+// the reference's own documentation (grove_flanking.ipp:47-54: equal strands, or either is '*').
+// returns 1 on std::invalid_argument from the query's constructor
+int ref_gc_flanking(ref_gc_grove* r, uint32_t chrom, char strand, uint64_t qs, uint64_t qe, int pred_mode, uint32_t* out2) {
+    try {
+        gdt::genomic_coordinate q(strand, qs, qe);
+        const std::string name = "chr" + std::to_string(chrom);
+        auto compatible = [](const gdt::genomic_coordinate& candidate, const gdt::genomic_coordinate& query) {
+            return query.get_strand() == '*' || candidate.get_strand() == '*' || candidate.get_strand() == query.get_strand();
+        };
+        auto res = pred_mode == 1 ? r->g.flanking(q, name, compatible) : r->g.flanking(q, name);
+        out2[0] = res.get_predecessor() ? res.get_predecessor()->get_data() : 0xFFFFFFFFu;
+        out2[1] = res.get_successor() ? res.get_successor()->get_data() : 0xFFFFFFFFu;
+        return 0;
+    } catch (const std::invalid_argument&) {
+        return 1;
+    }
+}
 int ref_gc_less(char sa, uint64_t as, uint64_t ae, char sb, uint64_t bs, uint64_t be) {
     return gdt::genomic_coordinate(sa, as, ae) < gdt::genomic_coordinate(sb, bs, be) ? 1 : 0;
 }

@@ -660,6 +660,28 @@ void scenario_stranded(trace_t& t) {
                 if (gc::overlaps(kk, gc(st, a, b))) want.insert(d);
             CHECK(std::multiset<int>(got.begin(), got.end()) == want);
         }
+        // flanking with the strand-compatible predicate (grove_flanking.ipp:47-82): nearest same-strand neighbours
+        for (int k = 0; k < 80; ++k) {
+            const std::size_t a = rng() % 42000, b = a + rng() % 300;
+            const gc q(sym[rng() % 4], a, b);
+            auto nn = g.flanking(q, "c", genogrove_b200::structure::strand_compatible);
+            std::ostringstream os;
+            os << "gc_flank q=" << q.to_string() << " pred=";
+            if (nn.get_predecessor()) os << nn.get_predecessor()->get_data(); else os << "null";
+            os << " succ=";
+            if (nn.get_successor()) os << nn.get_successor()->get_data(); else os << "null";
+            t.push_back(os.str());
+            // brute force on the test's own data: largest compatible end below a, smallest compatible start above b
+            std::size_t best_end = 0, best_start = 0;
+            bool hp = false, hs = false;
+            for (const auto& [kk, d] : items) {
+                if (!genogrove_b200::structure::strand_compatible(kk, q)) continue;
+                if (kk.get_end() < a && (!hp || kk.get_end() > best_end)) { hp = true; best_end = kk.get_end(); }
+                if (kk.get_start() > b && (!hs || kk.get_start() < best_start)) { hs = true; best_start = kk.get_start(); }
+            }
+            CHECK((nn.get_predecessor() != nullptr) == hp && (!hp || nn.get_predecessor()->get_value().get_end() == best_end));
+            CHECK((nn.get_successor() != nullptr) == hs && (!hs || nn.get_successor()->get_value().get_start() == best_start));
+        }
     }
 }
 

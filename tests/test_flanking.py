@@ -163,3 +163,164 @@ def test_gpu_flanking_device_buffers_u32():
                         stream=torch.cuda.current_stream().cuda_stream)
     assert np.array_equal(dp.cpu().numpy().view(np.uint32), ep)
     assert np.array_equal(dsu.cpu().numpy().view(np.uint32), es)
+
+
+# ------------------------------------------------------------ genomic_coordinate keys, strand-compatible predicate
+# grove<genomic_coordinate, T>::flanking(q, index, pred) with the predicate the reference documents
+# (include/genogrove/structure/grove/grove_flanking.ipp:47-54).  Golden answers: tests/golden/flanking_strand_cases.json,
+# written by tests/golden/make_golden_flanking_strand.py from the unmodified reference (identical over 4 tree orders x 3
+# insert paths).
+GOLD_S = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "flanking_strand_cases.json")
+with open(GOLD_S) as f:
+    FS = json.load(f)
+
+
+def _gc_arrays(case):
+    it = case["items"]  # [strand, start, end, id], id = chain rank
+    st = np.frombuffer("".join(t[0] for t in it).encode(), dtype=np.uint8)
+    s = np.array([t[1] for t in it], dtype=np.uint64)
+    e = np.array([t[2] for t in it], dtype=np.uint64)
+    q = case["queries"]
+    qc = np.array([t[0] for t in q], dtype=np.uint32)
+    qst = np.frombuffer("".join(t[1] for t in q).encode(), dtype=np.uint8)
+    qs = np.array([t[2] for t in q], dtype=np.uint64)
+    qe = np.array([t[3] for t in q], dtype=np.uint64)
+    exp_p = np.array([NONE if v is None else v for v in case["pred"]], dtype=np.uint32)
+    exp_s = np.array([NONE if v is None else v for v in case["succ"]], dtype=np.uint32)
+    return st, s, e, qc, qst, qs, qe, exp_p, exp_s
+
+
+def test_flanking_strand_golden_shape():
+    assert len(FS["cases"]) >= 7 and sum(len(c["queries"]) for c in FS["cases"]) >= 900
+    assert len(FS["default_predicate_shape_dependence"]) >= 1
+
+
+@pytest.mark.parametrize("case", FS["cases"], ids=[c["name"] for c in FS["cases"]])
+def test_flat_stranded_flanking_oracle_matches_reference_golden(case):
+    st, s, e, qc, qst, qs, qe, exp_p, exp_s = _gc_arrays(case)
+    pred, succ = O.flat_flanking_batch_stranded(s, e, st, [0, len(s)], qc, qs, qe, qst)
+    assert np.array_equal(pred, exp_p)
+    assert np.array_equal(succ, exp_s)
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+def test_default_predicate_on_genomic_coordinate_keys_depends_on_tree_shape():
+    """Why the default predicate has no device form on genomic_coordinate keys: the unmodified reference gives different
+    answers for the SAME keys depending on how they were inserted (the pruning rule of query_engine.hpp:176-199 assumes
+    non-overlapping candidates lie wholly before / after the query, which strand-incompatible overlaps violate)."""
+    rec = FS["default_predicate_shape_dependence"][0]
+    items, (c, st, qs, qe) = rec["items"], rec["query"]
+    a, b = O.RefGcGrove(rec["order"]), O.RefGcGrove(rec["order"])
+    rng = np.random.default_rng(5)
+    seen = set()
+    for trial in range(40):  # some insertion order reproduces a second answer
+        g = O.RefGcGrove(rec["order"])
+        for j in rng.permutation(len(items)):
+            g.insert(0, *items[j])
+        seen.add(g.flanking(c, st, qs, qe))
+        g.close()
+    b.insert_bulk(0, "".join(t[0] for t in items), [t[1] for t in items], [t[2] for t in items], [t[3] for t in items])
+    seen.add(b.flanking(c, st, qs, qe))
+    assert len(seen) >= 2, seen
+    # ... while the strand-compatible predicate gives one answer whatever the shape
+    for j in rng.permutation(len(items)):
+        a.insert(0, *items[j])
+    assert a.flanking(c, st, qs, qe, strand_predicate=True) == b.flanking(c, st, qs, qe, strand_predicate=True)
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+def test_flat_stranded_flanking_oracle_matches_reference_random():
+    rng = np.random.default_rng(123)
+    sym = np.frombuffer(b"*.+-", dtype=np.uint8)
+    for trial in range(5):
+        n = int(rng.integers(1, 400))
+        s = (rng.integers(0, 500, n) * 4).astype(np.uint64)
+        e = s + (rng.integers(0, 12, n) * 4).astype(np.uint64) + np.where(rng.random(n) < 0.05, 800, 0).astype(np.uint64)
+        st = sym[rng.integers(0, 4, n)]
+        keys = sorted({(int(a), int(b), int(c)) for a, b, c in zip(s, e, st)}, key=lambda k: (k[0], k[1], O.STRAND_ORDER[chr(k[2])]))
+        s, e, st = (np.array([k[i] for k in keys], dtype=dt) for i, dt in ((0, np.uint64), (1, np.uint64), (2, np.uint8)))
+        g = O.RefGcGrove(int(rng.choice([3, 6, 32])))
+        for j in rng.permutation(len(s)):
+            g.insert(0, chr(st[j]), int(s[j]), int(e[j]), int(j))
+        qs = rng.integers(0, 2100, 300).astype(np.uint64)
+        qe = qs + rng.integers(0, 200, 300).astype(np.uint64)
+        qst = sym[rng.integers(0, 4, 300)]
+        fp, fsu = O.flat_flanking_batch_stranded(s, e, st, [0, len(s)], np.zeros(300, np.uint32), qs, qe, qst)
+        for i in range(300):
+            assert g.flanking(0, chr(qst[i]), int(qs[i]), int(qe[i]), strand_predicate=True) == (int(fp[i]), int(fsu[i]))
+        g.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", FS["cases"], ids=[c["name"] for c in FS["cases"]])
+def test_gpu_stranded_flanking_matches_reference_golden(case):
+    from genogrove_b200 import DeviceIndex
+    st, s, e, qc, qst, qs, qe, exp_p, exp_s = _gc_arrays(case)
+    idx = DeviceIndex(0)
+    idx.upload_sorted(np.zeros(len(s), np.uint32), s, e, 1)
+    idx.set_strands(st)
+    pred, succ = idx.flanking_batch_stranded(qc, qs, qe, qst)
+    assert np.array_equal(pred, exp_p)
+    assert np.array_equal(succ, exp_s)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("wide", [False, True])
+@pytest.mark.parametrize("skew", ["uniform", "one_strand_runs"])
+def test_gpu_stranded_flanking_matches_oracle_random(wide, skew):
+    """Several chromosomes (one empty, one tiny), duplicated end values, long runs of a single strand (the per-node count
+    search instead of the mask of the node at hand), u64 layout, unknown chromosomes; and the error contract."""
+    import torch
+    from genogrove_b200 import DeviceIndex, GGError, TIE_EXPLICIT
+    rng = np.random.default_rng(77 + wide)
+    n_chrom = 5
+    n = 30_000
+    chrom = rng.integers(0, n_chrom, n).astype(np.uint32)
+    chrom[chrom == 3] = 2
+    chrom[:3] = 3
+    s = (rng.integers(0, 400_000, n) // 8 * 8).astype(np.uint64)
+    e = s + (rng.integers(0, 40, n) * 8).astype(np.uint64)
+    long_ = rng.random(n) < 0.01
+    e[long_] += np.uint64(100_000)
+    sym = np.frombuffer(b"*.+-", dtype=np.uint8)
+    st = sym[rng.integers(0, 4, n)]
+    if skew == "one_strand_runs":  # thousands of consecutive '+' keys: a '-' query has to jump over them
+        st = np.where((s > 100_000) & (s < 300_000), np.uint8(ord("+")), st).astype(np.uint8)
+    if wide:
+        s, e = s + np.uint64(2**34), e + np.uint64(2**34)
+    so = np.array([O.STRAND_ORDER[chr(c)] for c in st], dtype=np.uint64)
+    idx = DeviceIndex(0)
+    perm = idx.build(chrom, s, e, n_chrom, tie_mode=TIE_EXPLICIT, tie_key=(so << np.uint64(32)) | np.arange(n, dtype=np.uint64))
+    idx.set_strands(st[perm])
+    coff = chrom_offsets(chrom, n_chrom)
+    nq = 20_000
+    qc = rng.integers(0, n_chrom + 1, nq).astype(np.uint32)
+    qs = rng.integers(0, 520_000, nq).astype(np.uint64)
+    qs[::50] = 0
+    qe = qs + rng.integers(0, 3000, nq).astype(np.uint64)
+    if wide:
+        qs, qe = qs + np.uint64(2**34), qe + np.uint64(2**34)
+        qs[::50] = 0
+    qst = sym[rng.integers(0, 4, nq)]
+    ep, es = O.flat_flanking_batch_stranded(s[perm], e[perm], st[perm], coff, qc, qs, qe, qst)
+    pred, succ = idx.flanking_batch_stranded(qc, qs, qe, qst)
+    assert np.array_equal(pred, ep) and np.array_equal(succ, es)
+    assert (pred != NONE).sum() > nq // 3 and (succ != NONE).sum() > nq // 3
+    if not wide:  # device-buffer form, u32 coordinates
+        dev = torch.device("cuda:0")
+        t = [torch.from_numpy(a).to(dev) for a in (qc.view(np.int32), qs.astype(np.uint32).view(np.int32),
+                                                   qe.astype(np.uint32).view(np.int32), qst)]
+        d_p = torch.empty(nq, dtype=torch.int32, device=dev)
+        d_s = torch.empty(nq, dtype=torch.int32, device=dev)
+        idx.flanking_stranded_device(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr(), 4, nq, d_p.data_ptr(),
+                                     d_s.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        assert np.array_equal(d_p.cpu().numpy().view(np.uint32), ep) and np.array_equal(d_s.cpu().numpy().view(np.uint32), es)
+    bad = qst.copy()
+    bad[7] = ord("x")
+    with pytest.raises(GGError) as ei:
+        idx.flanking_batch_stranded(qc, qs, qe, bad)
+    assert ei.value.status == 1  # GG_ERR_INVALID_ARG: the reference's std::invalid_argument for a bad strand
+    plain = DeviceIndex(0)
+    plain.build(chrom, s, e, n_chrom)
+    with pytest.raises(GGError):
+        plain.flanking_batch_stranded(qc, qs, qe, qst)  # no strands attached

@@ -537,6 +537,49 @@ def test_long_nested_intervals_use_max_end_pruning(gg, oracle):
     _check(idx, chrom, start, end, 1, (np.zeros(50_000, np.uint32), qs, qs + np.uint64(100)))
 
 
+@pytest.mark.parametrize("budget", [0, 1, 3, 12])
+@pytest.mark.parametrize("wide", [False, True])
+def test_warp_cooperative_walk_on_skewed_lists(gg, oracle, budget, wide):
+    """Dense-batch emit with the warp-cooperative walk (emit_scan.cuh, coop_walk): GENCODE-like nesting — a few very long
+    intervals over many short ones, heavy duplicates, several chromosomes with ragged sizes (256-slot blocks straddle
+    chromosome boundaries), queries at position 0 (pads hold end = 0), lists far larger than the stage (global form) —
+    for per-lane budgets from "always cooperative" to the default, and budget 0 (per-lane only) as the control."""
+    rng = np.random.default_rng(900 + budget + 10 * wide)
+    n_chrom = 5
+    sizes = [70_001, 33, 9_000, 1, 41_237]
+    chrom = np.concatenate([np.full(m, c, np.uint32) for c, m in enumerate(sizes)])
+    n = len(chrom)
+    start = rng.integers(0, 2_000_000, n).astype(np.uint64)
+    ln = rng.integers(0, 300, n).astype(np.uint64)
+    nest = rng.random(n) < 0.01
+    ln[nest] = rng.integers(100_000, 1_900_000, int(nest.sum())).astype(np.uint64)   # genes / transcripts
+    ln[rng.random(n) < 0.0005] = 2_000_000                                            # spans everything after it
+    start = (start // 16) * 16                                                        # duplicates
+    if wide:
+        start = start + np.uint64(2**36)
+    end = start + ln
+    sh = rng.permutation(n)
+    chrom, start, end = chrom[sh], start[sh], end[sh]
+    idx = gg.DeviceIndex(0)
+    idx.set_option("dense_emit", 1)
+    idx.set_option("coop_budget", budget)
+    idx.set_option("fused_kernel", 0)
+    perm = idx.build(chrom, start, end, n_chrom)
+    assert np.array_equal(perm, expected_chain(chrom, start, end))
+    nq = 60_000
+    qc = rng.integers(0, n_chrom + 1, nq).astype(np.uint32)
+    qs = rng.integers(0, 2_100_000, nq).astype(np.uint64)
+    qs[::17] = 0
+    qe = qs + rng.integers(0, 1000, nq).astype(np.uint64)
+    qe[::1001] = qs[::1001] + np.uint64(1_500_000)   # a few enormous lists among short ones: tiles beyond the stage
+    if wide:
+        qs, qe = qs + np.uint64(2**36), qe + np.uint64(2**36)
+        qs[::17] = 0
+    _check(idx, chrom, start, end, n_chrom, (qc, qs, qe))
+    o = np.lexsort((qs, qc))
+    _check(idx, chrom, start, end, n_chrom, (qc[o], qs[o], qe[o]))
+
+
 def test_smoke_entry(gg, oracle):
     import __graft_entry__ as ge
     ge.smoke()

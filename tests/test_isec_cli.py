@@ -118,3 +118,38 @@ def test_isec_gff_and_cross_type_known_answers(tmp_path):
     assert _run(["-q", str(qg), "-t", str(tb)]).stdout == "chr1\t100\t500\n"  # base 500 (1-based) = 0-based 499: inside [100,500)
     qg.write_text("chr1\t.\tx\t0\t5\t.\t+\t.\tID=a\n")
     assert "Invalid GFF coordinates" in _run(["-q", str(qg), "-t", str(tb)], 1).stderr
+
+
+@pytest.mark.gpu
+def test_isec_sam_queries_follow_the_reader_coordinate_rule(tmp_path):
+    """Read-shaped (text SAM) queries: start = POS - 1, end = start + reference bases the CIGAR consumes, closed
+    interval(start, end - 1) ONLY when the record consumes reference (include/genogrove/io/bam_reader.hpp:244-248,283-287;
+    src/io/bam_reader.cpp:261-282).  Records restate tests/io/data/test.sam and tests/io/bamfile-test.cpp:676-765."""
+    t = tmp_path / "target.bed"
+    # targets placed to separate the cases: one base past each expected end must NOT be hit
+    t.write_text("chr1\t999\t1000\nchr1\t1049\t1050\nchr1\t1050\t1051\n"      # read001: 50M at POS 1000 -> [999, 1049)
+                 "chr1\t2039\t2040\nchr1\t2040\t2041\n"                        # read002: 30M10I10M -> 40 ref bases: [1999, 2039)
+                 "chr2\t5053\t5054\nchr2\t5054\t5055\n"                        # read003: 25M5D25M -> 55 ref bases: [4999, 5054)
+                 "chr1\t0\t10\nchr1\t499\t500\nchr1\t999\t1000\n"              # unmapped / hard-clip-only / soft-clip-only ask nothing
+                 "chr3\t100\t400\n")                                           # read006: 10S20M100N20M5H -> 140 ref bases: [199, 339)
+    q = tmp_path / "reads.sam"
+    q.write_text("@HD\tVN:1.6\tSO:coordinate\n@SQ\tSN:chr1\tLN:248956422\n"
+                 "read001\t99\tchr1\t1000\t60\t50M\t=\t1200\t250\tACGT\tIIII\n"
+                 "read002\t0\tchr1\t2000\t30\t30M10I10M\t*\t0\t0\tACGT\tIIII\n"
+                 "read003\t16\tchr2\t5000\t45\t25M5D25M\t*\t0\t0\tACGT\tIIII\n"
+                 "read004\t4\t*\t0\t0\t*\t*\t0\t0\tNNNN\t!!!!\n"
+                 "read_hardclip\t256\tchr1\t500\t60\t100H\t*\t0\t0\t*\t*\n"
+                 "read_softclip\t0\tchr1\t1000\t60\t100S\t*\t0\t0\tAAAA\t!!!!\n"
+                 "read006\t0\tchr3\t200\t60\t10S20M100N20M5H\t*\t0\t0\tAAAA\t!!!!\n")
+    r = _run(["-q", str(q), "-t", str(t)])
+    assert r.stdout == ("chr1\t999\t1000\nchr1\t999\t1000\n"   # read001 hits both [999,1000) targets (equal keys), not [1049,1050)
+                        # read002 covers [1999, 2039): neither [2039,2040) nor [2040,2041)
+                        "chr2\t5053\t5054\n"                   # last base 5053 of read003, not 5054
+                        "chr3\t100\t400\n")
+    # SAM on the target side: hits print RNAME, start, end (0-based half-open)
+    q2 = tmp_path / "q.bed"
+    q2.write_text("chr1\t1040\t1060\nchr3\t338\t339\nchr3\t339\t340\n")
+    assert _run(["-q", str(q2), "-t", str(q)]).stdout == "chr1\t999\t1049\nchr3\t199\t339\n"
+    bad = tmp_path / "bad.sam"
+    bad.write_text("r\t0\tchr1\t10\t60\t5Q\t*\t0\t0\tA\t!\n")
+    assert "Invalid CIGAR" in _run(["-q", str(bad), "-t", str(t)], 1).stderr

@@ -8,7 +8,15 @@
 // calls grove.intersect once per query line; this reads the whole query file into structure-of-arrays buffers and
 // makes ONE grove.intersect_batch call (count -> scan -> emit on the device), then prints from the CSR result.
 //
-//   gg_isec -q query.{bed,gff,gtf} -t target.{bed,gff,gtf} [-o out] [-k order] [-s]   (-s: target is sorted -> sorted inserts)
+//   gg_isec -q query.{bed,gff,gtf,sam} -t target.{bed,gff,gtf,sam} [-o out] [-k order] [-s]   (-s: target is sorted -> sorted inserts)
+//
+// Text SAM (by extension .sam; read-shaped queries, BASELINE configs[3]) follows the reference reader's coordinate rule
+// (src/io/bam_reader.cpp:180-211,261-282, include/genogrove/io/bam_reader.hpp:244-248,283-287): start = POS - 1 (0-based),
+// end = start + the reference bases the CIGAR consumes (M, D, N, =, X; bam_reader.hpp:112-116), half-open; unmapped
+// records (FLAG & 4) are skipped as by the reader's default options; a record becomes the closed
+// interval(start, end - 1) ONLY when it consumes reference (start < end): pure soft-clip ("100S") and hard-clip-only
+// secondary records yield [pos, pos) and ask nothing (tests/io/bamfile-test.cpp:676-765).  A SAM target prints
+// RNAME, start, end (0-based half-open) per hit.
 //
 // GFF/GTF files (by extension .gff / .gff3 / .gtf) are accepted on either side, as in the reference CLI: 1-based
 // inclusive [start, end] becomes interval(start - 1, end - 1) (cli/src/handlers/gff.cpp:22-30,
@@ -119,9 +127,65 @@ static void for_each_gff(const std::string& path, F&& cb) {
     }
 }
 
+static bool is_sam(const std::string& path) { return path.size() >= 4 && path.compare(path.size() - 4, 4, ".sam") == 0; }
+
+// reference bases consumed by a CIGAR string ("*" = none); ops other than MIDNSHP=X are an error like htslib's parser
+static std::size_t cigar_ref_len(std::string_view cigar, std::size_t line_num) {
+    if (cigar == "*") return 0;
+    std::size_t total = 0, len = 0;
+    bool have = false;
+    for (const char ch : cigar) {
+        if (ch >= '0' && ch <= '9') {
+            len = len * 10 + static_cast<std::size_t>(ch - '0');
+            have = true;
+            continue;
+        }
+        if (!have || std::strchr("MIDNSHP=X", ch) == nullptr) throw std::runtime_error("Invalid CIGAR at line " + std::to_string(line_num));
+        if (ch == 'M' || ch == 'D' || ch == 'N' || ch == '=' || ch == 'X') total += len;
+        len = 0;
+        have = false;
+    }
+    if (have) throw std::runtime_error("Invalid CIGAR at line " + std::to_string(line_num));
+    return total;
+}
+
+// text SAM: QNAME FLAG RNAME POS MAPQ CIGAR ... (tab separated); '@' header lines skipped
+template <typename F>
+static void for_each_sam(const std::string& path, F&& cb) {
+    std::ifstream in(path);
+    if (!in) throw std::runtime_error("Failed to open file: " + path);
+    std::string line;
+    std::size_t line_num = 0;
+    while (std::getline(in, line)) {
+        ++line_num;
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        if (line.empty() || line[0] == '@') continue;
+        std::string_view l(line), col[6];
+        std::size_t pos = 0;
+        int k = 0;
+        for (; k < 6 && pos <= l.size(); ++k) {
+            const std::size_t t = l.find('\t', pos);
+            col[k] = l.substr(pos, t == std::string_view::npos ? std::string_view::npos : t - pos);
+            if (t == std::string_view::npos) { ++k; break; }
+            pos = t + 1;
+        }
+        if (k < 6) throw std::runtime_error("Invalid line format at line " + std::to_string(line_num));
+        const std::size_t flag = parse_coord(col[1], line_num);
+        if (flag & 4u) continue;  // unmapped: start == end == 0, skipped by the reader's default options
+        const std::size_t pos1 = parse_coord(col[3], line_num);
+        if (pos1 == 0 || col[2] == "*") continue;  // no position
+        bed3 r{std::string(col[2]), pos1 - 1, pos1 - 1 + cigar_ref_len(col[5], line_num), 0, 0};
+        if (!(r.start < r.end)) continue;  // consumes_reference() == false: no interval to ask with
+        r.lo = r.start;
+        r.hi = r.end - 1;
+        cb(std::move(r));
+    }
+}
+
 template <typename F>
 static void for_each_record(const std::string& path, F&& cb) {
     if (is_gff(path)) for_each_gff(path, cb);
+    else if (is_sam(path)) for_each_sam(path, cb);
     else for_each_bed(path, cb);
 }
 
