@@ -244,7 +244,11 @@ __device__ __forceinline__ void emit_walk_staged8m(const IndexView<C>& ix, const
     sp_out = sp;
 }
 
-template <typename C, typename Q, int kWalk, bool kStrand = false, bool kDense = false>
+// kVecOut: the stage is laid out with the phase (address mod 16) of its global destination, so the copy-out moves 16 bytes
+// per lane and instruction (one LDS.128 + one STG.128 per 4 hits) instead of 4; the <= 3 hits at either end go out as
+// scalar stores (the per-hit LDS + STG.32 loop was 10-13 % of this kernel's instructions).
+constexpr uint32_t kVecOutTailWords = 4;  // room behind the stage for the phase shift
+template <typename C, typename Q, int kWalk, bool kStrand = false, bool kDense = false, bool kVecOut = false>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
                            const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
@@ -254,7 +258,7 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                            StrandArgs sa = StrandArgs{nullptr, nullptr, 0}, CoopArgs<C> ca = CoopArgs<C>{}) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStage = emit_stage_entries(kStrand, kDense);
-    constexpr uint32_t kStageWords = kStage + kEmitScanSlack;
+    constexpr uint32_t kStageWords = kStage + kEmitScanSlack + (kVecOut ? kVecOutTailWords : 0u);
     constexpr uint32_t kWarps = kQueryThreads / 32;
     uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + kWarps * kStageWords;
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
@@ -329,9 +333,11 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                 if (kStrand) qst = sa.qstrand[q];
             }
             if (wtotal <= kStage) {
+                // (kVecOut) bytes by which the tile's stage image is shifted: shared and global addresses agree modulo 16
+                const uint32_t phase = kVecOut ? static_cast<uint32_t>(reinterpret_cast<uintptr_t>(hits + wbase)) & 15u : 0u;
                 if (kDense && !kStrand) {
                     // per-lane walks for a bounded number of steps, then the warp finishes the unfinished lists one by one
-                    const uint32_t s_begin = stage_addr + static_cast<uint32_t>(excl) * 4u;
+                    const uint32_t s_begin = stage_addr + phase + static_cast<uint32_t>(excl) * 4u;
                     uint32_t r_stop = 0, sp_stop = s_begin;
                     if (c != 0) emit_walk_staged8m<C>(ix, tabp, stride, n_levels, chrom, qs, hi, s_begin, s_begin + c * 4u, ca.budget, r_stop, sp_stop);
                     uint32_t pend = ca.budget > 0 ? __ballot_sync(0xffffffffu, sp_stop > s_begin && r_stop != 0) : 0u;
@@ -344,7 +350,7 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                                            cb, sp_j, (sp_j - sb_j) >> 2, nullptr, 0);
                     }
                 } else if (c != 0) {
-                    const uint32_t s_begin = stage_addr + static_cast<uint32_t>(excl) * 4u;
+                    const uint32_t s_begin = stage_addr + phase + static_cast<uint32_t>(excl) * 4u;
                     if (kStrand)
                         emit_walk_staged8_strand<C>(ix, tabp, stride, n_levels, chrom, qs, hi,
                                                     sa.strands + (tabp[chrom] - sa.slot_base), qst, s_begin, s_begin + c * 4u);
@@ -355,10 +361,27 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                 }
                 __syncwarp();
                 const uint32_t n = static_cast<uint32_t>(wtotal);
-                uint32_t sa = stage_addr + lane * 4u;
+                uint32_t sa = stage_addr + phase + lane * 4u;
                 if (wbase + wtotal <= capacity) {
-                    uint32_t* out = hits + wbase + lane;
-                    for (uint32_t i = lane; i < n; i += 32, out += 32, sa += 128) __stcs(out, lds32(sa));
+                    if (kVecOut) {
+                        const uint32_t n_bytes = n * 4u;
+                        const uint32_t head = min(n_bytes, (16u - phase) & 15u);  // bytes up to the first 16-byte boundary
+                        const uint32_t mid = (n_bytes - head) & ~15u;             // whole 16-byte vectors
+                        const uint32_t tail = n_bytes - head - mid;
+                        unsigned char* g = reinterpret_cast<unsigned char*>(hits + wbase);
+                        const uint32_t s0 = stage_addr + phase;
+                        for (uint32_t v = lane * 16u; v < mid; v += 512u)
+                            __stcs(reinterpret_cast<uint4*>(g + head + v), lds128(s0 + head + v));
+                        const uint32_t e = (lane & 3u) * 4u;  // lanes 0-3: the head words, lanes 4-7: the tail words
+                        if (lane < 4) {
+                            if (e < head) __stcs(reinterpret_cast<uint32_t*>(g + e), lds32(s0 + e));
+                        } else if (lane < 8) {
+                            if (e < tail) __stcs(reinterpret_cast<uint32_t*>(g + head + mid + e), lds32(s0 + head + mid + e));
+                        }
+                    } else {
+                        uint32_t* out = hits + wbase + lane;
+                        for (uint32_t i = lane; i < n; i += 32, out += 32, sa += 128) __stcs(out, lds32(sa));
+                    }
                 } else {
                     for (uint32_t i = lane; i < n; i += 32, sa += 128)
                         if (wbase + i < capacity) hits[wbase + i] = lds32(sa);

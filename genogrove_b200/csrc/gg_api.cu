@@ -87,6 +87,7 @@ struct gg_index {
     // chain_perm (inside bw.perm or bw.perm_alt) maps chain rank -> input index
     int chain_src = 0;
     const uint32_t* chain_perm = nullptr;
+    int64_t emit_vec_out = 0;  // pass 2 copy-out: 1 = 16-byte vector stores from a phase-aligned stage (emit_scan.cuh, kVecOut)
     int64_t coop_budget = 32;  // dense-batch emit: per-lane walk steps before the warp finishes a query together (0 = never)
     int64_t sort_geom = 0;     // onesweep tile geometry (radix_sort.cuh)
     int64_t sort_legacy = 0;   // 1 = three-kernel radix passes (histogram, scan, scatter) instead of the onesweep form
@@ -533,11 +534,14 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     }
     {
         const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
-        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (emit_stage_entries(false, dense) + kEmitScanSlack) * 4 + (tab_in_smem ? tab_bytes : 0) + 16;
+        const bool vec_out = !dense && idx->emit_walk == 8 && idx->emit_vec_out != 0;
+        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (emit_stage_entries(false, dense) + kEmitScanSlack + (vec_out ? kVecOutTailWords : 0u)) * 4 +
+                            (tab_in_smem ? tab_bytes : 0) + 16;
         void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
                      uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs, CoopArgs<C>) =
             dense ? intersect_emit_scan_kernel<C, Q, 8, false, true>
-                  : (idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16> : intersect_emit_scan_kernel<C, Q, 8>);
+                  : (idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16>
+                                          : (vec_out ? intersect_emit_scan_kernel<C, Q, 8, false, false, true> : intersect_emit_scan_kernel<C, Q, 8>));
         if (smem > 48 * 1024)
             GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         int per_sm = static_cast<int>(idx->emit_ctas_per_sm);
@@ -2044,6 +2048,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "sort_legacy" && (value == 0 || value == 1)) idx->sort_legacy = value;
     else if (k == "sort_geom" && value >= 0 && value <= 2) idx->sort_geom = value;
     else if (k == "coop_budget" && value >= 0 && value <= 1000000) idx->coop_budget = value;
+    else if (k == "emit_vec_out" && (value == 0 || value == 1)) idx->emit_vec_out = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;

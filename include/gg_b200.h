@@ -388,6 +388,9 @@ void gg_host_free(void* p);
  * the device-buffer calls for gg_last_batch_stats); "compact_delta_bytes" (1, 2, 4: width the compact call starts with);
  * "keep_build_workspace" (1 [default]: the sort buffers of gg_index_build stay allocated between builds — a facade that
  * re-syncs after every mutation saves 60 % of a rebuild; 0: freed after each build);
+ * "coop_budget" (dense-batch pass 2: per-lane walk steps before the warp finishes a query's list together — 256 slots per
+ * step through the per-8-slot maxima; 32 [default], 0 = per-lane walks only); "sort_geom" (onesweep tile: 0 = 256 threads
+ * x 12 keys [default], 1 = 512 x 12, 2 = 256 x 8);
  * "sort_legacy" (0 [default]: onesweep radix passes — one kernel per 8-bit digit with a decoupled look-back; 1: the
  * three-kernel passes of round 1 (per-CTA histogram, scan, scatter), which builds of 2^30 intervals or more always use);
  * "inject_alloc_failure" (debug: the k-th device allocation from now on fails, to drive the error paths). */

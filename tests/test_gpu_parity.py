@@ -580,6 +580,29 @@ def test_warp_cooperative_walk_on_skewed_lists(gg, oracle, budget, wide):
     _check(idx, chrom, start, end, n_chrom, (qc[o], qs[o], qe[o]))
 
 
+@pytest.mark.parametrize("sorted_batch", [True, False])
+def test_emit_vector_copy_out(gg, oracle, sorted_batch):
+    """emit_scan with the phase-aligned stage and 16-byte copy-out (option emit_vec_out): every alignment of a tile's first
+    hit (0, 4, 8, 12 bytes), tiles of 0 / 1 / 2 / 3 hits (head or tail only), tiles near the stage size."""
+    rng = np.random.default_rng(404 + sorted_batch)
+    n_chrom = 3
+    chrom, start, end = random_index(rng, 90_000, n_chrom, span=900_000, max_len=400, dup=True, nested=True)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("fused_kernel", 0)
+    idx.set_option("dense_emit", 0)
+    idx.set_option("emit_vec_out", 1)
+    idx.build(chrom, start, end, n_chrom)
+    nq = 200_003
+    qc, qs, qe = random_queries(rng, nq, n_chrom, span=900_000, max_len=60, extra_chrom=1)
+    qe[::7] = qs[::7]                                    # point queries: many empty / single-hit lists
+    qe[::501] = qs[::501] + np.uint64(30_000)            # a few long lists: tiles near and above the 512-hit stage
+    if sorted_batch:
+        o = np.lexsort((qs, qc))
+        qc, qs, qe = qc[o], qs[o], qe[o]
+    total = _check(idx, chrom, start, end, n_chrom, (qc, qs, qe))
+    assert total > nq
+
+
 def test_smoke_entry(gg, oracle):
     import __graft_entry__ as ge
     ge.smoke()
