@@ -39,6 +39,9 @@ struct StrandArgs {
 // walk costs 8x the L2 write transactions).  Runs in its own kernel (intersect_emit_dense_kernel) so the common
 // path keeps its register budget.
 constexpr uint32_t kDenseSeg = kEmitStage / 32;  // stage entries per lane (16)
+// per-warp stage of intersect_emit_dense_kernel: the interval build also holds the shared candidate list of a sorted tile
+// (ranks + ends; emit_tile_delta) and is as large as the stage of the dense-batch intersect_emit_scan_kernel
+__host__ __device__ constexpr uint32_t dense_stage_entries(bool strand) { return strand ? kEmitStage : 2u * kEmitStage; }
 // Tiles between the stage size and this many hits are walked straight to global memory by intersect_emit_scan_kernel
 // (skewed lists: a few long ones among short ones — GENCODE-shaped data — gain nothing from the segment flush);
 // from 64 hits per query on average the 8x saving in L2 write transactions wins (cfg5: 201 -> 89 ms).
@@ -138,6 +141,7 @@ struct CoopArgs {
     uint32_t n_groups;      // entries of m8
     int n_lv;
     int budget;             // per-lane walk steps before a query is handed to the warp (0: per-lane walks only)
+    uint32_t delta_min;     // tiles with at least this many hits may take the sorted-tile path (emit_tile_delta); 0 = never
 };
 
 // dst[j] = max(src[8 j .. 8 j + 8)); src is padded to whole 32-slot nodes, so every group is complete
@@ -155,9 +159,21 @@ __device__ __forceinline__ uint32_t strip_top_bit(uint32_t f) { return f != 0 ? 
 // All 32 lanes call this with the same arguments.  Hits are slots < abs_hi with end >= qs, highest first; value stored =
 // slot - cb.  kShared: the next hit goes to shared address sp - 4, downwards.  Else: to dst[rem - 1] down to dst[0],
 // positions at or beyond `room` dropped (hit buffer too small; the caller has flagged it).
+__device__ __forceinline__ void sts_coord(uint32_t a, uint32_t v) { sts32(a, v); }
+__device__ __forceinline__ void sts_coord(uint32_t a, uint64_t v) {
+    sts32(a, static_cast<uint32_t>(v));
+    sts32(a + 4u, static_cast<uint32_t>(v >> 32));
+}
+__device__ __forceinline__ void lds_coord(uint32_t a, uint32_t& v) { v = lds32(a); }
+__device__ __forceinline__ void lds_coord(uint32_t a, uint64_t& v) {
+    const uint2 w = lds64(a);
+    v = (static_cast<uint64_t>(w.y) << 32) | w.x;
+}
+
+// ends_base != 0 (kShared only): the end of the hit stored at list index i also goes to shared address ends_base + i * sizeof(C)
 template <typename C, bool kShared>
 __device__ __forceinline__ void coop_walk(const CoopArgs<C>& ca, C qs, uint32_t abs_hi, uint32_t cb, uint32_t sp, uint32_t rem,
-                                          uint32_t* __restrict__ dst, uint64_t room) {
+                                          uint32_t* __restrict__ dst, uint64_t room, uint32_t ends_base = 0) {
     const uint32_t lane = lane_id();
     const uint32_t sub = 3u - (lane >> 3);  // lanes 24-31 take the highest flagged group, 16-23 the next, ...
     uint32_t r_hi = abs_hi;
@@ -181,12 +197,17 @@ __device__ __forceinline__ void coop_walk(const CoopArgs<C>& ca, C qs, uint32_t 
             if (sub >= 2) f = strip_top_bit(f);
             if (sub >= 3) f = strip_top_bit(f);
             const uint32_t slot = (blk * 32 + (31u - __clz(f | 1u))) * 8 + (lane & 7u);
-            const bool hit = f != 0 && slot < r_hi && !(ca.leaf[slot] < qs);
+            const C ev = (f != 0 && slot < r_hi) ? ca.leaf[slot] : C(0);
+            const bool hit = f != 0 && slot < r_hi && !(ev < qs);
             const uint32_t hm = __ballot_sync(0xffffffffu, hit);
             const uint32_t k = __popc((hm >> 1) >> lane);  // hits in higher slots of this step
             if (hit && k < rem) {
-                if (kShared) sts32(sp - 4u * (k + 1), slot - cb);
-                else if (rem - 1 - k < room) dst[rem - 1 - k] = slot - cb;
+                if (kShared) {
+                    sts32(sp - 4u * (k + 1), slot - cb);
+                    if (ends_base != 0) sts_coord(ends_base + (rem - 1 - k) * static_cast<uint32_t>(sizeof(C)), ev);
+                } else if (rem - 1 - k < room) {
+                    dst[rem - 1 - k] = slot - cb;
+                }
             }
             const uint32_t nh = min(static_cast<uint32_t>(__popc(hm)), rem);
             sp -= 4u * nh;
@@ -195,6 +216,136 @@ __device__ __forceinline__ void coop_walk(const CoopArgs<C>& ca, C qs, uint32_t 
         }
         r_hi = blk << 8;
     }
+}
+
+// ---- sorted dense tiles: one candidate list per 32-query tile ------------------------------------------------------
+// On a dense index (cfg5: 150 hits per 150 bp query) the per-lane forms spend ~4 warp-instructions per hit testing ~650
+// ranks per query and flushing per-lane segments.  In a coordinate-sorted batch the 32 queries of a tile ask almost the
+// same question: with q.start and hi non-decreasing along the tile (one chromosome), every hit of query j is either a hit
+// of query 0 or a rank in [hi_0, hi_j).  So the warp builds ONE candidate list U = hits(query 0) ++ [hi_0, hi_31) in shared
+// memory, ranks ascending with their ends beside them — one cooperative walk for the whole tile — and each query's list is
+// the prefix U[0, c_0 + hi_j - hi_0) filtered by end >= q_j.start: 32 candidates per step, one compare, a ballot for the
+// write positions, one coalesced store.  ~0.5 warp-instructions per hit; no per-rank test per query.
+// Both pass-2 kernels of the dense variant evaluate tile_delta_ok on the same values, so exactly one of them writes a tile.
+template <typename C>
+__host__ __device__ constexpr uint32_t delta_cap(uint32_t stage_entries) {  // candidates that fit the warp's stage (even)
+    return (stage_entries * 4u / (4u + static_cast<uint32_t>(sizeof(C)))) & ~1u;
+}
+template <typename C>
+__device__ __forceinline__ bool tile_delta_ok(uint32_t c, uint32_t hi, C qs, uint32_t chrom, uint64_t wtotal, uint32_t cap,
+                                              uint32_t delta_min) {
+    if (delta_min == 0 || wtotal < delta_min || wtotal >= (1ull << 31)) return false;
+    const uint32_t hi_prev = __shfl_up_sync(0xffffffffu, hi, 1), ch0 = __shfl_sync(0xffffffffu, chrom, 0);
+    const C qs_prev = __shfl_up_sync(0xffffffffu, qs, 1);
+    const bool ok = c != 0 && chrom == ch0 && (lane_id() == 0 || (hi >= hi_prev && !(qs < qs_prev)));
+    if (!__all_sync(0xffffffffu, ok)) return false;
+    const uint32_t c0 = __shfl_sync(0xffffffffu, c, 0), hi0 = __shfl_sync(0xffffffffu, hi, 0), hi31 = __shfl_sync(0xffffffffu, hi, 31);
+    return static_cast<uint64_t>(c0) + (hi31 - hi0) <= cap;
+}
+
+template <typename C>
+__device__ __forceinline__ C warp_min(C v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        const C o = __shfl_xor_sync(0xffffffffu, v, d);
+        v = o < v ? o : v;
+    }
+    return v;
+}
+
+// The tile's list is kept INCREMENTALLY (second version; the first filtered the whole candidate list for every query, 23
+// instructions per 32 candidates): going from query j-1 to j the list gains the ranks [hi_{j-1}, hi_j) at its end and loses
+// the members whose end fell below q_j.start — known from the smallest end among the members, so most queries lose nothing
+// and their list goes out as a plain shared -> global copy.
+template <typename C>
+__device__ __forceinline__ void emit_tile_delta(const CoopArgs<C>& ca, uint32_t c, uint32_t hi, C qs, uint32_t chrom, uint64_t excl,
+                                                uint64_t wbase, uint32_t stage_addr, uint32_t cap, uint32_t* __restrict__ hits,
+                                                uint64_t capacity) {
+    constexpr uint32_t kSz = static_cast<uint32_t>(sizeof(C));
+    const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+    const uint32_t rb = stage_addr, eb = stage_addr + cap * 4u;  // ranks, then ends (8-byte aligned: cap is even)
+    const uint32_t c0 = __shfl_sync(0xffffffffu, c, 0), hi0 = __shfl_sync(0xffffffffu, hi, 0);
+    const C qs0 = __shfl_sync(0xffffffffu, qs, 0);
+    const uint32_t cb = ca.cslot[__shfl_sync(0xffffffffu, chrom, 0)];
+    // the list of query 0, by the whole warp: ranks ascending at rb, their ends at eb
+    coop_walk<C, true>(ca, qs0, cb + hi0, cb, rb + 4u * c0, c0, nullptr, 0, eb);
+    __syncwarp();
+    uint32_t len = c0, prev_hi = hi0;
+    C my_min = coord_max<C>::value;
+    for (uint32_t i = lane; i < len; i += 32) {
+        C e;
+        lds_coord(eb + i * kSz, e);
+        my_min = e < my_min ? e : my_min;
+    }
+    C min_end = warp_min<C>(my_min);
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t hj = __shfl_sync(0xffffffffu, hi, j);
+        const C qj = __shfl_sync(0xffffffffu, qs, j);
+        const uint64_t oj = wbase + __shfl_sync(0xffffffffu, excl, j);
+        if (hj != prev_hi) {  // new members: the ranks whose start lies in (q_{j-1}.end, q_j.end]
+            const uint32_t add = hj - prev_hi;
+            C m = coord_max<C>::value;
+            for (uint32_t i = lane; i < add; i += 32) {
+                const C e = ca.leaf[cb + prev_hi + i];
+                sts32(rb + 4u * (len + i), prev_hi + i);
+                sts_coord(eb + (len + i) * kSz, e);
+                m = e < m ? e : m;
+            }
+            m = warp_min<C>(m);
+            min_end = m < min_end ? m : min_end;
+            len += add;
+            prev_hi = hj;
+            __syncwarp();
+        }
+        const uint64_t room64 = capacity > oj ? capacity - oj : 0ull;
+        if (min_end < qj) {
+            // at least one member ended before q_j.start: ONE pass filters the list, writes the survivors out and compacts
+            // the list in place (queries sparser than the index lose a member at almost every step; a separate compaction
+            // pass in front of the copy made those batches slower than filtering the whole candidate list every time)
+            const uint32_t room = room64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : static_cast<uint32_t>(room64);
+            uint32_t* __restrict__ out = hits + oj;
+            uint32_t kept = 0;
+            C m = coord_max<C>::value;
+            for (uint32_t k = 0; k < len; k += 32) {
+                const uint32_t i = k + lane;
+                C e = 0;
+                uint32_t r = 0;
+                if (i < len) {
+                    lds_coord(eb + i * kSz, e);
+                    r = lds32(rb + 4u * i);
+                }
+                const bool alive = i < len && !(e < qj);
+                const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+                const uint32_t pos = kept + __popc(mask & lt);
+                __syncwarp();  // every lane has read its slot before slots at or below it are rewritten
+                if (alive) {
+                    sts32(rb + 4u * pos, r);
+                    sts_coord(eb + pos * kSz, e);
+                    m = e < m ? e : m;
+                    if (pos < room) __stcs(out + pos, r);
+                }
+                kept += __popc(mask);
+            }
+            len = kept;
+            min_end = warp_min<C>(m);
+            __syncwarp();
+        } else {
+            // nobody left: the list of query j is a plain copy
+            const uint32_t n_out = room64 < len ? static_cast<uint32_t>(room64) : len;
+            uint32_t* __restrict__ out = hits + oj + lane;
+            uint32_t sa = rb + 4u * lane;
+            uint32_t i = lane;
+            for (; i + 96 < n_out; i += 128, out += 128, sa += 512u) {
+                const uint32_t v0 = lds32(sa), v1 = lds32(sa + 128u), v2 = lds32(sa + 256u), v3 = lds32(sa + 384u);
+                __stcs(out, v0);
+                __stcs(out + 32, v1);
+                __stcs(out + 64, v2);
+                __stcs(out + 96, v3);
+            }
+            for (; i < n_out; i += 32, out += 32, sa += 128u) __stcs(out, lds32(sa));
+        }
+    }
+    __syncwarp();
 }
 
 // emit_walk_staged8 (intersect.cuh) for the dense-batch variant: a group of 8 ranks is first tested as a whole (max end
@@ -387,8 +538,10 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                         if (wbase + i < capacity) hits[wbase + i] = lds32(sa);
                 }
                 __syncwarp();
-            } else if (kDense && dense_tile(wtotal, cmax, kStage)) {
-                // a dense tile: intersect_emit_dense_kernel finds it from the per-tile totals of the count pass and writes it
+            } else if (kDense && (dense_tile(wtotal, cmax, kStage) ||
+                                  (!kStrand && tile_delta_ok<C>(c, hi, qs, chrom, wtotal, delta_cap<C>(kStage), ca.delta_min)))) {
+                // a dense tile, or a sorted tile that shares one candidate list: intersect_emit_dense_kernel finds it from the
+                // per-tile totals of the count pass and writes it
             } else if (kDense && !kStrand && ca.budget > 0) {
                 // too large for the stage, one or a few long lists among short ones: every list by the whole warp, straight to
                 // global memory (a single lane walking a 100 k-hit list alone was the worst case of the per-lane form)
@@ -424,9 +577,10 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
                             const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
                             const uint64_t* __restrict__ block_prefix, const uint32_t* __restrict__ tile_total,
                             uint32_t blk_q, uint32_t* __restrict__ hits, uint64_t capacity, StrandArgs sa,
-                            uint32_t stage_entries /* of the intersect_emit_scan_kernel build that ran before */) {
+                            uint32_t stage_entries /* of the intersect_emit_scan_kernel build that ran before */,
+                            CoopArgs<C> ca /* delta_min: sorted tiles from this many hits share one candidate list (0 = off) */) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr uint32_t kStageWords = kEmitStage + kEmitScanSlack;
+    constexpr uint32_t kStageWords = dense_stage_entries(kStrand) + kEmitScanSlack;
     constexpr uint32_t kWarps = kQueryThreads / 32;
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
     const uint32_t stage_addr = smem_u32(smem_raw) + (warp * kStageWords + kEmitScanSlack) * 4u;
@@ -469,7 +623,8 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
                 if (lane >= static_cast<uint32_t>(d)) inc += o;
             }
             const uint64_t excl = inc - c, wtotal = __shfl_sync(0xffffffffu, inc, 31);
-            if (!dense_tile(wtotal, __reduce_max_sync(0xffffffffu, c), stage_entries)) continue;  // written by intersect_emit_scan_kernel itself
+            const bool dense = dense_tile(wtotal, __reduce_max_sync(0xffffffffu, c), stage_entries);
+            if (!dense && (kStrand || ca.delta_min == 0 || wtotal < ca.delta_min)) continue;  // written by intersect_emit_scan_kernel itself
             const uint64_t wbase = tile_base - block_prefix[0];
             uint32_t chrom = 0, hi = 0, qst = 0;
             C qs = 0;
@@ -479,6 +634,13 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
                 hi = hi_in[q];
                 if (kStrand) qst = sa.qstrand[q];
             }
+            // a coordinate-sorted tile: one shared candidate list instead of 32 walks (same predicate and values as in
+            // intersect_emit_scan_kernel, which left the tile alone)
+            if (!kStrand && tile_delta_ok<C>(c, hi, qs, chrom, wtotal, delta_cap<C>(stage_entries), ca.delta_min)) {
+                emit_tile_delta<C>(ca, c, hi, qs, chrom, excl, wbase, stage_addr, delta_cap<C>(stage_entries), hits, capacity);
+                continue;
+            }
+            if (!dense) continue;
             const uint8_t* strands = kStrand && c != 0 ? sa.strands + (tabp[chrom] - sa.slot_base) : nullptr;
             const uint64_t room = capacity > wbase ? capacity - wbase : 0ull;  // positions of this tile that fit the buffer
             emit_dense_tile<C, kStrand>(ix, tabp, stride, n_levels, chrom, qs, hi, c, excl, stage_addr, hits + wbase, room, strands, qst);

@@ -88,6 +88,7 @@ struct gg_index {
     int chain_src = 0;
     const uint32_t* chain_perm = nullptr;
     int64_t emit_vec_out = 0;  // pass 2 copy-out: 1 = 16-byte vector stores from a phase-aligned stage (emit_scan.cuh, kVecOut)
+    int64_t delta_min_hits = 1024;  // dense-batch emit: sorted 32-query tiles with at least this many hits share one candidate list (0 = off)
     int64_t coop_budget = 32;  // dense-batch emit: per-lane walk steps before the warp finishes a query together (0 = never)
     int64_t sort_geom = 0;     // onesweep tile geometry (radix_sort.cuh)
     int64_t sort_legacy = 0;   // 1 = three-kernel radix passes (histogram, scan, scatter) instead of the onesweep form
@@ -271,6 +272,8 @@ CoopArgs<C> make_coop(const gg_index* idx) {
     a.n_groups = idx->n_m8;
     a.n_lv = idx->n_flat;
     a.budget = static_cast<int>(idx->coop_budget);
+    // (only tiles beyond the dense-batch stage reach the second pass-2 kernel, which owns the sorted-tile path)
+    a.delta_min = idx->delta_min_hits > 0 ? static_cast<uint32_t>(std::max<int64_t>(idx->delta_min_hits, emit_stage_entries(false, true) + 1)) : 0u;
     return a;
 }
 
@@ -454,17 +457,19 @@ inline size_t single_scratch_bytes(size_t nq) {
 template <typename C, typename Q, bool kStrand>
 gg_status launch_emit_dense(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, size_t nq, const uint32_t* d_cnt,
                             const uint32_t* d_hi, const uint64_t* block_prefix, const uint32_t* d_tile,
-                            uint32_t* d_hits, uint64_t capacity, StrandArgs sa, cudaStream_t st) {
+                            uint32_t* d_hits, uint64_t capacity, StrandArgs sa, cudaStream_t st, bool delta = false) {
     if (nq == 0) return GG_OK;
     auto kern = intersect_emit_dense_kernel<C, Q, kStrand>;
-    const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (kEmitStage + kEmitScanSlack) * 4 + 16;
+    const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (dense_stage_entries(kStrand) + kEmitScanSlack) * 4 + 16;
+    CoopArgs<C> ca = delta ? make_coop<C>(idx) : CoopArgs<C>{};
+    if (!delta) ca.delta_min = 0;
     int per_sm = 0;
     GG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kQueryThreads, smem));
     if (per_sm < 1) return fail(idx, GG_ERR_CUDA, "dense emit kernel does not fit on an SM");
     const size_t ctas = div_up(div_up(nq, 32 * 32), kQueryThreads / 32);  // a warp step covers 32 tiles
     const unsigned grid = static_cast<unsigned>(std::min<size_t>(std::max<size_t>(ctas, 1), static_cast<size_t>(idx->sm_count) * per_sm));
     kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix, d_tile,
-                                            static_cast<uint32_t>(kBatchBlockQ), d_hits, capacity, sa, emit_stage_entries(kStrand, true));
+                                            static_cast<uint32_t>(kBatchBlockQ), d_hits, capacity, sa, emit_stage_entries(kStrand, true), ca);
     GG_CUDA(cudaGetLastError());
     idx->bstats.kernel_launches++;
     return GG_OK;
@@ -559,7 +564,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     }
     if (!dense) return GG_OK;
     return launch_emit_dense<C, Q, false>(idx, d_chrom, d_start, nq, d_cnt, d_hi, block_prefix, d_tile, d_hits, capacity,
-                                          StrandArgs{nullptr, nullptr, 0}, st);
+                                          StrandArgs{nullptr, nullptr, 0}, st, /*delta=*/true);
 }
 
 // measured on B200 (tools/small_batch_probe.py, cfg2 index): 1 k .. 100 k queries 30-33 us in one kernel against 39-44 us for
@@ -2048,6 +2053,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "sort_legacy" && (value == 0 || value == 1)) idx->sort_legacy = value;
     else if (k == "sort_geom" && value >= 0 && value <= 2) idx->sort_geom = value;
     else if (k == "coop_budget" && value >= 0 && value <= 1000000) idx->coop_budget = value;
+    else if (k == "delta_min_hits" && value >= 0 && value <= (1ll << 30)) idx->delta_min_hits = value;
     else if (k == "emit_vec_out" && (value == 0 || value == 1)) idx->emit_vec_out = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;

@@ -603,6 +603,66 @@ def test_emit_vector_copy_out(gg, oracle, sorted_batch):
     assert total > nq
 
 
+@pytest.mark.parametrize("delta_min", [1, 512, 0])
+@pytest.mark.parametrize("wide", [False, True])
+def test_sorted_tile_candidate_list(gg, oracle, delta_min, wide):
+    """Dense-batch emit, sorted tiles (emit_scan.cuh, emit_tile_delta): one candidate list per 32-query tile.  Fixed-length
+    reads sorted by start on a dense index (every tile qualifies), with equal starts, chromosome changes inside tiles
+    (those tiles fall back), jumps in the query stream larger than the stage holds (fall back), nested long intervals,
+    the u64 layout, and a hit buffer that is too small.  delta_min 1 forces the path for every sorted tile, 0 is the control."""
+    import torch
+    from genogrove_b200 import GGError
+    rng = np.random.default_rng(606 + wide)
+    n_chrom = 4
+    sizes = [60_000, 257, 30_011, 12_000]
+    chrom = np.concatenate([np.full(m, c, np.uint32) for c, m in enumerate(sizes)])
+    n = len(chrom)
+    start = rng.integers(0, 300_000, n).astype(np.uint64)
+    ln = np.exp(rng.uniform(np.log(20), np.log(4000), n)).astype(np.uint64)
+    ln[rng.random(n) < 0.002] = 250_000
+    start[rng.random(n) < 0.2] //= np.uint64(64)
+    start[rng.random(n) < 0.2] *= np.uint64(1)
+    off = np.uint64(2**35) if wide else np.uint64(0)
+    start, end = start + off, start + ln + off
+    sh = rng.permutation(n)
+    chrom, start, end = chrom[sh], start[sh], end[sh]
+    idx = gg.DeviceIndex(0)
+    idx.set_option("dense_emit", 1)
+    idx.set_option("fused_kernel", 0)
+    idx.set_option("delta_min_hits", delta_min)
+    idx.build(chrom, start, end, n_chrom)
+    nq = 50_001
+    qc = np.sort(rng.integers(0, n_chrom, nq)).astype(np.uint32)
+    qs = rng.integers(0, 310_000, nq).astype(np.uint64)
+    qs[rng.random(nq) < 0.3] //= np.uint64(16)          # runs of equal starts, and a cluster near 0
+    qs[1000:1400] = 5                                   # 400 identical queries
+    o = np.lexsort((qs, qc))
+    qc, qs = qc[o], qs[o]
+    qs[20_000:20_032] += np.uint64(200_000)             # a jump the stage cannot hold (still sorted inside its tile?)
+    qs = qs + off
+    qe = qs + np.uint64(149)
+    exp_total = _check(idx, chrom, start, end, n_chrom, (qc, qs, qe))
+    assert exp_total / nq > 30
+    # the same batch with a hit buffer that is too small: offsets complete, nothing beyond the capacity
+    if not wide:
+        dev = torch.device("cuda:0")
+        d = [torch.from_numpy(a).to(dev) for a in (qc.view(np.int32), qs.astype(np.uint32).view(np.int32), qe.astype(np.uint32).view(np.int32))]
+        d_off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
+        cap = exp_total // 2
+        d_hits = torch.full((cap + 64,), -1, dtype=torch.int32, device=dev)
+        with pytest.raises(GGError) as ei:
+            idx.fused_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(), cap,
+                             torch.cuda.current_stream().cuda_stream, sync_total=True)
+        assert ei.value.status == 7 and idx.last_total == exp_total
+        got = d_hits.cpu().numpy()
+        assert (got[cap:] == -1).all()
+        exp_off, exp_hits = oracle_csr(chrom, start, end, n_chrom, qc, qs, qe)
+        assert np.array_equal(d_off.cpu().numpy().view(np.uint64), exp_off)
+        last_full = (int(np.searchsorted(exp_off, cap, side="right")) - 1) // 128 * 128  # every complete block below the capacity is exact
+        upto = int(exp_off[last_full]) if last_full > 0 else 0
+        assert upto > cap // 2 and np.array_equal(got[:upto].view(np.uint32), exp_hits[:upto])
+
+
 def test_smoke_entry(gg, oracle):
     import __graft_entry__ as ge
     ge.smoke()

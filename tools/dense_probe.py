@@ -23,6 +23,9 @@ nq = len(qc)
 dev = torch.device("cuda:0")
 idx = DeviceIndex(0)
 idx.set_option("dense_emit", int(os.environ.get("DENSE", "1")))
+for kv in os.environ.get("GG_OPTS", "").split(","):  # e.g. GG_OPTS=delta_min_hits=0
+    if kv:
+        idx.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 idx.build(chrom, start, end, 3, want_perm=False)
 d_c = torch.from_numpy(qc.view(np.int32)).to(dev)
 d_s = torch.from_numpy(qs.astype(np.uint32).view(np.int32)).to(dev)
