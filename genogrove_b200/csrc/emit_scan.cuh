@@ -399,7 +399,15 @@ __device__ __forceinline__ void emit_walk_staged8m(const IndexView<C>& ix, const
 // per lane and instruction (one LDS.128 + one STG.128 per 4 hits) instead of 4; the <= 3 hits at either end go out as
 // scalar stores (the per-hit LDS + STG.32 loop was 10-13 % of this kernel's instructions).
 constexpr uint32_t kVecOutTailWords = 4;  // room behind the stage for the phase shift
-template <typename C, typename Q, int kWalk, bool kStrand = false, bool kDense = false, bool kVecOut = false>
+// kTileList (coordinate-sorted batches on ordinary indexes, cfg4): when a tile's 32 queries are on one chromosome with
+// q.start and hi non-decreasing, every hit of query j is a hit of query 0 or a rank in [hi_0, hi_j) — the observation behind
+// emit_tile_delta, used here with the lanes still working in parallel: the warp builds the short shared candidate list once
+// (one cooperative walk for query 0 instead of 32 walks over the same ~30 ranks), then every lane filters that list for its
+// own query: ~11 candidates tested per lane where the walk tested ~30 ranks.  Other tiles take the walk as before.
+constexpr uint32_t kTileListCap = 64;  // candidates (ranks + ends) per warp
+template <typename C>
+__host__ __device__ constexpr uint32_t tile_list_words() { return kTileListCap + kTileListCap * static_cast<uint32_t>(sizeof(C)) / 4u; }
+template <typename C, typename Q, int kWalk, bool kStrand = false, bool kDense = false, bool kVecOut = false, bool kTileList = false>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart, size_t nq,
                            const uint32_t* __restrict__ cnt_in, const uint32_t* __restrict__ hi_in,
@@ -409,11 +417,12 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                            StrandArgs sa = StrandArgs{nullptr, nullptr, 0}, CoopArgs<C> ca = CoopArgs<C>{}) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStage = emit_stage_entries(kStrand, kDense);
-    constexpr uint32_t kStageWords = kStage + kEmitScanSlack + (kVecOut ? kVecOutTailWords : 0u);
+    constexpr uint32_t kStageWords = kStage + kEmitScanSlack + (kVecOut ? kVecOutTailWords : 0u) + (kTileList ? tile_list_words<C>() : 0u);
     constexpr uint32_t kWarps = kQueryThreads / 32;
     uint32_t* stab = reinterpret_cast<uint32_t*>(smem_raw) + kWarps * kStageWords;
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
     const uint32_t stage_addr = smem_u32(smem_raw) + (warp * kStageWords + kEmitScanSlack) * 4u;
+    const uint32_t list_addr = stage_addr + (kStage + (kVecOut ? kVecOutTailWords : 0u)) * 4u;  // (kTileList) ranks, then ends
     const uint32_t stride = ix.n_chrom + 1;
     const int n_levels = ix.n_levels;
     const uint32_t* __restrict__ tabp = ix.tab;
@@ -499,6 +508,30 @@ intersect_emit_scan_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom,
                         const uint32_t sp_j = __shfl_sync(0xffffffffu, sp_stop, j), sb_j = __shfl_sync(0xffffffffu, s_begin, j);
                         coop_walk<C, true>(ca, static_cast<C>(__shfl_sync(0xffffffffu, qs, j)), cb + __shfl_sync(0xffffffffu, r_stop, j),
                                            cb, sp_j, (sp_j - sb_j) >> 2, nullptr, 0);
+                    }
+                } else if (kTileList && tile_delta_ok<C>(c, hi, qs, chrom, wtotal, kTileListCap, 1u)) {
+                    constexpr uint32_t kSz = static_cast<uint32_t>(sizeof(C));
+                    const uint32_t ur = list_addr, ue = list_addr + kTileListCap * 4u;
+                    const uint32_t c0 = __shfl_sync(0xffffffffu, c, 0), hi0 = __shfl_sync(0xffffffffu, hi, 0), hi31 = __shfl_sync(0xffffffffu, hi, 31);
+                    const uint32_t cb = ca.cslot[__shfl_sync(0xffffffffu, chrom, 0)];
+                    coop_walk<C, true>(ca, static_cast<C>(__shfl_sync(0xffffffffu, qs, 0)), cb + hi0, cb, ur + 4u * c0, c0, nullptr, 0, ue);
+                    if (lane < hi31 - hi0) {  // (at most kTileListCap - c0 <= 64 ranks: two rounds)
+                        for (uint32_t i = lane; i < hi31 - hi0; i += 32) {
+                            sts32(ur + 4u * (c0 + i), hi0 + i);
+                            sts_coord(ue + (c0 + i) * kSz, ca.leaf[cb + hi0 + i]);
+                        }
+                    }
+                    __syncwarp();
+                    const uint32_t p_max = c0 + (hi31 - hi0), p = c0 + (hi - hi0);
+                    uint32_t sp = stage_addr + phase + static_cast<uint32_t>(excl) * 4u;
+                    for (uint32_t i = 0; i < p_max; ++i) {  // every lane reads the same candidate (a broadcast), keeps its own hits
+                        C e;
+                        lds_coord(ue + i * kSz, e);
+                        const uint32_t r = lds32(ur + 4u * i);
+                        if (i < p && !(e < qs)) {
+                            sts32(sp, r);
+                            sp += 4u;
+                        }
                     }
                 } else if (c != 0) {
                     const uint32_t s_begin = stage_addr + phase + static_cast<uint32_t>(excl) * 4u;

@@ -87,6 +87,7 @@ struct gg_index {
     // chain_perm (inside bw.perm or bw.perm_alt) maps chain rank -> input index
     int chain_src = 0;
     const uint32_t* chain_perm = nullptr;
+    int64_t emit_tile_list = 0;  // pass 2 on sorted tiles: 1 = one shared candidate list per 32-query tile, filtered per lane (emit_scan.cuh, kTileList)
     int64_t emit_vec_out = 0;  // pass 2 copy-out: 1 = 16-byte vector stores from a phase-aligned stage (emit_scan.cuh, kVecOut)
     int64_t delta_min_hits = 1024;  // dense-batch emit: sorted 32-query tiles with at least this many hits share one candidate list (0 = off)
     int64_t coop_budget = 32;  // dense-batch emit: per-lane walk steps before the warp finishes a query together (0 = never)
@@ -540,13 +541,16 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
     {
         const size_t tab_bytes = static_cast<size_t>(idx->n_levels) * (idx->n_chrom + 1) * 4;
         const bool vec_out = !dense && idx->emit_walk == 8 && idx->emit_vec_out != 0;
-        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (emit_stage_entries(false, dense) + kEmitScanSlack + (vec_out ? kVecOutTailWords : 0u)) * 4 +
+        const bool tile_list = !dense && !vec_out && idx->emit_walk == 8 && idx->emit_tile_list != 0;
+        const size_t smem = static_cast<size_t>(kQueryThreads / 32) * (emit_stage_entries(false, dense) + kEmitScanSlack + (vec_out ? kVecOutTailWords : 0u) +
+                                                                       (tile_list ? tile_list_words<C>() : 0u)) * 4 +
                             (tab_in_smem ? tab_bytes : 0) + 16;
         void (*kern)(IndexView<C>, const uint32_t*, const Q*, size_t, const uint32_t*, const uint32_t*, const uint64_t*, uint32_t,
                      uint64_t*, uint32_t*, uint64_t, uint64_t*, uint64_t*, uint32_t*, int, StrandArgs, CoopArgs<C>) =
             dense ? intersect_emit_scan_kernel<C, Q, 8, false, true>
                   : (idx->emit_walk == 16 ? intersect_emit_scan_kernel<C, Q, 16>
-                                          : (vec_out ? intersect_emit_scan_kernel<C, Q, 8, false, false, true> : intersect_emit_scan_kernel<C, Q, 8>));
+                                          : (vec_out ? intersect_emit_scan_kernel<C, Q, 8, false, false, true>
+                                                     : (tile_list ? intersect_emit_scan_kernel<C, Q, 8, false, false, false, true> : intersect_emit_scan_kernel<C, Q, 8>)));
         if (smem > 48 * 1024)
             GG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         int per_sm = static_cast<int>(idx->emit_ctas_per_sm);
@@ -558,7 +562,7 @@ gg_status launch_batch(gg_index* idx, const uint32_t* d_chrom, const Q* d_start,
         const unsigned grid = static_cast<unsigned>(std::min<size_t>(ctas, static_cast<size_t>(idx->sm_count) * per_sm));
         kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_cnt, d_hi, block_prefix,
                                                 static_cast<uint32_t>(kBatchBlockQ), d_off, d_hits, capacity, d_next_base, d_total,
-                                                d_err, tab_in_smem ? 1 : 0, StrandArgs{nullptr, nullptr, 0}, dense ? make_coop<C>(idx) : CoopArgs<C>{});
+                                                d_err, tab_in_smem ? 1 : 0, StrandArgs{nullptr, nullptr, 0}, (dense || tile_list) ? make_coop<C>(idx) : CoopArgs<C>{});
         GG_CUDA(cudaGetLastError());
         idx->bstats.kernel_launches++;
     }
@@ -2055,6 +2059,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "coop_budget" && value >= 0 && value <= 1000000) idx->coop_budget = value;
     else if (k == "delta_min_hits" && value >= 0 && value <= (1ll << 30)) idx->delta_min_hits = value;
     else if (k == "emit_vec_out" && (value == 0 || value == 1)) idx->emit_vec_out = value;
+    else if (k == "emit_tile_list" && (value == 0 || value == 1)) idx->emit_tile_list = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;

@@ -580,6 +580,35 @@ def test_warp_cooperative_walk_on_skewed_lists(gg, oracle, budget, wide):
     _check(idx, chrom, start, end, n_chrom, (qc[o], qs[o], qe[o]))
 
 
+@pytest.mark.parametrize("wide", [False, True])
+def test_emit_shared_candidate_list_per_tile(gg, oracle, wide):
+    """emit_scan with one shared candidate list per sorted 32-query tile (option emit_tile_list): fixed-length sorted reads
+    (every tile qualifies), equal starts, chromosome changes and unsorted stretches inside the batch (those tiles take the
+    walk), nested long intervals, tiles whose list exceeds the 64-candidate cap, the u64 layout."""
+    rng = np.random.default_rng(707 + wide)
+    n_chrom = 3
+    chrom, start, end = random_index(rng, 120_000, n_chrom, span=4_000_000, max_len=900, dup=True, nested=True, wide=wide)
+    idx = gg.DeviceIndex(0)
+    idx.set_option("fused_kernel", 0)
+    idx.set_option("dense_emit", 0)
+    idx.set_option("emit_tile_list", 1)
+    idx.build(chrom, start, end, n_chrom)
+    nq = 300_007
+    off = np.uint64(2**40) if wide else np.uint64(0)
+    qc = np.sort(rng.integers(0, n_chrom + 1, nq)).astype(np.uint32)
+    qs = rng.integers(0, 4_100_000, nq).astype(np.uint64)
+    qs[5000:5600] = 1234
+    o = np.lexsort((qs, qc))
+    qc, qs = qc[o], qs[o]
+    qs[100_000:101_000] = rng.permutation(qs[100_000:101_000])   # an unsorted stretch
+    qs = qs + off
+    qs[::97] = 0                                                   # position 0 (pads hold end = 0), breaks the order too
+    qe = qs + np.uint64(149)
+    qe[200_000:200_064] += np.uint64(40_000)                       # lists beyond the cap
+    total = _check(idx, chrom, start, end, n_chrom, (qc, qs, qe))
+    assert total > nq
+
+
 @pytest.mark.parametrize("sorted_batch", [True, False])
 def test_emit_vector_copy_out(gg, oracle, sorted_batch):
     """emit_scan with the phase-aligned stage and 16-byte copy-out (option emit_vec_out): every alignment of a tile's first
