@@ -257,27 +257,46 @@ __device__ __forceinline__ C warp_min(C v) {
 // instructions per 32 candidates): going from query j-1 to j the list gains the ranks [hi_{j-1}, hi_j) at its end and loses
 // the members whose end fell below q_j.start — known from the smallest end among the members, so most queries lose nothing
 // and their list goes out as a plain shared -> global copy.
+// The list outlives the tile: a warp of the dense kernel takes up to 32 consecutive tiles, and when the next sorted tile
+// continues where this one stopped (same chromosome, q.start and hi not below the last query's) its first query is just
+// one more incremental step — the cooperative walk that builds a list from nothing (~650 ranks on cfg5) then runs once per
+// 1024 queries instead of once per 32.
+template <typename C>
+struct DeltaCarry {
+    bool valid = false;
+    uint32_t chrom = 0, len = 0, prev_hi = 0;
+    C last_qs = 0, min_end = 0;
+};
+
 template <typename C>
 __device__ __forceinline__ void emit_tile_delta(const CoopArgs<C>& ca, uint32_t c, uint32_t hi, C qs, uint32_t chrom, uint64_t excl,
                                                 uint64_t wbase, uint32_t stage_addr, uint32_t cap, uint32_t* __restrict__ hits,
-                                                uint64_t capacity) {
+                                                uint64_t capacity, DeltaCarry<C>& carry) {
     constexpr uint32_t kSz = static_cast<uint32_t>(sizeof(C));
     const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
     const uint32_t rb = stage_addr, eb = stage_addr + cap * 4u;  // ranks, then ends (8-byte aligned: cap is even)
-    const uint32_t c0 = __shfl_sync(0xffffffffu, c, 0), hi0 = __shfl_sync(0xffffffffu, hi, 0);
+    const uint32_t c0 = __shfl_sync(0xffffffffu, c, 0), hi0 = __shfl_sync(0xffffffffu, hi, 0), hi31 = __shfl_sync(0xffffffffu, hi, 31);
     const C qs0 = __shfl_sync(0xffffffffu, qs, 0);
-    const uint32_t cb = ca.cslot[__shfl_sync(0xffffffffu, chrom, 0)];
-    // the list of query 0, by the whole warp: ranks ascending at rb, their ends at eb
-    coop_walk<C, true>(ca, qs0, cb + hi0, cb, rb + 4u * c0, c0, nullptr, 0, eb);
-    __syncwarp();
-    uint32_t len = c0, prev_hi = hi0;
-    C my_min = coord_max<C>::value;
-    for (uint32_t i = lane; i < len; i += 32) {
-        C e;
-        lds_coord(eb + i * kSz, e);
-        my_min = e < my_min ? e : my_min;
+    const uint32_t ch0 = __shfl_sync(0xffffffffu, chrom, 0);
+    const uint32_t cb = ca.cslot[ch0];
+    uint32_t len, prev_hi;
+    C min_end;
+    if (carry.valid && carry.chrom == ch0 && hi0 >= carry.prev_hi && !(qs0 < carry.last_qs) &&
+        static_cast<uint64_t>(carry.len) + (hi31 - carry.prev_hi) <= cap) {
+        len = carry.len, prev_hi = carry.prev_hi, min_end = carry.min_end;  // the stage still holds the last query's list
+    } else {
+        // the list of query 0, by the whole warp: ranks ascending at rb, their ends at eb
+        coop_walk<C, true>(ca, qs0, cb + hi0, cb, rb + 4u * c0, c0, nullptr, 0, eb);
+        __syncwarp();
+        len = c0, prev_hi = hi0;
+        C my_min = coord_max<C>::value;
+        for (uint32_t i = lane; i < len; i += 32) {
+            C e;
+            lds_coord(eb + i * kSz, e);
+            my_min = e < my_min ? e : my_min;
+        }
+        min_end = warp_min<C>(my_min);
     }
-    C min_end = warp_min<C>(my_min);
     for (int j = 0; j < 32; ++j) {
         const uint32_t hj = __shfl_sync(0xffffffffu, hi, j);
         const C qj = __shfl_sync(0xffffffffu, qs, j);
@@ -346,6 +365,12 @@ __device__ __forceinline__ void emit_tile_delta(const CoopArgs<C>& ca, uint32_t 
         }
     }
     __syncwarp();
+    carry.valid = true;
+    carry.chrom = ch0;
+    carry.len = len;
+    carry.prev_hi = prev_hi;
+    carry.min_end = min_end;
+    carry.last_qs = __shfl_sync(0xffffffffu, qs, 31);
 }
 
 // emit_walk_staged8 (intersect.cuh) for the dense-batch variant: a group of 8 ranks is first tested as a whole (max end
@@ -627,6 +652,7 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
     for (size_t t0 = (static_cast<size_t>(blockIdx.x) * kWarps + warp) * 32; t0 < n_tiles; t0 += warps_total * 32) {
         const uint32_t my_total = t0 + lane < n_tiles ? tile_total[t0 + lane] : 0u;
         uint32_t dense = __ballot_sync(0xffffffffu, my_total > stage_entries);  // candidates; dense_tile() below decides
+        DeltaCarry<C> carry;  // (sorted tiles) the candidate list left in the stage by the previous tile of this step
         while (dense != 0) {
             const uint32_t j = __ffs(dense) - 1;
             dense &= dense - 1;
@@ -656,8 +682,8 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
                 if (lane >= static_cast<uint32_t>(d)) inc += o;
             }
             const uint64_t excl = inc - c, wtotal = __shfl_sync(0xffffffffu, inc, 31);
-            const bool dense = dense_tile(wtotal, __reduce_max_sync(0xffffffffu, c), stage_entries);
-            if (!dense && (kStrand || ca.delta_min == 0 || wtotal < ca.delta_min)) continue;  // written by intersect_emit_scan_kernel itself
+            const bool is_dense = dense_tile(wtotal, __reduce_max_sync(0xffffffffu, c), stage_entries);
+            if (!is_dense && (kStrand || ca.delta_min == 0 || wtotal < ca.delta_min)) continue;  // written by intersect_emit_scan_kernel itself
             const uint64_t wbase = tile_base - block_prefix[0];
             uint32_t chrom = 0, hi = 0, qst = 0;
             C qs = 0;
@@ -670,10 +696,11 @@ intersect_emit_dense_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom
             // a coordinate-sorted tile: one shared candidate list instead of 32 walks (same predicate and values as in
             // intersect_emit_scan_kernel, which left the tile alone)
             if (!kStrand && tile_delta_ok<C>(c, hi, qs, chrom, wtotal, delta_cap<C>(stage_entries), ca.delta_min)) {
-                emit_tile_delta<C>(ca, c, hi, qs, chrom, excl, wbase, stage_addr, delta_cap<C>(stage_entries), hits, capacity);
+                emit_tile_delta<C>(ca, c, hi, qs, chrom, excl, wbase, stage_addr, delta_cap<C>(stage_entries), hits, capacity, carry);
                 continue;
             }
-            if (!dense) continue;
+            if (!is_dense) continue;
+            carry.valid = false;  // the segment flush below reuses the stage
             const uint8_t* strands = kStrand && c != 0 ? sa.strands + (tabp[chrom] - sa.slot_base) : nullptr;
             const uint64_t room = capacity > wbase ? capacity - wbase : 0ull;  // positions of this tile that fit the buffer
             emit_dense_tile<C, kStrand>(ix, tabp, stride, n_levels, chrom, qs, hi, c, excl, stage_addr, hits + wbase, room, strands, qst);
