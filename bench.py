@@ -64,7 +64,11 @@ def parse_args():
                     help="cfg5: chromosome-sharded 200M-interval build + 1B-query batch over --gpus ranks (BASELINE configs[4])")
     ap.add_argument("--cfg5-intervals", type=int, default=200_000_000)
     ap.add_argument("--cfg5-queries", type=int, default=1_000_000_000)
-    ap.add_argument("--cfg5-chunk", type=int, default=16_000_000, help="queries per rank and routed call")
+    ap.add_argument("--cfg5-chunk", type=int, default=64_000_000, help="queries per rank and routed call")
+    ap.add_argument("--cfg5-layout", default="genome_wide_chunks", choices=["contiguous", "genome_wide_chunks"],
+                    help="how the 1B-query coordinate-sorted batch reaches the ranks: contiguous = rank r reads the r-th contiguous "
+                         "part of the sorted batch and submits it in consecutive chunks (a reader of a sorted BAM) [default]; "
+                         "genome_wide_chunks = every chunk is its own sorted batch spanning the whole genome (round-2 early runs)")
     ap.add_argument("--no-multi", action="store_true", help="skip the strong-scaling / chromosome-sharded side measurements (N > 1)")
     ap.add_argument("--emit-tma", type=int, default=-1, help="pass 2 kernel: 1 TMA ring + bulk store [default], 2 TMA ring + vector stores, 0 emit_scan")
     ap.add_argument("--emit-ctas-per-sm", type=int, default=0)
@@ -339,7 +343,12 @@ def run_cfg5(args, rank, local_rank, world):
     for k in range(n_chunks):
         a, b = min(lo + k * chunk, hi), min(lo + (k + 1) * chunk, hi)
         m = b - a
-        qc, qs, qe = synth.hg38_queries(m, 150, 1000 + rank * 4096 + k, True) if m else (np.zeros(0, np.uint32),) * 3
+        if not m:
+            qc, qs, qe = (np.zeros(0, np.uint32),) * 3
+        elif args.cfg5_layout == "contiguous":
+            qc, qs, qe = synth.hg38_sorted_slice(Q, a, b, 150, 1000)
+        else:
+            qc, qs, qe = synth.hg38_queries(m, 150, 1000 + rank * 4096 + k, True)
         d_c = torch.from_numpy(np.ascontiguousarray(qc).view(np.int32)).to(dev)
         d_s = torch.from_numpy(qs.astype(np.uint32).view(np.int32)).to(dev)
         d_e = torch.from_numpy(qe.astype(np.uint32).view(np.int32)).to(dev)
@@ -380,6 +389,9 @@ def run_cfg5(args, rank, local_rank, world):
                "config": {"workload": "cfg5: bulk build of %d hg38-shaped intervals (unsorted input, 1/N per rank) + %d 150bp queries, "
                                       "chromosome-sharded over %d B200 (LPT on interval count), hit lists stay on the owner" % (N, Q, world),
                           "intervals": N, "queries": Q, "chunk_queries_per_rank": chunk, "chunks": n_chunks,
+                          "query_layout": ("ONE coordinate-sorted 1B-query batch; rank r holds its r-th contiguous part and submits it in "
+                                           "consecutive chunks" if args.cfg5_layout == "contiguous" else
+                                           "every chunk of every rank is its own coordinate-sorted batch spanning the whole genome"),
                           "parallelism": f"chromosome-sharded x{world} (gg_group rank form, NCCL)"},
                "build": {"seconds_first": float(t_build.item()), "seconds": float(t_build2.item()),
                          "intervals_per_sec": N / float(t_build2.item()),

@@ -492,9 +492,9 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
             for (Rk& r : g->rk) {
                 if (attempt == 1 && r.n_hits_owner <= r.r_hits.cap / 4) continue;
                 GGG_CUDA(cudaSetDevice(r.dev));
-                const size_t want = attempt == 0 ? static_cast<size_t>(r.hits_per_query * 1.25 * static_cast<double>(r.nq)) + 4096
+                const size_t want = attempt == 0 ? static_cast<size_t>(r.hits_per_query * static_cast<double>(r.nq)) + 4096
                                                  : static_cast<size_t>(r.n_hits_owner);
-                if (r.r_hits.cap / 4 < want) GGG_CUDA(r.r_hits.ensure(want * 4));
+                if (r.r_hits.cap / 4 < want) GGG_CUDA(r.r_hits.ensure((want + want / 4) * 4));  // (slack only when growing, see below)
                 GGG_IDX(r, gg_intersect_fused_device(r.idx, r.q_c, r.q_s, r.q_e, coord_bytes, r.nq, r.r_off.as<uint64_t>(),
                                                      r.r_hits.as<uint32_t>(), r.r_hits.cap / 4, nullptr, r.st));
             }
@@ -596,9 +596,12 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
         for (Rk& r : g->rk) {
             if (attempt == 1 && r.n_hits_owner <= r.r_hits.cap / 4) continue;
             GGG_CUDA(cudaSetDevice(r.dev));
-            const size_t want = attempt == 0 ? static_cast<size_t>(r.hits_per_query * 1.25 * static_cast<double>(r.n_recv)) + 4096
+            // grow only when the expected hits do not fit, and then with slack: re-allocating tens of GB because a chunk is a
+            // little larger than the last one cost more than the intersect itself (cfg5 on 8 GPUs: 64 M-query chunks ran at
+            // 1.9 ms per M queries against 0.3 on one GPU)
+            const size_t want = attempt == 0 ? static_cast<size_t>(r.hits_per_query * static_cast<double>(r.n_recv)) + 4096
                                              : static_cast<size_t>(r.n_hits_owner);
-            if (r.r_hits.cap / 4 < want) GGG_CUDA(r.r_hits.ensure(want * 4));
+            if (r.r_hits.cap / 4 < want) GGG_CUDA(r.r_hits.ensure((want + want / 4) * 4));
             GGG_IDX(r, gg_intersect_fused_device(r.idx, r.recv_c.as<uint32_t>(), r.recv_s.p, r.recv_e.p, coord_bytes, r.n_recv,
                                                  r.r_off.as<uint64_t>(), r.r_hits.as<uint32_t>(), r.r_hits.cap / 4, nullptr, r.st));
             // hit offsets at the source-segment boundaries (what each source gets back) ride along with the total

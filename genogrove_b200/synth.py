@@ -92,6 +92,34 @@ def hg38_queries(q: int, length: int, seed: int = 43, sorted_by_coord: bool = Tr
     return chrom, start, end
 
 
+def hg38_sorted_slice(q_total: int, lo: int, hi: int, length: int, seed: int = 43, n_chrom: int = 24):
+    """Records [lo, hi) of ONE coordinate-sorted batch of q_total fixed-length queries (chromosomes in id order, queries
+    apportioned to chromosomes by length, uniform starts) — what a reader of a sorted BAM sees in a contiguous part of the
+    file, without generating the rest: inside chromosome c the records [a, b) of its m_c sorted uniform starts are drawn as
+    b - a sorted uniform starts on the sub-range [a / m_c, b / m_c) of the chromosome (the order statistics' expected
+    span).  Deterministic in (seed, chromosome, a)."""
+    lengths = HG38_LENGTHS[:n_chrom]
+    per = _split_by_length(q_total, lengths)
+    first = np.concatenate([[0], np.cumsum(per)])
+    chrom, start = [], []
+    for c in range(n_chrom):
+        a, b = max(lo, int(first[c])) - int(first[c]), min(hi, int(first[c + 1])) - int(first[c])
+        if b <= a:
+            continue
+        m, span = int(per[c]), int(lengths[c]) - length
+        p0, p1 = a * span // m, max(b * span // m, a * span // m + 1)
+        rng = np.random.default_rng([seed, c, a])
+        s = rng.integers(p0, p1, b - a, dtype=np.int64)
+        s.sort()
+        chrom.append(np.full(b - a, c, np.uint32))
+        start.append(s.astype(np.uint64))
+    if not chrom:
+        z = np.zeros(0, np.uint64)
+        return np.zeros(0, np.uint32), z, z
+    chrom, start = np.concatenate(chrom), np.concatenate(start)
+    return chrom, start, start + np.uint64(length - 1)
+
+
 def cfg1(n: int = 100_000, q: int = 10_000, seed: int = 42) -> Workload:
     """Single chromosome of 248,956,422 bp; lengths U[200,5200); 1 kb queries (reference runs as-is)."""
     rng = np.random.default_rng(seed)

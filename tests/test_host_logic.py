@@ -79,3 +79,23 @@ def test_route_and_merge_keep_query_order():
         assert off[q + 1] - off[q] == exp
         assert (hits[int(off[q]):int(off[q + 1])] == q).all()
     assert shard.global_offset_base([5, 7, 9], 2) == 12 and shard.gather_hit_totals(11) == [11]
+
+
+def test_sorted_slice_is_a_partition_of_one_sorted_batch():
+    """synth.hg38_sorted_slice: contiguous parts of ONE coordinate-sorted batch (what bench.py --mode cfg5 hands the ranks):
+    the parts tile the batch, stay sorted across part boundaries, and follow the per-chromosome apportionment."""
+    from genogrove_b200 import synth
+    q = 200_003
+    cuts = [0, 1, 777, 25_000, 25_001, 130_000, q]
+    parts = [synth.hg38_sorted_slice(q, a, b, 150, 5) for a, b in zip(cuts[:-1], cuts[1:])]
+    c = np.concatenate([p[0] for p in parts])
+    s = np.concatenate([p[1] for p in parts]).astype(np.int64)
+    e = np.concatenate([p[2] for p in parts]).astype(np.int64)
+    assert len(c) == q and np.array_equal(e - s, np.full(q, 149))
+    assert np.array_equal(np.bincount(c, minlength=24), synth._split_by_length(q, synth.HG38_LENGTHS))
+    assert np.all(np.diff(c.astype(np.int64)) >= 0)
+    same = np.diff(c.astype(np.int64)) == 0
+    assert np.all(np.diff(s)[same] >= 0)
+    assert np.all(s >= 0) and np.all(e < synth.HG38_LENGTHS[c])
+    again = synth.hg38_sorted_slice(q, 777, 25_000, 150, 5)
+    assert np.array_equal(again[1], parts[2][1])  # deterministic
