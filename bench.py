@@ -627,6 +627,15 @@ def main():
                                               d_off.data_ptr(), d_hits.data_ptr(), d_hits.numel(), stream, sync_total=True)
 
         st_ms = timed(stranded_step, ex_steps)
+        fls_ms = None
+        try:  # flanking with the strand-compatible predicate on the same stranded index (a side number: never fatal)
+            d_pred = torch.empty(nq, dtype=torch.int32, device=dev)
+            d_succ = torch.empty(nq, dtype=torch.int32, device=dev)
+            fls_ms = timed(lambda: idx.flanking_stranded_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), d_str.data_ptr(), 4, nq,
+                                                                d_pred.data_ptr(), d_succ.data_ptr(), stream, sync=False), ex_steps)
+            del d_pred, d_succ
+        except Exception as ex:  # noqa: BLE001
+            fls_ms = repr(ex)
         del d_str
         fl_bytes = 20 * nq  # read (chrom,start,end) u32, write pred + succ u32
         st_bytes = 13 * nq + 8 * (nq + 1) + 4 * st_total[0]
@@ -638,6 +647,10 @@ def main():
                                "hits_per_query": st_total[0] / nq, "algorithmic_bytes": st_bytes,
                                "achieved_gbs": st_bytes / (st_ms / 1e3) / 1e9, "frac": st_bytes / (st_ms / 1e3) / 1e9 / peak,
                                "strands": "index: uniform over + - . ; queries: uniform over + -"},
+                  "flanking_stranded": ({"queries_per_sec": nq * world / (fls_ms / 1e3), "ms_per_step": fls_ms, "kernel": "flanking_strand_kernel",
+                                         "algorithmic_bytes": 21 * nq, "achieved_gbs": 21 * nq / (fls_ms / 1e3) / 1e9,
+                                         "frac": 21 * nq / (fls_ms / 1e3) / 1e9 / peak,
+                                         "predicate": "strand-compatible (grove_flanking.ipp:47-54)"} if isinstance(fls_ms, float) else {"error": fls_ms}),
                   "note": "per-rank device time, same index and query batch as the headline; steps=%d" % ex_steps}
 
     # ---- side measurements that need the headline buffers: the shuffled batch, strong scaling, the chromosome-sharded grove
