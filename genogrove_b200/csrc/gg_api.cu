@@ -87,6 +87,7 @@ struct gg_index {
     // chain_perm (inside bw.perm or bw.perm_alt) maps chain rank -> input index
     int chain_src = 0;
     const uint32_t* chain_perm = nullptr;
+    int64_t debug_checks = 0;    // 1: asynchronous device calls that can detect misuse synchronise and report it (gg_intersect_emit_device)
     int64_t emit_tile_list = 0;  // pass 2 on sorted tiles: 1 = one shared candidate list per 32-query tile, filtered per lane (emit_scan.cuh, kTileList)
     int64_t emit_vec_out = 0;  // pass 2 copy-out: 1 = 16-byte vector stores from a phase-aligned stage (emit_scan.cuh, kVecOut)
     int64_t delta_min_hits = 1024;  // dense-batch emit: sorted 32-query tiles with at least this many hits share one candidate list (0 = off)
@@ -363,7 +364,8 @@ inline size_t count_scratch_bytes(size_t nq) { return scan2_scratch_bytes(nq); }
 
 template <typename C, typename Q>
 gg_status launch_emit(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, size_t nq, const uint32_t* d_hi,
-                      const uint64_t* d_off, uint32_t* d_hits, uint64_t hits_base, cudaStream_t st) {
+                      const uint64_t* d_off, uint32_t* d_hits, uint64_t hits_base, cudaStream_t st,
+                      const uint32_t* d_cnt_check = nullptr) {
     auto kern = intersect_emit_kernel<C, Q>;
     size_t smem = emit_smem_bytes(idx);
     if (smem > 48 * 1024)
@@ -376,7 +378,7 @@ gg_status launch_emit(gg_index* idx, const uint32_t* d_chrom, const Q* d_start, 
     size_t tiles = div_up(nq ? nq : 1, static_cast<size_t>(kQueryThreads));
     unsigned grid = static_cast<unsigned>(std::min<size_t>(tiles, static_cast<size_t>(idx->sm_count) * per_sm));
     kern<<<grid, kQueryThreads, smem, st>>>(make_view<C>(idx), d_chrom, d_start, nq, d_hi, d_off, d_hits, hits_base,
-                                            tab_fits_smem(idx) ? 1 : 0);
+                                            tab_fits_smem(idx) ? 1 : 0, d_cnt_check, d_cnt_check ? idx->err_flag.as<uint32_t>() : nullptr);
     GG_CUDA(cudaGetLastError());
     idx->bstats.kernel_launches++;
     return GG_OK;
@@ -396,14 +398,14 @@ gg_status dispatch_count(gg_index* idx, const uint32_t* d_chrom, const void* d_s
 }
 gg_status dispatch_emit(gg_index* idx, const uint32_t* d_chrom, const void* d_start, int q_bytes, size_t nq,
                         const uint32_t* d_hi, const uint64_t* d_off, uint32_t* d_hits, uint64_t hits_base,
-                        cudaStream_t st) {
+                        cudaStream_t st, const uint32_t* d_cnt_check = nullptr) {
     if (idx->coord_bytes == 4 && q_bytes == 4)
-        return launch_emit<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+        return launch_emit<uint32_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st, d_cnt_check);
     if (idx->coord_bytes == 4 && q_bytes == 8)
-        return launch_emit<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+        return launch_emit<uint32_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st, d_cnt_check);
     if (idx->coord_bytes == 8 && q_bytes == 4)
-        return launch_emit<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
-    return launch_emit<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st);
+        return launch_emit<uint64_t, uint32_t>(idx, d_chrom, (const uint32_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st, d_cnt_check);
+    return launch_emit<uint64_t, uint64_t>(idx, d_chrom, (const uint64_t*)d_start, nq, d_hi, d_off, d_hits, hits_base, st, d_cnt_check);
 }
 
 // The one-kernel path (fused.cuh): scratch = [ticket][tile state], zeroed per launch.
@@ -1151,6 +1153,7 @@ gg_status check_query_error(gg_index* idx, cudaStream_t st) {
     GG_CUDA(cudaMemcpyAsync(&flag, idx->err_flag.p, 4, cudaMemcpyDeviceToHost, st));
     GG_CUDA(cudaStreamSynchronize(st));
     if (flag & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+    if (flag & 32u) return fail(idx, GG_ERR_INVALID_ARG, "offsets passed to gg_intersect_emit_device are not the ones gg_intersect_count_device wrote");
     return GG_OK;
 }
 
@@ -1879,12 +1882,15 @@ gg_status gg_intersect_emit_device(gg_index* idx, const uint32_t* d_chrom, const
     GG_CUDA(cudaSetDevice(idx->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (idx->timing) GG_CUDA(cudaEventRecord(idx->ev[3], st));
-    gg_status s = dispatch_emit(idx, d_chrom, d_start, coord_bytes, nq, idx->q_hi.as<uint32_t>(), d_offsets, d_hits, 0, st);
+    // (the offsets went through the caller's hands: the kernel checks them against the counts kept on the handle)
+    gg_status s = dispatch_emit(idx, d_chrom, d_start, coord_bytes, nq, idx->q_hi.as<uint32_t>(), d_offsets, d_hits, 0, st,
+                                idx->q_cnt.as<uint32_t>());
     if (s != GG_OK) return s;
     if (idx->timing) {
         GG_CUDA(cudaEventRecord(idx->ev[4], st));
         idx->ev_emit_valid = true;
     }
+    if (idx->debug_checks) return check_query_error(idx, st);  // synchronises: a debugging aid, the call is asynchronous otherwise
     return GG_OK;
 }
 
@@ -2060,6 +2066,7 @@ gg_status gg_set_option(gg_index* idx, const char* key, int64_t value) {
     else if (k == "delta_min_hits" && value >= 0 && value <= (1ll << 30)) idx->delta_min_hits = value;
     else if (k == "emit_vec_out" && (value == 0 || value == 1)) idx->emit_vec_out = value;
     else if (k == "emit_tile_list" && (value == 0 || value == 1)) idx->emit_tile_list = value;
+    else if (k == "debug_checks" && (value == 0 || value == 1)) idx->debug_checks = value;
     else if (k == "host_mode" && (value == 0 || value == 1)) idx->host_mode = value;
     else if (k == "count_mode" && value >= 0 && value <= 2) idx->count_mode = value;
     else if (k == "timing") idx->timing = value != 0;

@@ -936,7 +936,8 @@ template <typename C, typename Q>
 __global__ void __launch_bounds__(kQueryThreads)
 intersect_emit_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, const Q* __restrict__ qstart,
                       size_t nq, const uint32_t* __restrict__ hi_in, const uint64_t* __restrict__ offsets,
-                      uint32_t* __restrict__ hits, uint64_t hits_base, int tab_in_smem) {
+                      uint32_t* __restrict__ hits, uint64_t hits_base, int tab_in_smem,
+                      const uint32_t* __restrict__ cnt_check = nullptr, uint32_t* __restrict__ err_flag = nullptr) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t kStageWords = kEmitStage + kEmitSlack;
     const uint32_t* __restrict__ stab = ix.tab;  // many-contig groves: the offset table stays in global memory (L1)
@@ -958,6 +959,13 @@ intersect_emit_kernel(IndexView<C> ix, const uint32_t* __restrict__ qchrom, cons
         const size_t qa = q < nq ? q : nq, qb = q + 1 < nq ? q + 1 : nq;
         const uint64_t o0 = offsets[qa], o1 = offsets[qb];
         const uint32_t n_hits = static_cast<uint32_t>(o1 - o0);
+        // The offsets of the device two-phase API come back from the caller.  They must still be the ones the count pass
+        // wrote: a list length that differs from the count kept on the handle would make the walk fill a wrong part of the
+        // stage (or leave stale entries in it).  Such a tile is not written and bit 32 of the error flag reports it.
+        if (cnt_check != nullptr && __any_sync(0xffffffffu, q < nq && (o1 < o0 || o1 - o0 != cnt_check[q]))) {
+            if (lane == 0 && err_flag != nullptr) atomicOr(err_flag, 32u);
+            continue;
+        }
         const uint64_t wbase = __shfl_sync(0xffffffffu, o0, 0);
         const uint64_t wtotal = __shfl_sync(0xffffffffu, o1, 31) - wbase;
         if (wtotal == 0) continue;

@@ -391,6 +391,11 @@ void gg_host_free(void* p);
  * "coop_budget" (dense-batch pass 2: per-lane walk steps before the warp finishes a query's list together — 256 slots per
  * step through the per-8-slot maxima; 32 [default], 0 = per-lane walks only); "sort_geom" (onesweep tile: 0 = 256 threads
  * x 12 keys [default], 1 = 512 x 12, 2 = 256 x 8);
+ * "delta_min_hits" (dense-batch pass 2: coordinate-sorted 32-query tiles with at least this many hits share one
+ * incrementally kept candidate list instead of 32 walks; 1024 [default], 0 = off); "emit_vec_out", "emit_tile_list" (0
+ * [default] / 1: measured variants of pass 2); "debug_checks" (1: gg_intersect_emit_device synchronises and
+ * returns GG_ERR_INVALID_ARG when the offsets it was given are not the ones gg_intersect_count_device wrote — the kernel
+ * always skips such tiles instead of trusting them; 0 [default]: the call stays asynchronous);
  * "sort_legacy" (0 [default]: onesweep radix passes — one kernel per 8-bit digit with a decoupled look-back; 1: the
  * three-kernel passes of round 1 (per-CTA histogram, scan, scatter), which builds of 2^30 intervals or more always use);
  * "inject_alloc_failure" (debug: the k-th device allocation from now on fails, to drive the error paths). */

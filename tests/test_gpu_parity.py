@@ -692,6 +692,46 @@ def test_sorted_tile_candidate_list(gg, oracle, delta_min, wide):
         assert upto > cap // 2 and np.array_equal(got[:upto].view(np.uint32), exp_hits[:upto])
 
 
+def test_two_phase_device_emit_rejects_foreign_offsets(gg, oracle):
+    """gg_intersect_emit_device gets the offsets back from the caller: offsets that are not the ones the count pass wrote
+    must neither corrupt the per-warp stage nor pass silently — the kernel skips the affected tiles, and with the
+    "debug_checks" option the call synchronises and fails with GG_ERR_INVALID_ARG."""
+    import torch
+    from genogrove_b200 import GGError
+    rng = np.random.default_rng(808)
+    chrom, start, end = random_index(rng, 60_000, 2, span=500_000, max_len=800, nested=True)
+    idx = gg.DeviceIndex(0)
+    idx.build(chrom, start, end, 2)
+    nq = 100_000
+    qc, qs, qe = random_queries(rng, nq, 2, span=500_000, max_len=600)
+    exp_off, exp_hits = oracle_csr(chrom, start, end, 2, qc, qs, qe)
+    dev = torch.device("cuda:0")
+    d = [torch.from_numpy(a).to(dev) for a in (qc.view(np.int32), qs.astype(np.uint32).view(np.int32), qe.astype(np.uint32).view(np.int32))]
+    d_off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    total = idx.count_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), 4, nq, d_off.data_ptr(), st, sync_total=True)
+    assert total == len(exp_hits)
+    d_hits = torch.full((total,), -1, dtype=torch.int32, device=dev)
+    idx.set_option("debug_checks", 1)
+    idx.emit_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(), st)  # untouched: fine
+    assert np.array_equal(d_hits.cpu().numpy().view(np.uint32), exp_hits)
+    bad = d_off.clone()
+    bad[50_001:50_020] += 40_000       # lists that claim to be far longer than the stage
+    bad[70_000] -= 3                   # and one that shrinks / goes backwards
+    d_hits.fill_(-1)
+    with pytest.raises(GGError) as ei:
+        idx.emit_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), 4, nq, bad.data_ptr(), d_hits.data_ptr(), st)
+    assert ei.value.status == 1
+    got = d_hits.cpu().numpy().view(np.uint32)
+    lo, hi = int(exp_off[49_920]), int(exp_off[50_176])   # the 256-query tile around the first tampering is left alone ...
+    assert np.array_equal(got[:lo], exp_hits[:lo])       # ... everything before it is exact
+    assert (got[lo:hi] == 0xFFFFFFFF).any()
+    idx.set_option("debug_checks", 0)
+    idx.count_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), 4, nq, d_off.data_ptr(), st, sync_total=True)
+    idx.emit_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), 4, nq, bad.data_ptr(), d_hits.data_ptr(), st)  # asynchronous form: no crash
+    torch.cuda.synchronize()
+
+
 def test_smoke_entry(gg, oracle):
     import __graft_entry__ as ge
     ge.smoke()
