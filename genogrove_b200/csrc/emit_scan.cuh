@@ -297,10 +297,14 @@ __device__ __forceinline__ void emit_tile_delta(const CoopArgs<C>& ca, uint32_t 
         }
         min_end = warp_min<C>(my_min);
     }
-    for (int j = 0; j < 32; ++j) {
+    // the tile's lists are consecutive in the CSR and each has exactly as many entries as the list kept here: the output
+    // position runs along with it (no per-query offset shuffle); the capacity is tested once per tile when everything fits
+    uint64_t oj = wbase + __shfl_sync(0xffffffffu, excl, 0);
+    const uint64_t tile_end = wbase + __shfl_sync(0xffffffffu, excl, 31) + __shfl_sync(0xffffffffu, c, 31);
+    const bool fits = tile_end <= capacity;
+    for (int j = 0; j < 32; ++j, oj += len) {
         const uint32_t hj = __shfl_sync(0xffffffffu, hi, j);
         const C qj = __shfl_sync(0xffffffffu, qs, j);
-        const uint64_t oj = wbase + __shfl_sync(0xffffffffu, excl, j);
         if (hj != prev_hi) {  // new members: the ranks whose start lies in (q_{j-1}.end, q_j.end]
             const uint32_t add = hj - prev_hi;
             C m = coord_max<C>::value;
@@ -316,7 +320,7 @@ __device__ __forceinline__ void emit_tile_delta(const CoopArgs<C>& ca, uint32_t 
             prev_hi = hj;
             __syncwarp();
         }
-        const uint64_t room64 = capacity > oj ? capacity - oj : 0ull;
+        const uint64_t room64 = fits ? 0xFFFFFFFFull : (capacity > oj ? capacity - oj : 0ull);
         if (min_end < qj) {
             // at least one member ended before q_j.start: ONE pass filters the list, writes the survivors out and compacts
             // the list in place (queries sparser than the index lose a member at almost every step; a separate compaction
