@@ -72,17 +72,25 @@ def global_offset_base(totals: List[int], rank: int) -> int:
 
 def merge_routed_results(nq: int, parts) -> Tuple[np.ndarray, np.ndarray]:
     """Chromosome-sharded mode: combine per-rank (query_index, offsets, hits) into one CSR in original query
-    order.  Each query was answered by at most one rank."""
+    order.  Each query was answered by at most one rank.  Vectorised (no per-query loop): the destination of hit k of a
+    part is offsets[query of k] + (k - first hit of that query), both obtained with one np.repeat per part — the host-side
+    twin of gather_lists_kernel (genogrove_b200/csrc/gg_group.cu), which does this on the source GPU inside
+    gg_group_intersect_batch; this function only serves host-side tests and tools."""
     counts = np.zeros(nq, dtype=np.uint64)
     for qidx, off, _ in parts:
-        counts[qidx] = np.diff(off)
+        counts[np.asarray(qidx, dtype=np.int64)] = np.diff(np.asarray(off, dtype=np.uint64))
     offsets = np.zeros(nq + 1, dtype=np.uint64)
     np.cumsum(counts, out=offsets[1:])
     hits = np.zeros(int(offsets[-1]), dtype=np.uint32)
     for qidx, off, h in parts:
-        for j, qi in enumerate(qidx):
-            a, b = int(off[j]), int(off[j + 1])
-            if b > a:
-                o = int(offsets[qi])
-                hits[o:o + (b - a)] = h[a:b]
+        qidx = np.asarray(qidx, dtype=np.int64)
+        off = np.asarray(off, dtype=np.int64)
+        n = int(off[-1] - off[0]) if len(off) else 0
+        if n == 0:
+            continue
+        per = np.diff(off)
+        src_first = np.repeat(off[:-1], per)                      # first hit (in the part) of the query each hit belongs to
+        dst_first = np.repeat(offsets[qidx].astype(np.int64), per)
+        k = np.arange(int(off[0]), int(off[-1]), dtype=np.int64)
+        hits[dst_first + (k - src_first)] = np.asarray(h)[k]
     return offsets, hits
