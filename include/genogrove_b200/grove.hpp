@@ -294,6 +294,17 @@ class batch_result {
         for (std::size_t j = 0; j < count(q); ++j) out.push_back(key(q, j));
         return out;
     }
+    /// Copy the rank array out of the library's pinned buffer into this object: afterwards the result survives later
+    /// queries on the grove (it still refers to the grove's keys, so not its mutation or destruction).  Costs one memcpy of
+    /// 4 bytes per hit; results that are consumed before the next query do not need it.
+    batch_result& keep() {
+        if (hits_ != nullptr && hits_ != owned_.data()) {
+            owned_.assign(hits_, hits_ + n_hits_);
+            hits_ = owned_.data();
+        }
+        return *this;
+    }
+    [[nodiscard]] bool owns_ranks() const noexcept { return hits_ == owned_.data() && hits_ != nullptr; }
 
   private:
     template <typename, typename, typename>
@@ -301,6 +312,7 @@ class batch_result {
     std::vector<std::uint64_t> offsets_;
     const std::uint32_t* hits_ = nullptr;
     std::uint64_t n_hits_ = 0;
+    std::vector<std::uint32_t> owned_;                         // keep(): the ranks, once copied out of the pinned buffer
     std::vector<std::uint32_t> q_index_;                       // copy of the per-query index ids
     std::vector<const std::vector<key_ptr>*> chains_;          // index id -> chain (rank -> key*)
 };

@@ -762,6 +762,15 @@ static void test_batch_entry_point() {
         total += r.get_keys().size();
     }
     CHECK(total > 0);
+    {   // keep(): a result that outlives the next query on the grove
+        auto kept = g.intersect_batch(qc.data(), qs.data(), qe.data(), nq);
+        kept.keep();
+        CHECK(kept.owns_ranks());
+        (void)g.intersect_batch(qc.data(), qe.data(), qe.data(), nq);  // overwrites the library's pinned buffer
+        bool ok = true;
+        for (std::size_t i = 0; i < nq; i += 3) ok = ok && kept.get_keys(i) == got[i];
+        CHECK(ok);
+    }
     std::vector<std::uint64_t> bad_s{10}, bad_e{5};
     std::vector<std::uint32_t> bad_c{ids[0]};
     CHECK_THROWS(g.intersect_batch(bad_c.data(), bad_s.data(), bad_e.data(), 1), std::invalid_argument);
