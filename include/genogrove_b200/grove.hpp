@@ -919,19 +919,28 @@ class grove {
             }
         };
         const std::size_t new_ids = next_id - std::min(next_id, device_n_chrom);
-        if (snapshot_valid && n_changed + emptied_ids.size() + new_ids <= max_partial_updates && 2 * changed <= total) {
+        bool partial = snapshot_valid && n_changed + emptied_ids.size() + new_ids <= max_partial_updates && 2 * changed <= total;
+        if (partial) {
+            // GG_ERR_NOT_BUILT: the handle no longer holds the chains (its build workspace was dropped) -> whole upload below
+            auto update = [&](std::uint32_t id, const std::uint64_t* s, const std::uint64_t* e, std::size_t n) {
+                const gg_status st = gg_index_update_chrom(dev.get(), id, s, e, n);
+                if (st == GG_ERR_NOT_BUILT) return false;
+                check(st);
+                return true;
+            };
             std::vector<std::uint64_t> s, e;
             for (const std::uint32_t id : emptied_ids)
-                if (id < device_n_chrom) check(gg_index_update_chrom(dev.get(), id, nullptr, nullptr, 0));
-            for (std::uint32_t id = 0; id < next_id; ++id) {
+                if (partial && id < device_n_chrom) partial = update(id, nullptr, nullptr, 0);
+            for (std::uint32_t id = 0; partial && id < next_id; ++id) {
                 chain_state* ch = by_id[id];
                 if (id < device_n_chrom && (ch == nullptr || !ch->dirty)) continue;
                 s.clear(), e.clear();
                 if (ch != nullptr) flatten(*ch, s, e);  // (an id created and retired between two syncs is appended empty)
-                check(gg_index_update_chrom(dev.get(), id, s.data(), e.data(), s.size()));
-                ++partial_updates;
+                partial = update(id, s.data(), e.data(), s.size());
+                if (partial) ++partial_updates;
             }
-        } else {
+        }
+        if (!partial) {
             std::vector<std::uint32_t> c;
             std::vector<std::uint64_t> s, e;
             c.reserve(total), s.reserve(total), e.reserve(total);

@@ -886,6 +886,24 @@ static void test_snapshot_cost_model() {
     CHECK(g.intersect(interval(0, 3), "chr6").get_keys().size() >= 1);
     CHECK(g.full_upload_count() == 1);
 
+    // the handle dropped its build workspace (no chains on the device any more): the next mutation falls back to one
+    // whole upload instead of failing
+    CHECK(gg_set_option(g.device_handle(), "keep_build_workspace", 0) == GG_OK);
+    const std::size_t full_before = g.full_upload_count(), partial_before = g.partial_update_count();
+    g.insert_data("chr1", interval(77, 88), 4242);
+    per_index.insert_data("chr1", interval(77, 88), 4242);
+    CHECK(sweep(g, per_index));
+    CHECK(g.full_upload_count() == full_before + 1 && g.partial_update_count() == partial_before);
+    CHECK(gg_set_option(g.device_handle(), "keep_build_workspace", 1) == GG_OK);
+    g.insert_data("chr2", interval(78, 89), 4243);  // (that upload ran without a kept workspace: one more whole upload ...)
+    per_index.insert_data("chr2", interval(78, 89), 4243);
+    CHECK(sweep(g, per_index));
+    CHECK(g.full_upload_count() == full_before + 2 && g.partial_update_count() == partial_before);
+    g.insert_data("chr2", interval(79, 90), 4244);  // (... which leaves the chains on the device: single-index updates again)
+    per_index.insert_data("chr2", interval(79, 90), 4244);
+    CHECK(sweep(g, per_index));
+    CHECK(g.full_upload_count() == full_before + 2 && g.partial_update_count() == partial_before + 1);
+
     // genomic_coordinate keys: the multi-index build leaves a usable stranded snapshot too
     using gcoord = facade_api::genomic_coordinate;
     gst::grove<gcoord, int> sg(5), sg_ref(5);
