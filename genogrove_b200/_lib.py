@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("GG_B200_LIB") or os.path.join(_HERE, "libgg_b200.so")
 
 NO_CHROM = 0xFFFFFFFF
 NO_RANK = 0xFFFFFFFF
+STATIC_MAX_QUERIES = 1048576  # GG_STATIC_MAX_QUERIES: per-call limit of gg_intersect_fused_device_static
 GG_OK = 0
 STATUS_NAMES = {
     0: "GG_OK",
@@ -33,7 +34,7 @@ EXPORTS = (
     "gg_index_build", "gg_index_build_device", "gg_index_upload_sorted", "gg_index_update_chrom", "gg_index_get_stats", "gg_index_chrom_counts",
     "gg_intersect_batch", "gg_intersect_batch_u32", "gg_intersect_batch_compact", "gg_compact_count", "gg_compact_rank",
     "gg_compact_expand", "gg_intersect_count", "gg_intersect_emit",
-    "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_last_batch_stats",
+    "gg_intersect_count_device", "gg_intersect_emit_device", "gg_intersect_fused_device", "gg_intersect_fused_device_static", "gg_last_batch_stats",
     "gg_host_alloc", "gg_host_free", "gg_set_option",
     "gg_flanking_batch", "gg_flanking_device", "gg_flanking_batch_stranded", "gg_flanking_stranded_device",
     "gg_index_set_strands", "gg_intersect_batch_stranded", "gg_intersect_stranded_device",
@@ -120,6 +121,7 @@ def lib():
     L.gg_intersect_count_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, _u64p, vp]
     L.gg_intersect_emit_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, vp]
     L.gg_intersect_fused_device.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_uint64, _u64p, vp]
+    L.gg_intersect_fused_device_static.argtypes = [vp, vp, vp, vp, C.c_int, C.c_size_t, vp, vp, C.c_uint64, _u64p, vp]
     L.gg_last_batch_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.gg_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.gg_host_free.argtypes = [vp]

@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <thread>
@@ -2502,6 +2503,110 @@ gg_status gg_intersect_batch_stranded(gg_index* idx, const uint32_t* q_chrom, co
     *hits = idx->pinned_hits;
     *n_hits = base;
     idx->bstats.n_hits = base;
+    return GG_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------ allocation-free single call
+//
+// gg_intersect_fused_device_static: the one-kernel single-call path (fused.cuh) for callers that must not allocate
+// device memory at query time.  Three kinds of caller are in that position: a service that handed all of its HBM to its
+// own pool at start-up, so a cudaMalloc from this library would simply fail; a process that shares the GPU with a
+// framework whose caching allocator already reserved the free memory; and a latency-bound loop, where cudaMalloc's
+// implicit device synchronisation and unbounded duration are not acceptable on the query path.  The regular entry point
+// grows a scratch buffer on the handle whenever it meets a larger batch; this one never does.  Its scratch — the tile
+// ticket and one 64-bit look-back word per 256 queries, plus the 16-byte error / hit-total mailbox — sits in a
+// fixed-size array in the library's device data segment instead.
+namespace {
+
+constexpr size_t kStaticMailboxBytes = 16;  // [0, 4) error flag, [8, 16) hit total
+constexpr size_t kStaticTiles = (static_cast<size_t>(GG_STATIC_MAX_QUERIES) + kQueryThreads - 1) / kQueryThreads;
+// mailbox + what launch_fused lays out ([ticket, padded to 16 B][state u64 x tiles]), rounded to the 256-byte alignment
+constexpr size_t kStaticScratchBytes = ((kStaticMailboxBytes + 16 + kStaticTiles * 8 + 255) / 256) * 256;
+
+// One copy per GPU that loads the library (33 KB each), held until the process exits.  In host code this name is only a
+// handle for the runtime's symbol table, NOT a device address: the pointer the kernel gets comes from
+// cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_addr[kStaticMaxDevices] = {};
+
+// Device address of g_static_scratch on `device`, which must be the current device.  Resolved once per device.
+cudaError_t static_scratch_on(int device, unsigned char** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_addr[device]) {
+        int current = -1;
+        cudaError_t e = cudaGetDevice(&current);
+        if (e != cudaSuccess) return e;
+        if (current != device) return cudaErrorInvalidDevice;
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_static_addr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_addr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" {
+
+gg_status gg_intersect_fused_device_static(gg_index* idx, const uint32_t* d_chrom, const void* d_start, const void* d_end,
+                                           int coord_bytes, size_t nq, uint64_t* d_offsets, uint32_t* d_hits,
+                                           uint64_t capacity, uint64_t* total_hits, void* stream) {
+    if (!idx) return GG_ERR_INVALID_ARG;
+    idx->err.clear();
+    if (!idx->built) return fail(idx, GG_ERR_NOT_BUILT, "index not built");
+    if (!d_offsets || (capacity && !d_hits) || (nq && (!d_chrom || !d_start || !d_end)))
+        return fail(idx, GG_ERR_INVALID_ARG, "null argument");
+    if (coord_bytes != 4 && coord_bytes != 8) return fail(idx, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
+    if (coord_bytes == 4 && idx->coord_bytes != 4) return fail(idx, GG_ERR_INVALID_ARG, "u32 queries need a u32-layout index");
+    if (nq > static_cast<size_t>(GG_STATIC_MAX_QUERIES))
+        return fail(idx, GG_ERR_CAPACITY,
+                    "gg_intersect_fused_device_static: more than GG_STATIC_MAX_QUERIES (1048576) queries in one call; split the "
+                    "batch or use gg_intersect_fused_device");
+    GG_CUDA(cudaSetDevice(idx->device));
+    unsigned char* scratch = nullptr;
+    GG_CUDA(static_scratch_on(idx->device, &scratch));  // first call on this device: cudaGetSymbolAddress
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint32_t* d_err = reinterpret_cast<uint32_t*>(scratch);
+    uint64_t* d_total = reinterpret_cast<uint64_t*>(scratch + 8);
+    idx->bstats = gg_batch_stats{};
+    idx->bstats.n_queries = nq;
+    idx->bstats.n_chunks = 1;
+    idx->ev_count_valid = idx->ev_emit_valid = false;
+    // the array keeps what the previous call left: the mailbox is cleared here, ticket + look-back words by launch_fused
+    GG_CUDA(cudaMemsetAsync(scratch, 0, kStaticMailboxBytes, st));
+    void* lookback = scratch + kStaticMailboxBytes;
+    gg_status s;
+    if (idx->coord_bytes == 4 && coord_bytes == 4)
+        s = launch_fused<uint32_t, uint32_t>(idx, d_chrom, static_cast<const uint32_t*>(d_start), static_cast<const uint32_t*>(d_end), nq,
+                                             d_offsets, d_hits, capacity, nullptr, nullptr, d_total, lookback, d_err, st);
+    else if (idx->coord_bytes == 4)
+        s = launch_fused<uint32_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start), static_cast<const uint64_t*>(d_end), nq,
+                                             d_offsets, d_hits, capacity, nullptr, nullptr, d_total, lookback, d_err, st);
+    else if (coord_bytes == 4)
+        s = launch_fused<uint64_t, uint32_t>(idx, d_chrom, static_cast<const uint32_t*>(d_start), static_cast<const uint32_t*>(d_end), nq,
+                                             d_offsets, d_hits, capacity, nullptr, nullptr, d_total, lookback, d_err, st);
+    else
+        s = launch_fused<uint64_t, uint64_t>(idx, d_chrom, static_cast<const uint64_t*>(d_start), static_cast<const uint64_t*>(d_end), nq,
+                                             d_offsets, d_hits, capacity, nullptr, nullptr, d_total, lookback, d_err, st);
+    if (s != GG_OK) return s;
+    if (total_hits) {
+        uint32_t mailbox[4] = {0, 0, 0, 0};  // on the stack: the handle's pinned mailbox may not exist yet and is not created here
+        GG_CUDA(cudaMemcpyAsync(mailbox, scratch, kStaticMailboxBytes, cudaMemcpyDeviceToHost, st));
+        GG_CUDA(cudaStreamSynchronize(st));
+        std::memcpy(total_hits, mailbox + 2, 8);
+        idx->bstats.n_hits = *total_hits;
+        if (mailbox[0] & 1u) return fail(idx, GG_ERR_INVALID_INTERVAL, "query interval: start must be <= end");
+        if (mailbox[0] & 2u) return fail(idx, GG_ERR_CAPACITY, "hit buffer smaller than offsets[nq]; offsets are complete");
+    }
     return GG_OK;
 }
 

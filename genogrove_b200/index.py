@@ -179,6 +179,19 @@ class DeviceIndex:
         self._check(st)
         return self.last_total
 
+    def fused_device_static(self, d_chrom: int, d_start: int, d_end: int, coord_bytes: int, nq: int, d_offsets: int,
+                            d_hits: int, capacity: int, stream: int = 0, sync_total: bool = False):
+        """gg_intersect_fused_device_static: same contract as :meth:`fused_device`, for callers that may not allocate
+        device memory while querying (their HBM is fully handed to a pool, or cudaMalloc's stall is unacceptable).  The
+        library's scratch is a fixed array on the device, so at most ``STATIC_MAX_QUERIES`` queries per call (status 7
+        beyond that) and calls that overlap on one GPU race — keep them on one stream."""
+        total = C.c_uint64(0)
+        st = self._L.gg_intersect_fused_device_static(self._h, d_chrom, d_start, d_end, coord_bytes, nq, d_offsets, d_hits,
+                                                      int(capacity), C.byref(total) if sync_total else None, stream or None)
+        self.last_total = int(total.value) if sync_total else None
+        self._check(st)
+        return self.last_total
+
     # ------------------------------------------------------------------ flanking (nearest predecessor / successor)
     def flanking_batch(self, q_chrom, q_start, q_end):
         """gg_flanking_batch: (pred u32[Q], succ u32[Q]) per-chromosome chain ranks, NO_RANK when absent."""

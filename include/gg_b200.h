@@ -224,6 +224,29 @@ gg_status gg_intersect_fused_device(gg_index* idx, const uint32_t* d_chrom, cons
                                     const void* d_end, int coord_bytes, size_t nq, uint64_t* d_offsets,
                                     uint32_t* d_hits, uint64_t capacity, uint64_t* total_hits, void* stream);
 gg_status gg_last_batch_stats(const gg_index* idx, gg_batch_stats* out);
+/* ---- single call without any allocation (no counterpart in the reference) ------------------------------------------ */
+/* Nothing in genogrove corresponds to this: it exists for callers of THIS library that may not allocate device memory
+ * while they query — a service that gave all of its HBM to its own pool at start-up (a cudaMalloc from here would just
+ * fail), a process whose GPU memory is already reserved by another framework's caching allocator, or a latency-bound loop
+ * that cannot take cudaMalloc's implicit device synchronisation.  gg_intersect_fused_device grows a scratch buffer on the
+ * handle when a batch is larger than any before it; this variant calls no cudaMalloc / cudaFree / cudaHostAlloc and no
+ * library routine that does, ever.
+ *   - Same arguments, results and status codes as gg_intersect_fused_device (always the one-kernel form, whatever the
+ *     "fused_kernel" option says); the index must have been built beforehand, the caller owns every input and output.
+ *   - Scratch (tile ticket, one look-back word per 256 queries, the 16-byte error / total mailbox) is a fixed array in the
+ *     library's device data segment: 33 KB on every GPU that loads the library, held until the process exits.
+ *   - Limit: nq <= GG_STATIC_MAX_QUERIES per call.  More -> GG_ERR_CAPACITY, nothing is launched; split the batch or use
+ *     the regular call.
+ *   - The first call on each device looks the array's device address up (cudaGetSymbolAddress, with that device
+ *     current).  Make that first call during set-up, before any stream capture is started on the device.
+ *   - All calls on one GPU — across handles and threads — share the one array, which still holds whatever the previous
+ *     call left; each call clears the parts that must start at zero on `stream` before its kernel.  Two calls whose
+ *     kernels can overlap on the GPU (different streams with no ordering between them) race on it and return garbage:
+ *     order them on one stream or with events.  The host side may return before the kernel ran unless total_hits is given. */
+#define GG_STATIC_MAX_QUERIES 1048576
+gg_status gg_intersect_fused_device_static(gg_index* idx, const uint32_t* d_chrom, const void* d_start,
+                                           const void* d_end, int coord_bytes, size_t nq, uint64_t* d_offsets,
+                                           uint32_t* d_hits, uint64_t capacity, uint64_t* total_hits, void* stream);
 
 /* ---- batched flanking (nearest predecessor / successor) ------------------------------------------ */
 /* Replaces grove::flanking(query, index) -> detail::search_flanking for interval keys with the default
