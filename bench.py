@@ -207,6 +207,44 @@ def timed_ms(torch, fn, n, warm=3):
     return a.elapsed_time(b) / n
 
 
+def other_configs(torch, dev, peak, steps=10):
+    """BASELINE.json's other single-GPU configurations, device-resident, at full size (N = 1 only): configs[1] (1M intervals x
+    10M 1-kb queries, random and coordinate-sorted) and configs[2] (GENCODE-shaped nested features x 50M queries).  Same
+    single call and same timing rules as the headline (CUDA events, 3 warm-up calls, inputs and outputs far larger than L2);
+    a total-hits check against the two-phase count pass guards each number."""
+    from genogrove_b200 import DeviceIndex, synth
+    out = {}
+    for name, make in (("cfg2_random", lambda: synth.cfg2(sorted_queries=False)), ("cfg2_sorted", lambda: synth.cfg2(sorted_queries=True)),
+                       ("cfg3_gencode", lambda: synth.cfg3())):
+        w = make()
+        nq = len(w.q_chrom)
+        idx = DeviceIndex(dev.index)
+        idx.build(w.chrom, w.start, w.end, w.n_chrom, want_perm=False)
+        d_c = torch.from_numpy(w.q_chrom.view(np.int32)).to(dev)
+        d_s = torch.from_numpy(w.q_start.astype(np.uint32).view(np.int32)).to(dev)
+        d_e = torch.from_numpy(w.q_end.astype(np.uint32).view(np.int32)).to(dev)
+        d_off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
+        st = torch.cuda.current_stream().cuda_stream
+        total = idx.count_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), st, sync_total=True)
+        d_hits = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+
+        def step():
+            t = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(),
+                                 d_hits.numel(), st, sync_total=True)
+            assert t == total, (name, t, total)
+
+        ms = timed_ms(torch, step, steps)
+        b = 12 * nq + 8 * (nq + 1) + 4 * total
+        out[name] = {"workload": w.name, "intervals": int(len(w.chrom)), "queries": nq, "hits": int(total),
+                     "hits_per_query": total / nq, "ms_per_step": ms, "queries_per_sec": nq / (ms / 1e3),
+                     "hit_pairs_per_sec": total / (ms / 1e3), "algorithmic_bytes": b, "path_frac": b / (ms / 1e3) / 1e9 / peak,
+                     "kernel_launches": int(idx.batch_stats().kernel_launches)}
+        del d_c, d_s, d_e, d_off, d_hits, w
+        idx.close()
+        torch.cuda.empty_cache()
+    return out
+
+
 def copy_ceiling(torch, dev, h2d_bytes, d2h_bytes, barrier, dist, reps=3):
     """Bare concurrent pinned copies of the e2e call's byte counts on two streams (all ranks at once): the box's ceiling for
     that result form.  Returns per-rank GB/s both ways and the queries/s it would allow (filled in by the caller's ratio)."""
@@ -252,7 +290,31 @@ def make_group(torch, dist, dev, rank, world):
     return DeviceGroup.from_rank(dev.index, rank, world, bytes(idt.cpu().numpy().tobytes()))
 
 
-def chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e, nq, steps=5):
+def _device_copy(torch, dev, ptr, n, dtype):
+    """A torch tensor holding a copy of n elements of library-owned device memory (plain cudaMemcpy, device to device)."""
+    import ctypes as C
+    t = torch.empty(max(int(n), 1), dtype=dtype, device=dev)
+    if n:
+        rt = C.CDLL("libcudart.so.12")
+        rc = rt.cudaMemcpy(C.c_void_p(t.data_ptr()), C.c_void_p(ptr), C.c_size_t(int(n) * t.element_size()), 3)
+        if rc != 0:
+            raise RuntimeError(f"cudaMemcpy D2D failed: {rc}")
+    return t[:int(n)]
+
+
+def _csr_checksum(torch, off, hits, ids):
+    """Two wrapping int64 sums over a CSR whose queries carry job-wide ids: sum(count_q * w(id_q)) and
+    sum((sum of (rank + 1) over q's hits) * w(id_q)) with w an odd multiplicative hash — independent of where a query was
+    answered and in which order the queries are listed, so the routed result can be compared with the replicated one."""
+    w = ids * -7046029254386353131 + 1442695040888963407  # (wraps; 0x9E3779B97F4A7C15 as int64)
+    cnt = off[1:] - off[:-1]
+    cs = torch.zeros(hits.numel() + 1, dtype=torch.int64, device=hits.device)
+    torch.cumsum(hits.to(torch.int64) + 1, 0, out=cs[1:])
+    seg = cs[off[1:]] - cs[off[:-1]]
+    return torch.stack([(cnt * w).sum(), (seg * w).sum(), cnt.sum()])
+
+
+def chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e, nq, idx, d_off, d_hits, stream, steps=5):
     """The cfg4 grove sharded by chromosome over the N ranks (gg_group_*, GG_SHARD_CHROM): every rank passes its slice of the
     interval input (records routed to their owners), then its own 100M-query batch is routed to the owners and answered there
     (hit lists stay on the owner: return_to_source = 0), and — second number — returned to the source in original order."""
@@ -265,6 +327,13 @@ def chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e
     dist.all_reduce(build_ms, op=dist.ReduceOp.MAX)
     out = {"build_ms": float(build_ms.item()), "intervals": int(len(c)),
            "owners": grp.owners(24).tolist()}
+    # the replicated index's answer to this rank's batch: what the routed results are checked against below
+    ref_total = idx.fused_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, d_off.data_ptr(), d_hits.data_ptr(),
+                                 d_hits.numel(), stream, sync_total=True)
+    torch.cuda.synchronize()
+    ref_sum = _csr_checksum(torch, d_off, d_hits[:ref_total], torch.arange(nq, dtype=torch.int64, device=dev) + rank * nq)
+    dist.all_reduce(ref_sum)  # (int64 sums wrap the same way on both sides)
+    verified = {}
     for back in (False, True):
         def step():
             return grp.intersect_device(d_c.data_ptr(), d_s.data_ptr(), d_e.data_ptr(), 4, nq, return_to_source=back)
@@ -279,6 +348,25 @@ def chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e
         dt = torch.tensor([(time.perf_counter() - t0) / steps], dtype=torch.float64, device=dev)
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         st = grp.stats()
+        # ---- parity of the routed result with the replicated index (untimed)
+        r_off = _device_copy(torch, dev, res.d_offsets, res.n_queries + 1, torch.int64)
+        r_hits = _device_copy(torch, dev, res.d_hits, res.n_hits, torch.int32)
+        if back:  # this rank's own CSR in original query order: bit for bit
+            same = bool(res.n_queries == nq and res.n_hits == ref_total and torch.equal(r_off, d_off) and
+                        torch.equal(r_hits, d_hits[:ref_total]))
+            flag = torch.tensor([1 if same else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            verified["returned_to_source"] = {"equal_to_replicated_csr": bool(flag.item()), "check": "torch.equal on offsets and hits, every rank"}
+        else:     # hit lists stay on the owner: job-wide checksums keyed by (source rank, query index)
+            origin = _device_copy(torch, dev, res.d_origin, res.n_queries, torch.int64)
+            ids = (origin >> 40) * nq + (origin & ((1 << 40) - 1))
+            got = _csr_checksum(torch, r_off, r_hits, ids)
+            dist.all_reduce(got)
+            verified["results_on_owner"] = {"equal_to_replicated_checksums": bool(torch.equal(got, ref_sum)),
+                                            "hits_job": int(got[2].item()), "hits_job_replicated": int(ref_sum[2].item()),
+                                            "check": "sum(count_q * w(id_q)), sum(sum_hits_q(rank + 1) * w(id_q)), sum(count_q) over all ranks, int64 wrapping"}
+            del origin, ids
+        del r_off, r_hits
         per = torch.tensor([st.n_answered, st.n_hits, st.bytes_sent, st.route_ms, st.exchange_ms, st.intersect_ms, st.return_ms],
                            dtype=torch.float64, device=dev)
         allp = [torch.zeros_like(per) for _ in range(world)]
@@ -294,6 +382,9 @@ def chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e
                                         "intersect": float(allp[:, 5].max()), "return": float(allp[:, 6].max())},
             "timer": "host wall clock around the synchronising C ABI call, max over ranks (the call reads count matrices and hit totals back)"}
         del res
+    out["verified"] = verified
+    if not all(v.get("equal_to_replicated_csr", v.get("equal_to_replicated_checksums")) for v in verified.values()):
+        raise RuntimeError(f"chromosome-sharded result differs from the replicated index: {verified}")
     out["note"] = ("gg_group rank form over NCCL: LPT chromosome owners, device-side stable partition by owner, all-to-all-v of "
                    "(chrom, start, end) as grouped ncclSend/ncclRecv, gg_intersect_fused_device on the owner")
     grp.close()
@@ -705,7 +796,7 @@ def main():
 
     chrom_shard = None
     if world > 1 and not args.no_multi:
-        chrom_shard = chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e, nq)
+        chrom_shard = chrom_shard_side(args, torch, dist, dev, rank, world, c, s, e, d_c, d_s, d_e, nq, idx, d_off, d_hits, stream)
 
     # ---- e2e: host-buffer C ABI calls with pinned buffers, H2D + D2H inside the timed region
     e2e = None
@@ -791,6 +882,12 @@ def main():
         v1, info1 = cpu_reference_run(args, w, steps=1, warmup=0, threads=1) if v else (None, None)
         if v1:
             cpu["single_thread_value"] = v1
+
+    # ---- BASELINE configs[1] and [2] (parity cases in tests/test_gpu_configs.py; timed here so the driver's record has them)
+    if world == 1 and not args.no_extras and not args.shuffled and extras is not None:
+        del idx
+        torch.cuda.empty_cache()
+        extras["configs"] = other_configs(torch, dev, peak)
 
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -1692,7 +1692,7 @@ void gg_index_destroy(gg_index* idx) {
     cudaDeviceSynchronize();
     for (DeviceBuf* b : {&idx->S, &idx->E, &idx->M, &idx->tab, &idx->cnt, &idx->dirS, &idx->dirE, &idx->dir_off, &idx->fused_scratch, &idx->fused_out, &idx->q_cnt, &idx->q_hi, &idx->scan_scratch,
                          &idx->err_flag, &idx->h2_qc, &idx->h2_qs, &idx->h2_qe, &idx->h2_off, &idx->h2_hits, &idx->d_base,
-                         &idx->ER, &idx->cbegin, &idx->cslot, &idx->flat[0], &idx->flat[1], &idx->flat[2], &idx->flat[3], &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
+                         &idx->ER, &idx->cbegin, &idx->cslot, &idx->flat[0], &idx->flat[1], &idx->flat[2], &idx->flat[3], &idx->m8, &idx->strand, &idx->SN, &idx->EN, &idx->sq_qc, &idx->sq_qs, &idx->sq_qe, &idx->sq_str, &idx->sq_off, &idx->sq_hits,
                          &idx->s_cnt, &idx->s_hi, &idx->s_tile, &idx->s_scan, &idx->s_total})
         b->release();
     for (auto& s : idx->slots) {

@@ -139,9 +139,12 @@ __global__ void origin_kernel(const uint32_t* __restrict__ orig, size_t n, const
                               uint64_t* __restrict__ origin) {
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    uint32_t p = 0;
-    while (p + 1 < W && seg[p + 1] <= i) ++p;
-    origin[i] = (static_cast<uint64_t>(p) << 40) | orig[i];
+    uint32_t lo = 0, hi = W;  // last p with seg[p] <= i (seg[0] = 0, non-decreasing; empty sources share a value)
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (seg[mid] <= i) lo = mid; else hi = mid;
+    }
+    origin[i] = (static_cast<uint64_t>(lo) << 40) | orig[i];
 }
 
 // Hit lists back into original query order.  Source lists are in partition order j (b_off = scan of the counts that came
@@ -194,6 +197,7 @@ struct Rk {
     DeviceBuf r_off, r_hits, r_cnt, origin, d_seg;                  // owner-side result
     DeviceBuf b_cnt, b_off, b_hits, f_cnt, f_off, f_hits, scan2;    // source side
     DeviceBuf d_mat;                                                // W x W count matrix (rank form)
+    DeviceBuf d_agree;                                              // W status words (rank form), allocated at creation
     uint64_t* h_box = nullptr;                                      // pinned: [W + 1] bounds + W x W matrix + scratch
     std::vector<uint64_t> soff, roff, hsoff, hroff;                 // W + 1 each
     size_t nq = 0, n_recv = 0;
@@ -268,7 +272,8 @@ gg_status init_rank_ctx(gg_group* g, Rk& r, int dev, int rank) {
     GGG_CUDA(cudaEventCreateWithFlags(&r.ev_done, cudaEventDisableTiming));
     for (auto& e : r.ev_t) GGG_CUDA(cudaEventCreate(&e));
     const size_t W = static_cast<size_t>(g->world);
-    GGG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&r.h_box), (2 * (W + 1) + W * W + 16) * 8, cudaHostAllocDefault));
+    GGG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&r.h_box), (2 * (W + 1) + W * W + 16 + W + 2) * 8, cudaHostAllocDefault));
+    if (g->rank_form) GGG_CUDA(r.d_agree.ensure((W + 1) * 8));  // agree() must not allocate: it runs when allocations fail
     r.soff.assign(W + 1, 0);
     r.roff.assign(W + 1, 0);
     r.hsoff.assign(W + 1, 0);
@@ -296,6 +301,32 @@ gg_status gather_matrix(gg_group* g, const std::vector<std::vector<uint64_t>>& m
     GGG_CUDA(cudaMemcpyAsync(h, d, W * W * 8, cudaMemcpyDeviceToHost, r.st));
     GGG_CUDA(cudaStreamSynchronize(r.st));
     std::copy(h, h + W * W, mat.begin());
+    return GG_OK;
+}
+
+// Rank form: every rank learns the worst status any rank holds, so that all of them leave a call together.  Without it a
+// rank that fails a local check or an allocation returns while the others wait for it in the next collective, forever.
+// Called by every rank at the same points — before each data-path collective — with what the rank did since the last
+// one; costs one all-gather of 8 bytes per rank.  Single-process form: nothing to agree on.
+gg_status agree(gg_group* g, gg_status local) {
+    if (!g->rank_form || g->world == 1) return local;
+    Rk& r = g->rk[0];
+    const size_t W = static_cast<size_t>(g->world);
+    const std::string local_msg = g->err;
+    GGG_CUDA(cudaSetDevice(r.dev));
+    uint64_t* h = r.h_box + 2 * (W + 1) + W * W + 16;
+    uint64_t* d = r.d_agree.as<uint64_t>();
+    h[W] = static_cast<uint64_t>(local);
+    GGG_CUDA(cudaMemcpyAsync(d + r.rank, h + W, 8, cudaMemcpyHostToDevice, r.st));
+    GGG_NCCL(nccl().AllGather(d + r.rank, d, 1, ncclUint64, g->comm, r.st));
+    GGG_CUDA(cudaMemcpyAsync(h, d, W * 8, cudaMemcpyDeviceToHost, r.st));
+    GGG_CUDA(cudaStreamSynchronize(r.st));
+    if (local != GG_OK) {
+        g->err = local_msg;
+        return local;
+    }
+    for (size_t p = 0; p < W; ++p)
+        if (h[p] != GG_OK) return gfail(g, static_cast<gg_status>(h[p]), "rank " + std::to_string(p) + " failed this call (see its gg_group_last_error)");
     return GG_OK;
 }
 
@@ -435,7 +466,7 @@ gg_status route_phase(gg_group* g, Rk& r, const uint32_t* d_chrom, size_t n) {
         sorted_dest = in_alt ? r.dest_alt.as<uint32_t>() : r.dest.as<uint32_t>();
         r.perm_ptr = in_alt ? r.perm_alt.as<uint32_t>() : r.perm.as<uint32_t>();
     }
-    bucket_bounds_kernel<<<1, 256, 0, r.st>>>(sorted_dest, n, W, r.d_bounds.as<uint64_t>());
+    bucket_bounds_kernel<<<blocks_for(static_cast<size_t>(W) + 1, 256), 256, 0, r.st>>>(sorted_dest, n, W, r.d_bounds.as<uint64_t>());
     GGG_CUDA(cudaGetLastError());
     GGG_CUDA(cudaMemcpyAsync(r.h_box, r.d_bounds.p, (W + 1) * 8, cudaMemcpyDeviceToHost, r.st));
     return GG_OK;
@@ -469,16 +500,24 @@ double ms_between(cudaEvent_t a, cudaEvent_t b) {
 // The device-side core shared by the host-buffer and the device-buffer calls: every local rank r has its slice on its GPU
 // (r.q_c / r.q_s / r.q_e / r.nq).  On return r.f_off / r.f_hits (return_to_source) or r.r_off / r.r_hits / r.origin describe
 // the result; streams are synchronised.
-gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
+// `pre`: what the caller's own preparation (argument checks, upload of the slice) ended with; it takes part in the first
+// agreement, so a rank that failed there does not leave the others waiting.  Each phase between two collectives runs as a
+// lambda whose status is agreed on (agree()) before the collective that follows it.
+gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source, gg_status pre = GG_OK) {
     const int W = g->world;
     const size_t cb = static_cast<size_t>(coord_bytes);
-    for (Rk& r : g->rk) {
-        r.bytes_sent = r.bytes_received = 0;
-        GGG_CUDA(cudaSetDevice(r.dev));
-        GGG_CUDA(cudaEventRecord(r.ev_t[0], r.st));
-    }
     const bool chrom_mode = g->shard_mode == GG_SHARD_CHROM;
+    gg_status ph = pre;
+    if (ph == GG_OK) ph = [&]() -> gg_status {
+        for (Rk& r : g->rk) {
+            r.bytes_sent = r.bytes_received = 0;
+            GGG_CUDA(cudaSetDevice(r.dev));
+            GGG_CUDA(cudaEventRecord(r.ev_t[0], r.st));
+        }
+        return GG_OK;
+    }();
     if (!chrom_mode) {
+      if (ph == GG_OK) ph = [&]() -> gg_status {
         // ---- replicated index: answer the own slice, no exchange
         for (Rk& r : g->rk) {
             GGG_CUDA(cudaSetDevice(r.dev));
@@ -516,6 +555,10 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
             r.n_hits_final = r.n_hits_owner;
             if (r.nq >= 65536) r.hits_per_query = std::max(1.0, static_cast<double>(r.n_hits_owner) / static_cast<double>(r.nq));
         }
+        return GG_OK;
+      }();
+        ph = agree(g, ph);
+        if (ph != GG_OK) return ph;
         // the path's one collective: hit totals of every rank (8 bytes each) -> global CSR base of each slice
         std::vector<std::vector<uint64_t>> mine(g->rk.size(), std::vector<uint64_t>(static_cast<size_t>(W), 0));
         for (size_t i = 0; i < g->rk.size(); ++i) mine[i][0] = g->rk[i].n_hits_owner;
@@ -532,6 +575,8 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
     }
 
     // ---- chromosome-sharded: route -> counts -> exchange -> answer -> (return)
+    std::vector<std::vector<uint64_t>> mine(g->rk.size(), std::vector<uint64_t>(static_cast<size_t>(W), 0));
+    if (ph == GG_OK) ph = [&]() -> gg_status {
     for (Rk& r : g->rk) {
         gg_status s = route_phase(g, r, r.q_c, r.nq);
         if (s != GG_OK) return s;
@@ -555,7 +600,6 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
         }
         GGG_CUDA(cudaEventRecord(r.ev_t[1], r.st));
     }
-    std::vector<std::vector<uint64_t>> mine(g->rk.size(), std::vector<uint64_t>(static_cast<size_t>(W), 0));
     for (size_t i = 0; i < g->rk.size(); ++i) {
         Rk& r = g->rk[i];
         GGG_CUDA(cudaSetDevice(r.dev));
@@ -563,9 +607,14 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
         for (int p = 0; p <= W; ++p) r.soff[p] = r.h_box[p];
         for (int p = 0; p < W; ++p) mine[i][p] = r.soff[p + 1] - r.soff[p];
     }
+    return GG_OK;
+    }();
+    ph = agree(g, ph);
+    if (ph != GG_OK) return ph;
     std::vector<uint64_t> mat;
     gg_status s = gather_matrix(g, mine, mat);
     if (s != GG_OK) return s;
+    ph = [&]() -> gg_status {
     for (Rk& r : g->rk) {
         recv_offsets_from(mat, W, r.rank, r.roff);
         r.n_recv = r.roff[W];
@@ -577,6 +626,10 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
         if (!return_to_source) GGG_CUDA(r.recv_o.ensure(m * 4));
         GGG_CUDA(r.r_off.ensure((m + 1) * 8));
     }
+    return GG_OK;
+    }();
+    ph = agree(g, ph);
+    if (ph != GG_OK) return ph;
     {
         std::vector<Col> cols = {{[](Rk& r) { return r.send_c.p; }, [](Rk& r) { return r.recv_c.p; }, 4},
                                  {[](Rk& r) { return r.send_s.p; }, [](Rk& r) { return r.recv_s.p; }, cb},
@@ -586,6 +639,7 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
                        [](Rk& r) -> const std::vector<uint64_t>& { return r.roff; });
         if (s != GG_OK) return s;
     }
+    ph = [&]() -> gg_status {
     for (Rk& r : g->rk) {
         GGG_CUDA(cudaSetDevice(r.dev));
         GGG_CUDA(cudaEventRecord(r.ev_t[2], r.st));
@@ -624,6 +678,10 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
         GGG_CUDA(cudaEventRecord(r.ev_t[3], r.st));
         if (r.n_recv >= 65536) r.hits_per_query = std::max(1.0, static_cast<double>(r.n_hits_owner) / static_cast<double>(r.n_recv));
     }
+    return GG_OK;
+    }();
+    ph = agree(g, ph);  // (also when the results stay on the owner: every rank reports the same outcome)
+    if (ph != GG_OK) return ph;
     if (!return_to_source) {
         for (Rk& r : g->rk) {
             GGG_CUDA(cudaSetDevice(r.dev));
@@ -646,6 +704,7 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
     }
     s = gather_matrix(g, mine, mat);
     if (s != GG_OK) return s;
+    ph = [&]() -> gg_status {
     for (Rk& r : g->rk) {
         // hits coming back to r from owner p = mat[p * W + r.rank]
         recv_offsets_from(mat, W, r.rank, r.hroff);
@@ -665,6 +724,10 @@ gg_status intersect_core(gg_group* g, int coord_bytes, bool return_to_source) {
         GGG_CUDA(r.f_hits.ensure((r.n_hits_final ? r.n_hits_final : 1) * 4));
         GGG_CUDA(r.scan2.ensure(scan_state_bytes(m)));
     }
+    return GG_OK;
+    }();
+    ph = agree(g, ph);
+    if (ph != GG_OK) return ph;
     s = all_to_all(g, {{[](Rk& r) { return r.r_cnt.p; }, [](Rk& r) { return r.b_cnt.p; }, 4}},
                    [](Rk& r) -> const std::vector<uint64_t>& { return r.roff; },
                    [](Rk& r) -> const std::vector<uint64_t>& { return r.soff; });
@@ -813,7 +876,7 @@ void gg_group_destroy(gg_group* g) {
         for (DeviceBuf* b : {&r.d_owner, &r.d_local, &r.in_c, &r.in_s, &r.in_e, &r.dest, &r.dest_alt, &r.perm, &r.perm_alt, &r.lchrom,
                              &r.hist, &r.scanst, &r.d_bounds, &r.send_c, &r.send_s, &r.send_e, &r.send_o, &r.recv_c, &r.recv_s,
                              &r.recv_e, &r.recv_o, &r.r_off, &r.r_hits, &r.r_cnt, &r.origin, &r.d_seg, &r.b_cnt, &r.b_off, &r.b_hits,
-                             &r.f_cnt, &r.f_off, &r.f_hits, &r.scan2, &r.d_mat})
+                             &r.f_cnt, &r.f_off, &r.f_hits, &r.scan2, &r.d_mat, &r.d_agree})
             b->release();
         if (r.idx) gg_index_destroy(r.idx);
         if (r.h_box) cudaFreeHost(r.h_box);
@@ -888,10 +951,17 @@ gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, con
 
     // ---- GG_SHARD_CHROM: per-chromosome interval counts of the whole input -> LPT owners (identical on every rank)
     std::vector<uint64_t> counts(n_chrom, 0);
-    for (size_t i = 0; i < n; ++i) {
-        if (chrom[i] >= n_chrom) return gfail(g, GG_ERR_INVALID_ARG, "chrom id >= n_chrom in index input");
-        ++counts[chrom[i]];
-    }
+    gg_status ph = [&]() -> gg_status {
+        // (rank form: n is this rank's part; the routing below carries the record's index in it as a u32)
+        if (g->rank_form && n >= 0xFFFFFFFFull) return gfail(g, GG_ERR_CAPACITY, "more than 2^32-2 input records on one rank");
+        for (size_t i = 0; i < n; ++i) {
+            if (chrom[i] >= n_chrom) return gfail(g, GG_ERR_INVALID_ARG, "chrom id >= n_chrom in index input");
+            ++counts[chrom[i]];
+        }
+        return GG_OK;
+    }();
+    ph = agree(g, ph);  // one rank's bad record fails the build on every rank instead of leaving the others in the gather
+    if (ph != GG_OK) return ph;
     std::vector<uint64_t> n_per_rank(static_cast<size_t>(W), 0);  // input records held by each rank (rank form)
     if (g->rank_form) {
         // all-gather of the per-rank histograms in slabs of W values (the same 8-byte-per-entry collective), summed on the host
@@ -914,14 +984,15 @@ gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, con
     }
     lpt_assign(counts.data(), n_chrom, W, g->owner.data());
     gg_status s = upload_routing(g);
-    if (s != GG_OK) return s;
+    if (s != GG_OK && !g->rank_form) return s;
+    ph = s;  // (rank form: agreed on below, together with the upload and the partition)
     std::vector<uint32_t> n_local_chrom(static_cast<size_t>(W), 0);
     for (uint32_t c = 0; c < n_chrom; ++c) ++n_local_chrom[g->owner[c]];
 
     if (!g->rank_form) {
         // single process: stable host partition of the records by owner, then one device build per GPU, in parallel
-        std::vector<std::vector<uint32_t>> lc(W), src(W);
-        std::vector<std::vector<uint64_t>> ls(W), le(W), lt(W);
+        std::vector<std::vector<uint32_t>> lc(W);
+        std::vector<std::vector<uint64_t>> ls(W), le(W), lt(W), src(W);  // src: global input index (the total may pass 2^32)
         std::vector<uint64_t> per_rank(static_cast<size_t>(W), 0);
         for (uint32_t c = 0; c < n_chrom; ++c) per_rank[g->owner[c]] += counts[c];
         for (int r = 0; r < W; ++r) {
@@ -934,7 +1005,7 @@ gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, con
         for (size_t i = 0; i < n; ++i) {
             const uint32_t o = g->owner[chrom[i]];
             lc[o].push_back(g->local_id[chrom[i]]);
-            src[o].push_back(static_cast<uint32_t>(i));
+            src[o].push_back(i);
             ls[o].push_back(start[i]);
             le[o].push_back(end[i]);
             if (tie_mode == GG_TIE_EXPLICIT) lt[o].push_back(tie_key[i]);
@@ -978,6 +1049,8 @@ gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, con
         } guard{{&in_c, &in_s, &in_e, &in_t, &s_c, &s_s, &s_e, &s_t, &s_o, &v_c, &v_s, &v_e, &v_t, &v_o, &d_perm, &d_r2i}};
         const size_t nn = n ? n : 1;
         const bool tie = tie_mode == GG_TIE_EXPLICIT;
+        std::vector<std::vector<uint64_t>> mine(1, std::vector<uint64_t>(static_cast<size_t>(W), 0));
+        if (ph == GG_OK) ph = [&]() -> gg_status {
         GGG_CUDA(in_c.ensure(nn * 4));
         GGG_CUDA(in_s.ensure(nn * 8));
         GGG_CUDA(in_e.ensure(nn * 8));
@@ -1005,19 +1078,32 @@ gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, con
             GGG_CUDA(cudaGetLastError());
         }
         GGG_CUDA(cudaStreamSynchronize(r.st));
-        std::vector<std::vector<uint64_t>> mine(1, std::vector<uint64_t>(static_cast<size_t>(W), 0));
         for (int p = 0; p <= W; ++p) r.soff[p] = r.h_box[p];
         for (int p = 0; p < W; ++p) mine[0][p] = r.soff[p + 1] - r.soff[p];
+        return GG_OK;
+        }();
+        ph = agree(g, ph);
+        if (ph != GG_OK) return ph;
         std::vector<uint64_t> mat;
         s = gather_matrix(g, mine, mat);
         if (s != GG_OK) return s;
         recv_offsets_from(mat, W, r.rank, r.roff);
         const size_t m = r.roff[W], mm = m ? m : 1;
-        GGG_CUDA(v_c.ensure(mm * 4));
-        GGG_CUDA(v_s.ensure(mm * 8));
-        GGG_CUDA(v_e.ensure(mm * 8));
-        GGG_CUDA(v_o.ensure(mm * 4));
-        if (tie) GGG_CUDA(v_t.ensure(mm * 8));
+        ph = [&]() -> gg_status {
+            // known as soon as the matrix is: checked here, before the exchange, so that every rank hears of it
+            if (rank_to_input && n_owned_capacity < m) {
+                if (n_owned) *n_owned = m;
+                return gfail(g, GG_ERR_CAPACITY, "rank_to_input buffer too small for the intervals this rank owns");
+            }
+            GGG_CUDA(v_c.ensure(mm * 4));
+            GGG_CUDA(v_s.ensure(mm * 8));
+            GGG_CUDA(v_e.ensure(mm * 8));
+            GGG_CUDA(v_o.ensure(mm * 4));
+            if (tie) GGG_CUDA(v_t.ensure(mm * 8));
+            return GG_OK;
+        }();
+        ph = agree(g, ph);
+        if (ph != GG_OK) return ph;
         // (the column buffers are locals of this call: pass them through the rank context's generic slots)
         r.send_c.borrow(s_c.p, s_c.cap);
         r.send_s.borrow(s_s.p, s_s.cap);
@@ -1049,7 +1135,6 @@ gg_status gg_group_build(gg_group* g, int shard_mode, const uint32_t* chrom, con
                                          rank_to_input ? d_perm.as<uint32_t>() : nullptr));
         if (n_owned) *n_owned = m;
         if (rank_to_input) {
-            if (n_owned_capacity < m) return gfail(g, GG_ERR_CAPACITY, "rank_to_input buffer too small for the intervals this rank owns");
             // chain rank -> received position -> (source rank, index in the source's input) -> global input index
             std::vector<uint32_t> h_perm(m), h_orig(m);
             if (m) {
@@ -1078,15 +1163,18 @@ gg_status gg_group_intersect_device(gg_group* g, const uint32_t* d_chrom, const 
     if (!g->built) return gfail(g, GG_ERR_NOT_BUILT, "group not built");
     if (g->rk.size() != 1) return gfail(g, GG_ERR_INVALID_ARG, "the device-buffer call drives one GPU per process (rank form, or a group of one)");
     if (coord_bytes != 4 && coord_bytes != 8) return gfail(g, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
-    if (nq && (!d_chrom || !d_start || !d_end)) return gfail(g, GG_ERR_INVALID_ARG, "null argument");
-    if (nq >= 0xFFFFFFFFull) return gfail(g, GG_ERR_CAPACITY, "more than 2^32-2 queries per rank and call");
+    // what depends on this rank's slice is not returned at once: the other ranks are about to enter the call's
+    // collectives, so the failure goes through intersect_core's first agreement and every rank returns it
+    gg_status pre = GG_OK;
+    if (nq && (!d_chrom || !d_start || !d_end)) pre = gfail(g, GG_ERR_INVALID_ARG, "null argument");
+    else if (nq >= 0xFFFFFFFFull) pre = gfail(g, GG_ERR_CAPACITY, "more than 2^32-2 queries per rank and call");
     Rk& r = g->rk[0];
     r.q_c = d_chrom;
     r.q_s = d_start;
     r.q_e = d_end;
-    r.nq = nq;
+    r.nq = pre == GG_OK ? nq : 0;
     const bool back = return_to_source != 0 || g->shard_mode == GG_SHARD_REPLICATE;
-    gg_status s = intersect_core(g, coord_bytes, back);
+    gg_status s = intersect_core(g, coord_bytes, back, pre);
     if (s != GG_OK) return s;
     collect_stats(g, back);
     *out = gg_group_device_result{};
@@ -1118,14 +1206,17 @@ gg_status gg_group_intersect_batch(gg_group* g, const uint32_t* q_chrom, const v
     if (!g) return GG_ERR_INVALID_ARG;
     g->err.clear();
     if (!g->built) return gfail(g, GG_ERR_NOT_BUILT, "group not built");
-    if (!offsets || !hits || !n_hits || (nq && (!q_chrom || !q_start || !q_end))) return gfail(g, GG_ERR_INVALID_ARG, "null argument");
     if (coord_bytes != 4 && coord_bytes != 8) return gfail(g, GG_ERR_INVALID_ARG, "coord_bytes must be 4 or 8");
     const size_t L = g->rk.size();
     const size_t cb = static_cast<size_t>(coord_bytes);
-    if (nq / L >= 0xFFFFFFF0ull) return gfail(g, GG_ERR_CAPACITY, "more than 2^32-16 queries per GPU and call");
     // contiguous slices of the batch, one per local GPU (rank form: the caller's batch IS this rank's slice)
     std::vector<size_t> lo(L + 1, 0);
     for (size_t i = 0; i < L; ++i) lo[i + 1] = lo[i] + nq / L + (i < nq % L ? 1 : 0);
+    // checks and uploads that depend on this rank's slice: a failure is agreed on inside intersect_core (rank form), not
+    // returned while the other ranks enter the collectives
+    gg_status pre = [&]() -> gg_status {
+    if (!offsets || !hits || !n_hits || (nq && (!q_chrom || !q_start || !q_end))) return gfail(g, GG_ERR_INVALID_ARG, "null argument");
+    if (nq / L >= 0xFFFFFFF0ull) return gfail(g, GG_ERR_CAPACITY, "more than 2^32-16 queries per GPU and call");
     for (size_t i = 0; i < L; ++i) {
         Rk& r = g->rk[i];
         const size_t m = lo[i + 1] - lo[i], mm = m ? m : 1;
@@ -1143,7 +1234,10 @@ gg_status gg_group_intersect_batch(gg_group* g, const uint32_t* q_chrom, const v
         r.q_e = r.in_e.p;
         r.nq = m;
     }
-    gg_status s = intersect_core(g, coord_bytes, true);
+    return GG_OK;
+    }();
+    if (pre != GG_OK && !g->rank_form) return pre;
+    gg_status s = intersect_core(g, coord_bytes, true, pre);
     if (s != GG_OK) return s;
     collect_stats(g, true);
     const bool rep = g->shard_mode == GG_SHARD_REPLICATE;

@@ -297,14 +297,58 @@ class batch_result {
     /// Copy the rank array out of the library's pinned buffer into this object: afterwards the result survives later
     /// queries on the grove (it still refers to the grove's keys, so not its mutation or destruction).  Costs one memcpy of
     /// 4 bytes per hit; results that are consumed before the next query do not need it.
-    batch_result& keep() {
+    batch_result& keep() & {
         if (hits_ != nullptr && hits_ != owned_.data()) {
             owned_.assign(hits_, hits_ + n_hits_);
             hits_ = owned_.data();
         }
         return *this;
     }
+    /// `auto r = g.intersect_batch(...).keep();` — on a temporary the kept result is handed over by value
+    [[nodiscard]] batch_result keep() && {
+        keep();
+        return std::move(*this);
+    }
     [[nodiscard]] bool owns_ranks() const noexcept { return hits_ == owned_.data() && hits_ != nullptr; }
+
+    batch_result() = default;
+    ~batch_result() = default;
+    /// A kept result's rank pointer refers to its own vector: copies and moves re-seat it (a copy of a view stays a view).
+    batch_result(const batch_result& o)
+        : offsets_(o.offsets_), hits_(o.hits_), n_hits_(o.n_hits_), owned_(o.owned_), q_index_(o.q_index_), chains_(o.chains_) {
+        if (o.owns_ranks()) hits_ = owned_.data();
+    }
+    batch_result(batch_result&& o) noexcept
+        : offsets_(std::move(o.offsets_)), hits_(o.hits_), n_hits_(o.n_hits_), q_index_(std::move(o.q_index_)),
+          chains_(std::move(o.chains_)) {
+        const bool owned = o.owns_ranks();
+        owned_ = std::move(o.owned_);
+        if (owned) hits_ = owned_.data();
+        o.hits_ = nullptr;
+        o.n_hits_ = 0;
+    }
+    batch_result& operator=(const batch_result& o) {
+        if (this != &o) {
+            batch_result tmp(o);
+            *this = std::move(tmp);
+        }
+        return *this;
+    }
+    batch_result& operator=(batch_result&& o) noexcept {
+        if (this != &o) {
+            const bool owned = o.owns_ranks();
+            offsets_ = std::move(o.offsets_);
+            hits_ = o.hits_;
+            n_hits_ = o.n_hits_;
+            owned_ = std::move(o.owned_);
+            q_index_ = std::move(o.q_index_);
+            chains_ = std::move(o.chains_);
+            if (owned) hits_ = owned_.data();
+            o.hits_ = nullptr;
+            o.n_hits_ = 0;
+        }
+        return *this;
+    }
 
   private:
     template <typename, typename, typename>

@@ -770,6 +770,26 @@ static void test_batch_entry_point() {
         bool ok = true;
         for (std::size_t i = 0; i < nq; i += 3) ok = ok && kept.get_keys(i) == got[i];
         CHECK(ok);
+        // chained on the temporary: the result is moved out, its ranks are its own
+        auto chained = g.intersect_batch(qc.data(), qs.data(), qe.data(), nq).keep();
+        CHECK(chained.owns_ranks());
+        // copies of a kept result own their ranks too (copy construction, copy assignment, move)
+        auto copy = chained;
+        CHECK(copy.owns_ranks() && copy.ranks().data() != chained.ranks().data());
+        decltype(chained) assigned;
+        assigned = chained;
+        CHECK(assigned.owns_ranks() && assigned.ranks().data() != chained.ranks().data());
+        auto moved = std::move(chained);
+        CHECK(moved.owns_ranks());
+        (void)g.intersect_batch(qc.data(), qe.data(), qe.data(), nq);  // overwrites the library's pinned buffer again
+        bool ok2 = true;
+        for (std::size_t i = 0; i < nq; i += 3)
+            ok2 = ok2 && copy.get_keys(i) == got[i] && assigned.get_keys(i) == got[i] && moved.get_keys(i) == got[i];
+        CHECK(ok2);
+        // a copy of a plain view stays a view of the library's buffer
+        auto view = g.intersect_batch(qc.data(), qs.data(), qe.data(), nq);
+        auto view2 = view;
+        CHECK(!view2.owns_ranks() && view2.ranks().data() == view.ranks().data());
     }
     std::vector<std::uint64_t> bad_s{10}, bad_e{5};
     std::vector<std::uint32_t> bad_c{ids[0]};

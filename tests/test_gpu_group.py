@@ -159,6 +159,34 @@ for mode in (gg.SHARD_CHROM, gg.SHARD_REPLICATE):
     st = grp.stats()
     if mode == gg.SHARD_CHROM:
         ok &= bool(st.bytes_sent > 0)
+# ---- a failure on ONE rank ends the call on EVERY rank with that rank's status: nobody is left waiting in a collective
+def status_of(fn):
+    try:
+        fn()
+        return 0, ""
+    except gg.GGError as e:
+        return e.status, str(e)
+bad = chrom[lo_i:hi_i].copy()
+if rank == world - 1:
+    bad[len(bad) // 2] = n_chrom + 5                       # one bad record in one rank's part of the input
+st, msg = status_of(lambda: grp.build(gg.SHARD_CHROM, bad, start[lo_i:hi_i], end[lo_i:hi_i], n_chrom, want_perm=False))
+ok &= st == 1 and (("rank %d failed" % (world - 1)) in msg if rank == 0 else "chrom id" in msg)
+# rank_to_input too small on one rank: known only after the count matrix, reported before the exchange
+st, msg = status_of(lambda: grp.build(gg.SHARD_CHROM, chrom[lo_i:hi_i], start[lo_i:hi_i], end[lo_i:hi_i], n_chrom,
+                                      owned_capacity=1 if rank == world - 1 else len(chrom)))
+ok &= st == 7
+for mode in (gg.SHARD_CHROM, gg.SHARD_REPLICATE):
+    grp.build(mode, chrom[lo_i:hi_i] if mode == gg.SHARD_CHROM else chrom, start[lo_i:hi_i] if mode == gg.SHARD_CHROM else start,
+              end[lo_i:hi_i] if mode == gg.SHARD_CHROM else end, n_chrom, want_perm=False)
+    big = np.tile(np.arange(lo, hi), 3)                    # a larger slice than any before: the upload buffers must grow
+    if rank == world - 1:
+        grp.set_option("inject_alloc_failure", 1)          # ... and on one rank the first allocation fails
+    ok &= status_of(lambda: grp.intersect_batch(qc[big], qs[big].astype(np.uint32), qe[big].astype(np.uint32)))[0] == 3
+    grp.set_option("inject_alloc_failure", 0)
+    # the group is usable afterwards
+    off, hits, base = grp.intersect_batch(qc[lo:hi], qs[lo:hi].astype(np.uint32), qe[lo:hi].astype(np.uint32))
+    ok &= bool(np.array_equal(off + np.uint64(base), exp_off[lo:hi + 1]))
+    ok &= bool(np.array_equal(hits, exp_hits[int(exp_off[lo]):int(exp_off[hi])]))
 t = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
 if rank == 0:
