@@ -267,6 +267,9 @@ inline constexpr strand_compatible_t strand_compatible{};
 struct detached_t {};
 inline constexpr detached_t detached{};
 
+template <typename key_type, typename data_type>
+class compact_batch_result;
+
 /// Result of grove::intersect_batch: CSR over the batch.  Query q's hits are ranks()[offsets()[q] ..
 /// offsets()[q+1]) — leaf-chain ranks inside the query's index, ascending — and key(q, j) maps them back to the
 /// grove's key pointers.  Valid until the grove is mutated, queried again or destroyed (the rank array is the
@@ -353,12 +356,60 @@ class batch_result {
   private:
     template <typename, typename, typename>
     friend class grove;
+    template <typename, typename>
+    friend class compact_batch_result;  // expand() fills one
     std::vector<std::uint64_t> offsets_;
     const std::uint32_t* hits_ = nullptr;
     std::uint64_t n_hits_ = 0;
     std::vector<std::uint32_t> owned_;                         // keep(): the ranks, once copied out of the pinned buffer
     std::vector<std::uint32_t> q_index_;                       // copy of the per-query index ids
     std::vector<const std::vector<key_ptr>*> chains_;          // index id -> chain (rank -> key*)
+};
+
+/// Result of grove::intersect_batch_compact: the same hits as intersect_batch in the form that crosses PCIe cheapest
+/// (gg_intersect_batch_compact: 8 bytes per query + 1-4 bytes per hit instead of 8 + 4) and is read in place — the host
+/// call is copy-bound, so on BED/BAM-shaped batches this form is 2-3x the plain CSR end to end.  count / rank / key decode
+/// on the fly; expand() materialises the plain CSR for callers that need arrays.  A view of the library's pinned
+/// buffers: valid until the grove is mutated, queried again or destroyed.
+template <typename key_type, typename data_type>
+class compact_batch_result {
+  public:
+    using key_ptr = gdt::key<key_type, data_type>*;
+    [[nodiscard]] std::size_t size() const noexcept { return static_cast<std::size_t>(res_.n_queries); }
+    [[nodiscard]] std::uint64_t total_hits() const noexcept { return res_.n_hits; }
+    [[nodiscard]] std::size_t count(std::size_t q) const { return static_cast<std::size_t>(gg_compact_count(&res_, q)); }
+    /// j-th hit of query q as a leaf-chain rank inside the query's index, ascending in j
+    [[nodiscard]] std::uint32_t rank(std::size_t q, std::size_t j) const { return gg_compact_rank(&res_, q_index_.data(), q, j); }
+    [[nodiscard]] key_ptr key(std::size_t q, std::size_t j) const { return (*chains_[q_index_[q]])[rank(q, j)]; }
+    [[nodiscard]] std::vector<key_ptr> get_keys(std::size_t q) const {
+        const std::size_t n = count(q);
+        std::vector<key_ptr> out;
+        out.reserve(n);
+        for (std::size_t j = 0; j < n; ++j) out.push_back(key(q, j));
+        return out;
+    }
+    /// the C-ABI view (chunk table, per-query records, delta bytes) for callers that decode in their own loops
+    [[nodiscard]] const gg_compact_result& raw() const noexcept { return res_; }
+    /// The plain CSR with its own rank array (survives later queries, like batch_result::keep()).  n_threads <= 0: all cores.
+    [[nodiscard]] batch_result<key_type, data_type> expand(int n_threads = 0) const {
+        batch_result<key_type, data_type> r;
+        r.offsets_.resize(size() + 1);
+        r.owned_.resize(static_cast<std::size_t>(res_.n_hits) + 1);
+        const gg_status st = gg_compact_expand(&res_, q_index_.data(), r.offsets_.data(), r.owned_.data(), n_threads);
+        if (st != GG_OK) throw device_error(st, "gg_compact_expand");
+        r.hits_ = r.owned_.data();
+        r.n_hits_ = res_.n_hits;
+        r.q_index_ = q_index_;
+        r.chains_ = chains_;
+        return r;
+    }
+
+  private:
+    template <typename, typename, typename>
+    friend class grove;
+    gg_compact_result res_{};
+    std::vector<std::uint32_t> q_index_;
+    std::vector<const std::vector<key_ptr>*> chains_;
 };
 
 template <typename key_type, typename data_type = void, typename edge_data_type = void>
@@ -639,6 +690,32 @@ class grove {
         batch_result<key_type, data_type> r;
         r.offsets_.resize(nq + 1);
         check(gg_intersect_batch(dev.get(), q_index, q_start, q_end, nq, r.offsets_.data(), &r.hits_, &r.n_hits_));
+        r.q_index_.assign(q_index, q_index + nq);
+        r.chains_ = chain_by_id;
+        return r;
+    }
+    /// The same with 32-bit coordinates (BED / SAM / hg38-sized; needs a grove whose coordinates all fit 32 bits, which the
+    /// device snapshot then stores as u32): 12 instead of 20 bytes per query over PCIe (gg_intersect_batch_u32).
+    [[nodiscard]] batch_result<key_type, data_type> intersect_batch(const std::uint32_t* q_index, const std::uint32_t* q_start,
+                                                                    const std::uint32_t* q_end, std::size_t nq)
+        requires(!stranded) {
+        sync();
+        batch_result<key_type, data_type> r;
+        r.offsets_.resize(nq + 1);
+        check(gg_intersect_batch_u32(dev.get(), q_index, q_start, q_end, nq, r.offsets_.data(), &r.hits_, &r.n_hits_));
+        r.q_index_.assign(q_index, q_index + nq);
+        r.chains_ = chain_by_id;
+        return r;
+    }
+    /// ... and with the result left in the compact form (gg_intersect_batch_compact), read in place: the fastest way to
+    /// put a host-resident batch through the device (bench.py's `e2e`).  Same hits, same order.
+    [[nodiscard]] compact_batch_result<key_type, data_type> intersect_batch_compact(const std::uint32_t* q_index,
+                                                                                    const std::uint32_t* q_start,
+                                                                                    const std::uint32_t* q_end, std::size_t nq)
+        requires(!stranded) {
+        sync();
+        compact_batch_result<key_type, data_type> r;
+        check(gg_intersect_batch_compact(dev.get(), q_index, q_start, q_end, nq, &r.res_));
         r.q_index_.assign(q_index, q_index + nq);
         r.chains_ = chain_by_id;
         return r;

@@ -791,6 +791,25 @@ static void test_batch_entry_point() {
         auto view2 = view;
         CHECK(!view2.owns_ranks() && view2.ranks().data() == view.ranks().data());
     }
+    {   // 32-bit coordinates: the u32 call and the compact result form give the same keys in the same order
+        std::vector<std::uint32_t> qs32(qs.begin(), qs.end()), qe32(qe.begin(), qe.end());
+        auto b32 = g.intersect_batch(qc.data(), qs32.data(), qe32.data(), nq);
+        CHECK(b32.size() == nq && b32.total_hits() == br.total_hits());
+        bool ok = true;
+        for (std::size_t i = 0; i < nq; ++i) ok = ok && b32.get_keys(i) == got[i];
+        CHECK(ok);
+        auto cr = g.intersect_batch_compact(qc.data(), qs32.data(), qe32.data(), nq);
+        CHECK(cr.size() == nq && cr.total_hits() == br.total_hits());
+        bool okc = true;
+        for (std::size_t i = 0; i < nq; ++i) okc = okc && cr.count(i) == got[i].size() && cr.get_keys(i) == got[i];
+        CHECK(okc);
+        auto ex = cr.expand();
+        CHECK(ex.owns_ranks() && ex.total_hits() == br.total_hits());
+        (void)g.intersect_batch(qc.data(), qe.data(), qe.data(), nq);  // the expanded CSR owns its ranks
+        bool oke = true;
+        for (std::size_t i = 0; i < nq; ++i) oke = oke && ex.get_keys(i) == got[i];
+        CHECK(oke);
+    }
     std::vector<std::uint64_t> bad_s{10}, bad_e{5};
     std::vector<std::uint32_t> bad_c{ids[0]};
     CHECK_THROWS(g.intersect_batch(bad_c.data(), bad_s.data(), bad_e.data(), 1), std::invalid_argument);
